@@ -1,0 +1,86 @@
+/* serenade_b200 C ABI -- the drop-in boundary for Serenade's CFM mel-infilling decoder hot path.
+ *
+ * The reference (imulki/serenade) is pure Python/PyTorch and has no FFI of its own; the seam this
+ * library replaces is the Python operator API of
+ *   serenade/models/matcha_components/flow_matching.py:10-19  CFM.__init__      -> srn_create
+ *   torch load_state_dict of `cfm_decoder.estimator.*` keys   (bin/ssc_decode.py:339) -> srn_load_weight / srn_finalize_weights
+ *   decoder.py:384-467   Decoder.forward(x, mask, mu, t, spk) -> srn_estimator_forward
+ *   flow_matching.py:65-93  CFM.solve_euler(x, t_span, mu, mask, spk) -> srn_solve_euler / srn_solve_euler_host
+ * Plain pointers and sizes only; no torch types.  All functions return 0 on success, non-zero on
+ * failure with a message available from srn_last_error().  A handle is bound to the CUDA device that
+ * was current at srn_create and is not thread-safe.  There is no CPU fallback: every entry point
+ * fails if no sm_100 device is present.
+ *
+ * Tensor layouts are the reference's: x, v (B, 80, T) f32 channels-first; mu (B, C_mu, T) f32;
+ * mask (B, T) uint8 (non-zero = valid frame; the reference's bool (B,1,T)); spk (B, spk_dim) f32.
+ */
+#ifndef SERENADE_B200_H_
+#define SERENADE_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct SrnHandle SrnHandle;
+
+enum { SRN_PRECISION_BF16 = 0, SRN_PRECISION_TF32 = 1 };
+
+typedef struct SrnConfig {
+  int32_t in_channels;        /* x + mu channels: 242 (Serenade) or 244 (SerenadeNew); <= 256 */
+  int32_t out_channels;       /* 80 */
+  int32_t spk_embed_dim;      /* 256 */
+  int32_t channels;           /* 512 (decoder_channels = (512, 512)) */
+  int32_t num_heads;          /* 4 */
+  int32_t attention_head_dim; /* 512 */
+  int32_t num_mid_blocks;     /* 2 */
+  int32_t precision;          /* SRN_PRECISION_* : GEMM operand type (accumulation is always f32) */
+} SrnConfig;
+
+const char* srn_last_error(void);
+int srn_version(void);
+
+int srn_create(const SrnConfig* cfg, SrnHandle** out);
+int srn_destroy(SrnHandle* h);
+
+/* Copy one parameter of the reference state dict (key relative to `cfm_decoder.`, i.e.
+ * "estimator.down_blocks.0.0.block1.block.0.weight"), f32, HOST memory, dims in torch order. */
+int srn_load_weight(SrnHandle* h, const char* key, const float* host_data, int32_t ndim, const int64_t* dims);
+/* Validate that every expected key arrived with the expected shape, repack (K-major conv taps, fused QKV,
+ * interleaved GEGLU, split transposed-conv parities, operand dtype) and upload. */
+int srn_finalize_weights(SrnHandle* h);
+
+/* v = Decoder.forward(x, mask, mu, t, spk).  DEVICE pointers.  `stream` is a cudaStream_t. */
+int srn_estimator_forward(SrnHandle* h, const float* x, const float* mu, const uint8_t* mask, const float* spk,
+                          float t, int32_t B, int32_t T, float* v_out, void* stream);
+
+/* x <- solve_euler(x, t_span, mu, mask, spk) in place on DEVICE memory.  t_span is a HOST array of
+ * n_steps + 1 f32 values.  blend_mask / blend_src (DEVICE, nullable): optional infill blend, after
+ * every step x[b,:,t] = blend_src[b,:,t] where blend_mask[b,t] != 0.  The reference has no blend
+ * (flow_matching.py:87); pass NULL for reference behaviour. */
+int srn_solve_euler(SrnHandle* h, float* x_inout, const float* mu, const uint8_t* mask, const float* spk,
+                    const float* t_span_host, int32_t n_steps, int32_t B, int32_t T, const uint8_t* blend_mask,
+                    const float* blend_src, void* stream);
+
+/* Same with HOST buffers (pinned for best speed): uploads z/mu/mask/spk, solves, downloads the mel. */
+int srn_solve_euler_host(SrnHandle* h, const float* z_host, const float* mu_host, const uint8_t* mask_host,
+                         const float* spk_host, const float* t_span_host, int32_t n_steps, int32_t B, int32_t T,
+                         float* mel_out_host, void* stream);
+
+/* Number of kernels of this library launched since the handle was created. */
+int64_t srn_launch_count(const SrnHandle* h);
+/* Use one CUDA graph per (B, T, n_steps) for srn_solve_euler (default 1). */
+int srn_set_use_graph(SrnHandle* h, int32_t enable);
+
+/* Test hooks: when enabled, every named intermediate of the next forward is kept (as f32, channels-last
+ * (B, rows, cols)) and can be fetched by name.  srn_debug_fetch returns the element count via *n_out
+ * and copies min(capacity, n) values. */
+int srn_debug_enable(SrnHandle* h, int32_t enable);
+int srn_debug_fetch(SrnHandle* h, const char* name, float* host_out, int64_t capacity, int64_t* n_out,
+                    int32_t* rows_out, int32_t* cols_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SERENADE_B200_H_ */

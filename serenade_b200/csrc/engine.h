@@ -1,0 +1,47 @@
+// Host-side engine: weight repacking, per-(B,T) execution plans (buffers + TMA maps + op list),
+// the estimator forward and the Euler solve loop (optionally replayed as one CUDA graph).
+#pragma once
+#include <memory>
+
+#include "../../include/serenade_b200.h"
+#include "common.h"
+#include "gemm.cuh"
+
+namespace srn {
+
+struct HostTensor {
+  std::vector<float> data;
+  std::vector<int64_t> dims;
+};
+
+struct DebugTensor {
+  std::vector<float> data;   // (B, rows, cols)
+  int B = 0, rows = 0, cols = 0;
+};
+
+class EngineBase {
+ public:
+  virtual ~EngineBase() = default;
+  virtual void load_weight(const std::string& key, const float* data, int ndim, const int64_t* dims) = 0;
+  virtual void finalize_weights() = 0;
+  virtual void estimator_forward(const float* x, const float* mu, const uint8_t* mask, const float* spk, float t,
+                                 int B, int T, float* v_out, cudaStream_t st) = 0;
+  virtual void solve_euler(float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
+                           int n_steps, int B, int T, const uint8_t* blend_mask, const float* blend_src,
+                           cudaStream_t st) = 0;
+  virtual void solve_euler_host(const float* z, const float* mu, const uint8_t* mask, const float* spk,
+                                const float* t_span, int n_steps, int B, int T, float* mel_out, cudaStream_t st) = 0;
+  int64_t launches = 0;
+  bool use_graph = true;
+  bool debug = false;
+  std::map<std::string, DebugTensor> debug_tensors;
+};
+
+std::unique_ptr<EngineBase> make_engine(const SrnConfig& cfg);
+
+}  // namespace srn
+
+struct SrnHandle {
+  std::unique_ptr<srn::EngineBase> eng;
+  int device = 0;
+};

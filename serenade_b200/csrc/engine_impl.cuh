@@ -1,0 +1,168 @@
+// Engine<OT>: OT is the GEMM operand / activation storage type (bf16, or float for the TF32 mode).
+#pragma once
+#include <cuda_bf16.h>
+
+#include <cmath>
+#include <cstring>
+#include <list>
+
+#include "engine.h"
+#include "rowops.cuh"
+
+namespace srn {
+
+template <typename OT>
+struct ResnetW {
+  OT* w1 = nullptr;  int cin_pad = 0;       // [512][3 * cin_pad]   conv k3 taps, K-major
+  OT* w2 = nullptr;                         // [512][3 * 512]
+  OT* wr = nullptr;                         // [512][cin_pad]       1x1 res_conv
+  float *b1 = nullptr, *g1 = nullptr, *be1 = nullptr, *b2 = nullptr, *g2 = nullptr, *be2 = nullptr, *br = nullptr;
+  float *mlp_w = nullptr, *mlp_b = nullptr;                  // Linear 2048 -> 512 (time bias)
+  float *ws_w = nullptr, *ws_b = nullptr, *wb_w = nullptr, *wb_b = nullptr;   // SpeakerAdapter
+};
+
+template <typename OT>
+struct TfmW {
+  float *ln1g = nullptr, *ln1b = nullptr, *ln3g = nullptr, *ln3b = nullptr;
+  OT* wqkv = nullptr;      // [6144][512]  = [Wq; Wk; Wv]
+  OT* wo = nullptr;        // [512][2048]
+  float* bo = nullptr;
+  OT* wgl = nullptr;       // [4096][512]  GEGLU proj, value/gate rows interleaved
+  float* bgl = nullptr;    // interleaved the same way
+  OT* wf = nullptr;        // [512][2048]
+  float* bf = nullptr;
+};
+
+template <typename OT>
+struct ConvW {
+  OT* w = nullptr;         // k3: [512][1536]; transposed conv: even / odd parity [512][1024] each
+  OT* w_odd = nullptr;
+  float* b = nullptr;
+};
+
+enum OpKind : int { OP_GEMM, OP_PACKX, OP_GN_APPLY, OP_GN_RES_SPK_LN, OP_LAYERNORM, OP_SOFTMAX };
+
+struct Tap {
+  const char* name = nullptr;   // debug tensor name (null = none)
+  const void* ptr = nullptr;
+  int is_ot = 0;                // element type: OT or float
+  int rows = 0, cols = 0, ld = 0;
+  long long bstride = 0;
+  int nb = 0;
+  int cf = 0;                   // channels-first (B, cols, rows) source (only for v)
+};
+
+struct Op {
+  OpKind kind = OP_GEMM;
+  std::string name;
+  // GEMM
+  GemmParams gp;
+  int bn = 128;
+  dim3 grid;
+  bool is_euler = false;
+  // row kernels
+  const float* y = nullptr;
+  const float* part = nullptr;
+  const float* gamma = nullptr;
+  const float* beta = nullptr;
+  const float* res = nullptr;
+  const float* ln_g = nullptr;
+  const float* ln_b = nullptr;
+  float* hres = nullptr;
+  void* out = nullptr;
+  int resnet_idx = -1;          // which time-bias / speaker table row (-1: none)
+  int use_tbias = 0;
+  int level = 0;
+  Tap tap;
+};
+
+struct Level {
+  int T = 0;        // valid rows
+  int R = 0;        // allocated rows per batch entry
+  int Sp = 0;       // padded key length (row stride of scores / P / V^T)
+  int mtiles = 0;
+  int mask_step = 1;
+};
+
+template <typename OT>
+struct Plan {
+  int B = 0, T = 0, Tp = 0;
+  Level lv[2];
+  DevBuf xin, y, r, gnpart, a1, hres, ln, qk, vt, sc, P, ao, gg, hid0, hid1, hc, cv;
+  DevBuf x_state, mask, spk_in, mu_in, spk_scale, spk_bias, tsteps, dts, temb0, temb1, temb2, tb;
+  DevBuf blend_mask, blend_src;
+  int tb_steps = 0;
+  std::vector<Op> ops;
+  int euler_op = -1;
+  // graph cache
+  cudaGraphExec_t graph = nullptr;
+  int graph_steps = 0;
+  bool graph_blend = false;
+  int64_t graph_nodes = 0;
+  ~Plan() {
+    if (graph) cudaGraphExecDestroy(graph);
+  }
+};
+
+template <typename OT>
+class Engine : public EngineBase {
+ public:
+  explicit Engine(const SrnConfig& cfg);
+  ~Engine() override;
+  void load_weight(const std::string& key, const float* data, int ndim, const int64_t* dims) override;
+  void finalize_weights() override;
+  void estimator_forward(const float* x, const float* mu, const uint8_t* mask, const float* spk, float t, int B,
+                         int T, float* v_out, cudaStream_t st) override;
+  void solve_euler(float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
+                   int n_steps, int B, int T, const uint8_t* blend_mask, const float* blend_src,
+                   cudaStream_t st) override;
+  void solve_euler_host(const float* z, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
+                        int n_steps, int B, int T, float* mel_out, cudaStream_t st) override;
+
+ private:
+  static constexpr int BK = OpTraits<OT>::kBK;
+  SrnConfig cfg_;
+  int cmu_ = 0;
+  bool finalized_ = false;
+  std::map<std::string, HostTensor> host_w_;
+  std::list<DevBuf> arena_;
+  // packed weights
+  float *time_w1_ = nullptr, *time_b1_ = nullptr, *time_w2_ = nullptr, *time_b2_ = nullptr;
+  std::vector<ResnetW<OT>> resnets_;   // down0, down1, mid0.., up0, up1
+  std::vector<TfmW<OT>> tfms_;
+  ConvW<OT> down_conv_[2], up_conv_[2], final_conv_;
+  float *final_g_ = nullptr, *final_be_ = nullptr;
+  OT* proj_w_ = nullptr;
+  float* proj_b_ = nullptr;
+  std::list<Plan<OT>> plans_;
+  bool blend_active_ = false;
+  cudaStream_t capture_stream_ = nullptr;
+
+  // weights
+  const HostTensor& hw(const std::string& key, std::initializer_list<int64_t> dims);
+  float* up_f32(const std::vector<float>& v);
+  OT* up_ot(const std::vector<float>& v);
+  ResnetW<OT> pack_resnet(const std::string& p, int cin);
+  TfmW<OT> pack_tfm(const std::string& p);
+  OT* pack_conv3(const HostTensor& w, int cin, int cin_pad, float* /*unused*/ = nullptr);
+
+  // plan
+  Plan<OT>& get_plan(int B, int T);
+  void build_plan(Plan<OT>& pl);
+  void add_resnet(Plan<OT>& pl, int ridx, int level, const OT* src0, int c0, int ld0, const OT* src1, int c1,
+                  const std::string& tag, const TfmW<OT>& next_ln);
+  void add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const std::string& tag);
+  GemmParams base_gemm(const Plan<OT>& pl, int level) const;
+
+  // run
+  void launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool update_x, cudaStream_t st);
+  void launch_gemm(const GemmParams& gp, int bn, dim3 grid, cudaStream_t st);
+  void run_forward(Plan<OT>& pl, int step, float* v_out, bool update_x, cudaStream_t st);
+  void stage_inputs(Plan<OT>& pl, const float* x, const float* mu, const uint8_t* mask, const float* spk,
+                    cudaMemcpyKind kind, cudaStream_t st);
+  void prepass(Plan<OT>& pl, const std::vector<float>& ts, const std::vector<float>& dts, cudaStream_t st);
+  void solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bool blend, cudaStream_t st);
+  void capture_tap(const Plan<OT>& pl, const Tap& tap, cudaStream_t st);
+};
+
+}  // namespace srn

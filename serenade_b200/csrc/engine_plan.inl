@@ -1,0 +1,523 @@
+// Engine<OT>: per-(B,T) plan = workspace buffers + the op list with TMA maps.  Included by engine.cu.
+namespace srn {
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+static inline int round_up(int a, int b) { return cdiv(a, b) * b; }
+
+template <typename OT>
+Plan<OT>& Engine<OT>::get_plan(int B, int T) {
+  if (!finalized_) fail("weights not finalized: call srn_finalize_weights first");
+  for (auto& p : plans_)
+    if (p.B == B && p.T == T) return p;
+  if (plans_.size() >= 4) plans_.pop_front();   // bounded cache, oldest first
+  plans_.emplace_back();
+  Plan<OT>& pl = plans_.back();
+  pl.B = B;
+  pl.T = T;
+  try {
+    build_plan(pl);
+  } catch (...) {
+    plans_.pop_back();
+    throw;
+  }
+  return pl;
+}
+
+template <typename OT>
+GemmParams Engine<OT>::base_gemm(const Plan<OT>& pl, int level) const {
+  GemmParams gp;
+  memset(&gp, 0, sizeof gp);
+  gp.HB = 1;
+  gp.alpha = 1.0f;
+  gp.M = pl.lv[level].T;
+  gp.mask_step = 1;
+  return gp;
+}
+
+namespace {
+template <typename OT>
+void set_A(GemmParams& gp, int idx, const OT* ptr, int cols, int rows, long long alloc_rows, int ld, int nbatch) {
+  gp.mapA[idx] = make_tmap_3d(ptr, sizeof(OT), cols, rows, nbatch, ld, (uint64_t)alloc_rows * ld, OpTraits<OT>::kBK, 128);
+  if (idx == 0) gp.mapA[1] = gp.mapA[0];
+}
+template <typename OT>
+void set_B_weight(GemmParams& gp, const OT* W, int N, int K, int bn) {
+  gp.mapB = make_tmap_3d(W, sizeof(OT), K, N, 1, K, (uint64_t)N * K, OpTraits<OT>::kBK, bn);
+  gp.b_batch_mode = 0;
+}
+inline void add_seg(GemmParams& gp, int src, int col0, int shift, int nblk) {
+  if (gp.nseg >= 6) fail("too many K segments");
+  gp.seg[gp.nseg++] = KSeg{src, col0, shift, nblk};
+  gp.nkb += nblk;
+}
+inline int pick_bn(int N, long long row_tiles) {
+  return (N % 256 == 0 && (long long)(N / 256) * row_tiles >= 148) ? 256 : 128;
+}
+}  // namespace
+
+template <typename OT>
+void Engine<OT>::add_resnet(Plan<OT>& pl, int ridx, int level, const OT* src0, int c0, int ld0, const OT* src1,
+                            int c1, const std::string& tag, const TfmW<OT>& next) {
+  const Level& L = pl.lv[level];
+  const ResnetW<OT>& w = resnets_[ridx];
+  const int B = pl.B;
+  const long long hs = (long long)L.R * 512;
+  const long long tiles = (long long)L.mtiles * B;
+  auto conv_op = [&](const char* nm, const OT* a0, int ac0, int ald0, const OT* a1, int ac1, const OT* W, int taps,
+                     const float* bias, float* out, bool gn) {
+    Op op;
+    op.kind = OP_GEMM;
+    op.name = tag + "." + nm;
+    op.gp = base_gemm(pl, level);
+    GemmParams& gp = op.gp;
+    set_A<OT>(gp, 0, a0, ac0, L.T, L.R, ald0, B);
+    if (a1 != nullptr) set_A<OT>(gp, 1, a1, ac1, L.T, L.R, 512, B);
+    for (int k = 0; k < taps; ++k) {
+      const int shift = taps == 3 ? k - 1 : 0;
+      add_seg(gp, 0, 0, shift, ac0 / BK);
+      if (a1 != nullptr) add_seg(gp, 1, 0, shift, ac1 / BK);
+    }
+    op.bn = pick_bn(512, tiles);
+    set_B_weight<OT>(gp, W, 512, taps * (ac0 + ac1), op.bn);
+    gp.N = 512;
+    gp.epi = EPI_STORE_F32;
+    gp.bias = bias;
+    gp.out = out;
+    gp.out_bstride = hs;
+    gp.ldo = 512;
+    gp.gn_part = gn ? pl.gnpart.template as<float>() : nullptr;
+    op.grid = dim3(512 / op.bn, L.mtiles, B);
+    op.tap = Tap{nullptr, out, 0, L.T, 512, 512, hs, B, 0};
+    op.level = level;
+    pl.ops.push_back(op);
+    return &pl.ops.back();
+  };
+  conv_op("y1", src0, c0, ld0, src1, c1, w.w1, 3, w.b1, pl.y.template as<float>(), true)->tap.name = "y1";
+  conv_op("r", src0, c0, ld0, src1, c1, w.wr, 1, w.br, pl.r.template as<float>(), false)->tap.name = "r";
+  {
+    Op op;
+    op.kind = OP_GN_APPLY;
+    op.name = tag + ".a1";
+    op.y = pl.y.template as<float>();
+    op.part = pl.gnpart.template as<float>();
+    op.gamma = w.g1;
+    op.beta = w.be1;
+    op.out = pl.a1.p;
+    op.resnet_idx = ridx;
+    op.use_tbias = 1;
+    op.level = level;
+    op.tap = Tap{"a1", pl.a1.p, 1, L.T, 512, 512, hs, B, 0};
+    pl.ops.push_back(op);
+  }
+  conv_op("y2", pl.a1.template as<OT>(), 512, 512, nullptr, 0, w.w2, 3, w.b2, pl.y.template as<float>(), true)->tap.name = "y2";
+  {
+    Op op;
+    op.kind = OP_GN_RES_SPK_LN;
+    op.name = tag + ".resnet";
+    op.y = pl.y.template as<float>();
+    op.part = pl.gnpart.template as<float>();
+    op.gamma = w.g2;
+    op.beta = w.be2;
+    op.res = pl.r.template as<float>();
+    op.ln_g = next.ln1g;
+    op.ln_b = next.ln1b;
+    op.hres = pl.hres.template as<float>();
+    op.out = pl.ln.p;
+    op.resnet_idx = ridx;
+    op.level = level;
+    op.tap = Tap{"resnet", pl.hres.p, 0, L.T, 512, 512, hs, B, 0};
+    pl.ops.push_back(op);
+  }
+}
+
+template <typename OT>
+void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const std::string& tag) {
+  const Level& L = pl.lv[level];
+  const TfmW<OT>& w = tfms_[tidx];
+  const int B = pl.B, S = L.T, Sp = L.Sp, H = 4;
+  const long long tiles = (long long)L.mtiles * B;
+  OT* ln = pl.ln.template as<OT>();
+  OT* qk = pl.qk.template as<OT>();
+  OT* vt = pl.vt.template as<OT>();
+  OT* P = pl.P.template as<OT>();
+  OT* ao = pl.ao.template as<OT>();
+  OT* gg = pl.gg.template as<OT>();
+  float* sc = pl.sc.template as<float>();
+  float* hres = pl.hres.template as<float>();
+  auto push = [&](Op& op, const char* nm) {
+    op.kind = OP_GEMM;
+    op.name = tag + "." + nm;
+    op.level = level;
+    pl.ops.push_back(op);
+  };
+  {  // fused Q|K|V projection; V is written transposed (V^T [B][2048][Sp]) so that P.V sees a K-major operand
+    Op op;
+    op.gp = base_gemm(pl, level);
+    GemmParams& gp = op.gp;
+    set_A<OT>(gp, 0, ln, 512, S, L.R, 512, B);
+    add_seg(gp, 0, 0, 0, 512 / BK);
+    op.bn = pick_bn(6144, tiles);
+    set_B_weight<OT>(gp, w.wqkv, 6144, 512, op.bn);
+    gp.N = 6144;
+    gp.epi = EPI_QKV;
+    gp.out = qk;
+    gp.out_bstride = (long long)L.R * 4096;
+    gp.ldo = 4096;
+    gp.split_n = 4096;
+    gp.out2 = vt;
+    gp.out2_bstride = (long long)2048 * Sp;
+    gp.ld2 = Sp;
+    op.grid = dim3(6144 / op.bn, L.mtiles, B);
+    op.tap = Tap{"qk", qk, 1, S, 4096, 4096, gp.out_bstride, B, 0};
+    push(op, "qkv");
+  }
+  {  // scores[b,h] = Q K^T / sqrt(d)
+    Op op;
+    op.gp = base_gemm(pl, level);
+    GemmParams& gp = op.gp;
+    op.bn = 128;
+    gp.HB = H;
+    set_A<OT>(gp, 0, qk, 4096, S, L.R, 4096, B);
+    gp.a_hcol = 512;
+    add_seg(gp, 0, 0, 0, 512 / BK);
+    gp.mapB = make_tmap_3d(qk, sizeof(OT), 4096, S, B, 4096, (uint64_t)L.R * 4096, BK, op.bn);
+    gp.b_col0 = 2048;
+    gp.b_hcol = 512;
+    gp.b_batch_mode = 1;
+    gp.N = S;
+    gp.epi = EPI_STORE_F32;
+    gp.alpha = 1.0f / sqrtf(512.0f);
+    gp.out = sc;
+    gp.out_bstride = (long long)H * S * Sp;
+    gp.out_hstride = (long long)S * Sp;
+    gp.ldo = Sp;
+    op.grid = dim3(cdiv(S, op.bn), L.mtiles, B * H);
+    op.tap = Tap{"sc", sc, 0, S, S, Sp, (long long)S * Sp, B * H, 0};
+    push(op, "scores");
+  }
+  {
+    Op op;
+    op.kind = OP_SOFTMAX;
+    op.name = tag + ".softmax";
+    op.level = level;
+    op.tap = Tap{"P", P, 1, S, S, Sp, (long long)S * Sp, B * H, 0};
+    pl.ops.push_back(op);
+  }
+  {  // O[b, :, h*512:(h+1)*512] = P[b,h] V[b,h]
+    Op op;
+    op.gp = base_gemm(pl, level);
+    GemmParams& gp = op.gp;
+    gp.HB = H;
+    gp.mapA[0] = make_tmap_3d(P, sizeof(OT), S, S, (uint64_t)B * H, Sp, (uint64_t)S * Sp, BK, 128);
+    gp.mapA[1] = gp.mapA[0];
+    gp.a_zbatch = 1;
+    add_seg(gp, 0, 0, 0, cdiv(S, BK));
+    op.bn = pick_bn(512, tiles * H);
+    gp.mapB = make_tmap_3d(vt, sizeof(OT), S, 2048, B, Sp, (uint64_t)2048 * Sp, BK, op.bn);
+    gp.b_hrow = 512;
+    gp.b_batch_mode = 1;
+    gp.N = 512;
+    gp.epi = EPI_STORE_OT;
+    gp.out = ao;
+    gp.out_bstride = (long long)L.R * 2048;
+    gp.out_hstride = 512;
+    gp.ldo = 2048;
+    op.grid = dim3(512 / op.bn, L.mtiles, B * H);
+    op.tap = Tap{"ao", ao, 1, S, 2048, 2048, gp.out_bstride, B, 0};
+    push(op, "pv");
+  }
+  {  // h = attn_out W_o^T + b_o + h    (transformer.py:304)
+    Op op;
+    op.gp = base_gemm(pl, level);
+    GemmParams& gp = op.gp;
+    set_A<OT>(gp, 0, ao, 2048, S, L.R, 2048, B);
+    add_seg(gp, 0, 0, 0, 2048 / BK);
+    op.bn = pick_bn(512, tiles);
+    set_B_weight<OT>(gp, w.wo, 512, 2048, op.bn);
+    gp.N = 512;
+    gp.epi = EPI_RESID_F32;
+    gp.bias = w.bo;
+    gp.resid = hres;
+    gp.resid_bstride = (long long)L.R * 512;
+    gp.ldr = 512;
+    gp.out = hres;
+    gp.out_bstride = gp.resid_bstride;
+    gp.ldo = 512;
+    op.grid = dim3(512 / op.bn, L.mtiles, B);
+    op.tap = Tap{"h_attn", hres, 0, S, 512, 512, gp.out_bstride, B, 0};
+    push(op, "attn_out");
+  }
+  {
+    Op op;
+    op.kind = OP_LAYERNORM;
+    op.name = tag + ".ln3";
+    op.ln_g = w.ln3g;
+    op.ln_b = w.ln3b;
+    op.level = level;
+    op.tap = Tap{"ln3", ln, 1, S, 512, 512, (long long)L.R * 512, B, 0};
+    pl.ops.push_back(op);
+  }
+  {  // GEGLU: (ln W_v^T + b_v) * gelu(ln W_g^T + b_g), value/gate interleaved in the packed weight
+    Op op;
+    op.gp = base_gemm(pl, level);
+    GemmParams& gp = op.gp;
+    set_A<OT>(gp, 0, ln, 512, S, L.R, 512, B);
+    add_seg(gp, 0, 0, 0, 512 / BK);
+    op.bn = pick_bn(4096, tiles);
+    set_B_weight<OT>(gp, w.wgl, 4096, 512, op.bn);
+    gp.N = 4096;
+    gp.epi = EPI_GEGLU;
+    gp.bias = w.bgl;
+    gp.out = gg;
+    gp.out_bstride = (long long)L.R * 2048;
+    gp.ldo = 2048;
+    op.grid = dim3(4096 / op.bn, L.mtiles, B);
+    op.tap = Tap{"gg", gg, 1, S, 2048, 2048, gp.out_bstride, B, 0};
+    push(op, "geglu");
+  }
+  {  // h = gg W_2^T + b_2 + h, stored masked in operand precision for the convs that consume it
+    Op op;
+    op.gp = base_gemm(pl, level);
+    GemmParams& gp = op.gp;
+    set_A<OT>(gp, 0, gg, 2048, S, L.R, 2048, B);
+    add_seg(gp, 0, 0, 0, 2048 / BK);
+    op.bn = pick_bn(512, tiles);
+    set_B_weight<OT>(gp, w.wf, 512, 2048, op.bn);
+    gp.N = 512;
+    gp.epi = EPI_RESID_OT;
+    gp.bias = w.bf;
+    gp.resid = hres;
+    gp.resid_bstride = (long long)L.R * 512;
+    gp.ldr = 512;
+    gp.out = out_hc;
+    gp.out_bstride = (long long)L.R * 512;
+    gp.ldo = 512;
+    gp.rowmask = pl.mask.template as<uint8_t>();
+    gp.mask_bstride = pl.Tp;
+    gp.mask_step = L.mask_step;
+    op.grid = dim3(512 / op.bn, L.mtiles, B);
+    op.tap = Tap{"tfm", out_hc, 1, S, 512, 512, gp.out_bstride, B, 0};
+    push(op, "ff_out");
+  }
+}
+
+template <typename OT>
+void Engine<OT>::build_plan(Plan<OT>& pl) {
+  const int B = pl.B, T = pl.T, H = 4, C = 512;
+  const int T2 = (T + 1) / 2;
+  pl.Tp = 2 * T2;
+  pl.lv[0] = Level{T, pl.Tp, round_up(T, 8), cdiv(T, 128), 1};
+  pl.lv[1] = Level{T2, T2, round_up(T2, 8), cdiv(T2, 128), 2};
+  const size_t rows = (size_t)B * pl.Tp;
+  const size_t es = sizeof(OT);
+  pl.xin.alloc(rows * 256 * es);
+  pl.y.alloc(rows * C * 4);
+  pl.r.alloc(rows * C * 4);
+  pl.gnpart.alloc((size_t)B * pl.lv[0].mtiles * 16 * 4);
+  pl.a1.alloc(rows * C * es);
+  pl.hres.alloc(rows * C * 4);
+  pl.ln.alloc(rows * C * es);
+  pl.qk.alloc(rows * 4096 * es);
+  pl.vt.alloc((size_t)B * 2048 * pl.lv[0].Sp * es);
+  pl.sc.alloc((size_t)B * H * T * pl.lv[0].Sp * 4);
+  pl.P.alloc((size_t)B * H * T * pl.lv[0].Sp * es);
+  pl.ao.alloc(rows * 2048 * es);
+  pl.gg.alloc(rows * 2048 * es);
+  pl.hid0.alloc(rows * C * es);
+  pl.hid1.alloc((size_t)B * T2 * C * es);
+  pl.hc.alloc(rows * C * es);
+  pl.cv.alloc(rows * C * es);
+  pl.x_state.alloc((size_t)B * cfg_.out_channels * T * 4);
+  pl.mask.alloc(rows);
+  pl.spk_in.alloc((size_t)B * cfg_.spk_embed_dim * 4);
+  pl.mu_in.alloc((size_t)B * cmu_ * T * 4);
+  const int nres = (int)resnets_.size();
+  pl.spk_scale.alloc((size_t)nres * B * C * 4);
+  pl.spk_bias.alloc((size_t)nres * B * C * 4);
+  pl.blend_mask.alloc((size_t)B * T);
+  pl.blend_src.alloc((size_t)B * cfg_.out_channels * T * 4);
+
+  OT* xin = pl.xin.template as<OT>();
+  OT* hid0 = pl.hid0.template as<OT>();
+  OT* hid1 = pl.hid1.template as<OT>();
+  OT* hc = pl.hc.template as<OT>();
+  OT* cv = pl.cv.template as<OT>();
+  const uint8_t* mask = pl.mask.template as<uint8_t>();
+  const long long tiles0 = (long long)pl.lv[0].mtiles * B, tiles1 = (long long)pl.lv[1].mtiles * B;
+
+  {  // x (B,80,T) -> xin[:, :, 0:80] (masked)
+    Op op;
+    op.kind = OP_PACKX;
+    op.name = "pack_x";
+    op.tap = Tap{"xin", xin, 1, T, 256, 256, (long long)pl.Tp * 256, B, 0};
+    pl.ops.push_back(op);
+  }
+  auto plain_conv3 = [&](const char* nm, int level, const OT* src, const ConvW<OT>& w, OT* dst, int out_level) {
+    const Level& L = pl.lv[level];
+    Op op;
+    op.kind = OP_GEMM;
+    op.name = nm;
+    op.level = level;
+    op.gp = base_gemm(pl, level);
+    GemmParams& gp = op.gp;
+    set_A<OT>(gp, 0, src, 512, L.T, L.R, 512, B);
+    for (int k = 0; k < 3; ++k) add_seg(gp, 0, 0, k - 1, 512 / BK);
+    op.bn = pick_bn(512, (long long)L.mtiles * B);
+    set_B_weight<OT>(gp, w.w, 512, 1536, op.bn);
+    gp.N = 512;
+    gp.epi = EPI_STORE_OT;
+    gp.bias = w.b;
+    gp.out = dst;
+    gp.out_bstride = (long long)L.R * 512;
+    gp.ldo = 512;
+    gp.rowmask = mask;
+    gp.mask_bstride = pl.Tp;
+    gp.mask_step = pl.lv[out_level].mask_step;
+    op.grid = dim3(512 / op.bn, L.mtiles, B);
+    op.tap = Tap{"out", dst, 1, L.T, 512, 512, gp.out_bstride, B, 0};
+    pl.ops.push_back(op);
+  };
+
+  int ri = 0;
+  // ---- down 0 (full rate): resnet(242 -> 512) + transformer, skip saved in hid0, Downsample1D
+  add_resnet(pl, ri, 0, xin, 256, 256, nullptr, 0, "down0", tfms_[ri]);
+  add_tfm(pl, ri, 0, hid0, "down0");
+  ++ri;
+  {  // Conv1d k3 s2 p1 on the pair view [B][T2][1024] of hid0: out[m] = W0 x[2m-1] + W1 x[2m] + W2 x[2m+1]
+    const Level& L = pl.lv[1];
+    Op op;
+    op.kind = OP_GEMM;
+    op.name = "down0.out";
+    op.level = 1;
+    op.gp = base_gemm(pl, 1);
+    GemmParams& gp = op.gp;
+    set_A<OT>(gp, 0, hid0, 1024, T2, T2, 1024, B);
+    add_seg(gp, 0, 512, -1, 512 / BK);
+    add_seg(gp, 0, 0, 0, 512 / BK);
+    add_seg(gp, 0, 512, 0, 512 / BK);
+    op.bn = pick_bn(512, tiles1);
+    set_B_weight<OT>(gp, down_conv_[0].w, 512, 1536, op.bn);
+    gp.N = 512;
+    gp.epi = EPI_STORE_OT;
+    gp.bias = down_conv_[0].b;
+    gp.out = cv;
+    gp.out_bstride = (long long)T2 * 512;
+    gp.ldo = 512;
+    gp.rowmask = mask;
+    gp.mask_bstride = pl.Tp;
+    gp.mask_step = 2;
+    op.grid = dim3(512 / op.bn, L.mtiles, B);
+    op.tap = Tap{"out", cv, 1, T2, 512, 512, gp.out_bstride, B, 0};
+    pl.ops.push_back(op);
+  }
+  // ---- down 1 (half rate)
+  add_resnet(pl, ri, 1, cv, 512, 512, nullptr, 0, "down1", tfms_[ri]);
+  add_tfm(pl, ri, 1, hid1, "down1");
+  ++ri;
+  plain_conv3("down1.out", 1, hid1, down_conv_[1], cv, 1);
+  // ---- mid blocks (half rate)
+  const OT* cur = cv;
+  for (int i = 0; i < cfg_.num_mid_blocks; ++i) {
+    const std::string tag = "mid" + std::to_string(i);
+    add_resnet(pl, ri, 1, cur, 512, 512, nullptr, 0, tag, tfms_[ri]);
+    add_tfm(pl, ri, 1, hc, tag);
+    cur = hc;
+    ++ri;
+  }
+  // ---- up 0 (half rate): cat([h, hid1]) -> resnet(1024 -> 512) + transformer, ConvTranspose1d(4, 2, 1)
+  add_resnet(pl, ri, 1, cur, 512, 512, hid1, 512, "up0", tfms_[ri]);
+  add_tfm(pl, ri, 1, hc, "up0");
+  ++ri;
+  for (int par = 0; par < 2; ++par) {
+    const Level& L = pl.lv[1];
+    Op op;
+    op.kind = OP_GEMM;
+    op.name = par == 0 ? "up0.out_even" : "up0.out";
+    op.level = 1;
+    op.gp = base_gemm(pl, 1);
+    GemmParams& gp = op.gp;
+    set_A<OT>(gp, 0, hc, 512, T2, T2, 512, B);
+    add_seg(gp, 0, 0, par == 0 ? -1 : 0, 512 / BK);
+    add_seg(gp, 0, 0, par == 0 ? 0 : 1, 512 / BK);
+    op.bn = pick_bn(512, tiles1);
+    set_B_weight<OT>(gp, par == 0 ? up_conv_[0].w : up_conv_[0].w_odd, 512, 1024, op.bn);
+    gp.N = 512;
+    gp.epi = EPI_STORE_OT;
+    gp.bias = up_conv_[0].b;
+    gp.out = cv + par * 512;              // frame 2m + par of the full-rate tensor viewed as [B][T2][1024]
+    gp.out_bstride = (long long)T2 * 1024;
+    gp.ldo = 1024;
+    gp.rowmask = mask;
+    gp.mask_bstride = pl.Tp;
+    gp.mask_step = 2;
+    gp.mask_off = par;
+    op.grid = dim3(512 / op.bn, L.mtiles, B);
+    if (par == 1) op.tap = Tap{"out", cv, 1, T, 512, 512, (long long)pl.Tp * 512, B, 0};
+    pl.ops.push_back(op);
+  }
+  // ---- up 1 (full rate): cat([h[:, :, :T], hid0]) -> resnet + transformer, Conv1d k3
+  add_resnet(pl, ri, 0, cv, 512, 512, hid0, 512, "up1", tfms_[ri]);
+  add_tfm(pl, ri, 0, hc, "up1");
+  ++ri;
+  plain_conv3("up1.out", 0, hc, up_conv_[1], cv, 0);
+  // ---- final Block1D + 1x1 projection fused with the Euler update
+  {
+    const Level& L = pl.lv[0];
+    Op op;
+    op.kind = OP_GEMM;
+    op.name = "final.y";
+    op.gp = base_gemm(pl, 0);
+    GemmParams& gp = op.gp;
+    set_A<OT>(gp, 0, cv, 512, T, pl.Tp, 512, B);
+    for (int k = 0; k < 3; ++k) add_seg(gp, 0, 0, k - 1, 512 / BK);
+    op.bn = pick_bn(512, tiles0);
+    set_B_weight<OT>(gp, final_conv_.w, 512, 1536, op.bn);
+    gp.N = 512;
+    gp.epi = EPI_STORE_F32;
+    gp.bias = final_conv_.b;
+    gp.out = pl.y.p;
+    gp.out_bstride = (long long)pl.Tp * 512;
+    gp.ldo = 512;
+    gp.gn_part = pl.gnpart.template as<float>();
+    op.grid = dim3(512 / op.bn, L.mtiles, B);
+    pl.ops.push_back(op);
+  }
+  {
+    Op op;
+    op.kind = OP_GN_APPLY;
+    op.name = "final_block";
+    op.y = pl.y.template as<float>();
+    op.part = pl.gnpart.template as<float>();
+    op.gamma = final_g_;
+    op.beta = final_be_;
+    op.out = pl.a1.p;
+    op.level = 0;
+    op.tap = Tap{"final_block", pl.a1.p, 1, T, 512, 512, (long long)pl.Tp * 512, B, 0};
+    pl.ops.push_back(op);
+  }
+  {
+    Op op;
+    op.kind = OP_GEMM;
+    op.name = "final_proj_euler";
+    op.is_euler = true;
+    op.gp = base_gemm(pl, 0);
+    GemmParams& gp = op.gp;
+    set_A<OT>(gp, 0, pl.a1.template as<OT>(), 512, T, pl.Tp, 512, B);
+    add_seg(gp, 0, 0, 0, 512 / BK);
+    op.bn = 128;
+    set_B_weight<OT>(gp, proj_w_, cfg_.out_channels, 512, op.bn);
+    gp.N = cfg_.out_channels;
+    gp.epi = EPI_EULER;
+    gp.bias = proj_b_;
+    gp.rowmask = mask;
+    gp.mask_bstride = pl.Tp;
+    gp.mask_step = 1;
+    gp.x_in = pl.x_state.template as<float>();
+    gp.T_cf = T;
+    op.grid = dim3(1, pl.lv[0].mtiles, B);
+    pl.euler_op = (int)pl.ops.size();
+    pl.ops.push_back(op);
+  }
+}
+
+}  // namespace srn

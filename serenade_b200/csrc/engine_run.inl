@@ -1,0 +1,292 @@
+// Engine<OT>: kernel launches, the estimator forward and the Euler solve loop.  Included by engine.cu.
+namespace srn {
+
+static inline float to_f_host(float v) { return v; }
+static inline float to_f_host(__nv_bfloat16 v) { return __bfloat162float(v); }
+
+template <typename OT, int BN, int STAGES>
+static void launch_gemm_impl(const GemmParams& gp, dim3 grid, cudaStream_t st) {
+  constexpr int smem = gemm_smem_bytes<BN, STAGES>();
+  gemm_kernel<OT, BN, STAGES><<<grid, 192, smem, st>>>(gp);
+  SRN_CUDA(cudaGetLastError());
+}
+
+template <typename OT>
+void Engine<OT>::launch_gemm(const GemmParams& gp, int bn, dim3 grid, cudaStream_t st) {
+  if (gp.nkb < 1 || gp.nseg < 1) fail("gemm with empty K");
+  if (bn == 256) launch_gemm_impl<OT, 256, 4>(gp, grid, st);
+  else launch_gemm_impl<OT, 128, 3>(gp, grid, st);
+  ++launches;
+}
+
+template <typename OT>
+void Engine<OT>::capture_tap(const Plan<OT>& pl, const Tap& tap, cudaStream_t st) {
+  (void)pl;
+  SRN_CUDA(cudaStreamSynchronize(st));
+  DebugTensor d;
+  d.B = tap.nb;
+  d.rows = tap.rows;
+  d.cols = tap.cols;
+  d.data.resize((size_t)tap.nb * tap.rows * tap.cols);
+  const size_t es = tap.is_ot ? sizeof(OT) : sizeof(float);
+  std::vector<uint8_t> raw((size_t)tap.rows * tap.ld * es);
+  for (int b = 0; b < tap.nb; ++b) {
+    SRN_CUDA(cudaMemcpy(raw.data(), static_cast<const uint8_t*>(tap.ptr) + (size_t)b * tap.bstride * es, raw.size(),
+                        cudaMemcpyDeviceToHost));
+    for (int r = 0; r < tap.rows; ++r)
+      for (int c = 0; c < tap.cols; ++c) {
+        const size_t si = (size_t)r * tap.ld + c;
+        float v;
+        if (tap.is_ot) v = to_f_host(reinterpret_cast<const OT*>(raw.data())[si]);
+        else v = reinterpret_cast<const float*>(raw.data())[si];
+        d.data[((size_t)b * tap.rows + r) * tap.cols + c] = v;
+      }
+  }
+  debug_tensors[tap.name] = std::move(d);
+}
+
+template <typename OT>
+void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool update_x, cudaStream_t st) {
+  const Level& L = pl.lv[op.level];
+  const uint8_t* mask = pl.mask.template as<uint8_t>();
+  const int B = pl.B;
+  switch (op.kind) {
+    case OP_GEMM: {
+      if (op.is_euler) {
+        GemmParams gp = op.gp;
+        gp.v_out = v_out;
+        gp.x_out = update_x ? pl.x_state.template as<float>() : nullptr;
+        gp.dt_ptr = pl.dts.template as<float>() + step;
+        if (update_x && blend_active_) {
+          gp.blend_mask = pl.blend_mask.template as<uint8_t>();
+          gp.blend_src = pl.blend_src.template as<float>();
+        }
+        launch_gemm(gp, op.bn, op.grid, st);
+      } else {
+        launch_gemm(op.gp, op.bn, op.grid, st);
+      }
+    } break;
+    case OP_PACKX: {
+      dim3 grid(cdiv(pl.T, 32), cdiv(cfg_.out_channels, 32), B);
+      pack_cf_to_cl<OT><<<grid, dim3(32, 8), 0, st>>>(pl.x_state.template as<float>(), cfg_.out_channels, pl.T, mask, pl.Tp,
+                                                      pl.xin.template as<OT>(), (long long)pl.Tp * 256, 256, 0);
+      SRN_CUDA(cudaGetLastError());
+      ++launches;
+    } break;
+    case OP_GN_APPLY: {
+      const float* tb = op.use_tbias ? pl.tb.template as<float>() + ((size_t)op.resnet_idx * pl.tb_steps + step) * 512
+                                     : nullptr;
+      dim3 grid(cdiv(L.T, 32), B);
+      gn_apply_kernel<OT><<<grid, 256, 0, st>>>(op.y, op.part, L.mtiles, L.T, (long long)L.R * 512, op.gamma, op.beta,
+                                                tb, mask, pl.Tp, L.mask_step, static_cast<OT*>(op.out), 32);
+      SRN_CUDA(cudaGetLastError());
+      ++launches;
+    } break;
+    case OP_GN_RES_SPK_LN: {
+      dim3 grid(cdiv(L.T, 32), B);
+      const float* sc = pl.spk_scale.template as<float>() + (size_t)op.resnet_idx * B * 512;
+      const float* sb = pl.spk_bias.template as<float>() + (size_t)op.resnet_idx * B * 512;
+      gn_res_spk_ln<OT><<<grid, 256, 0, st>>>(op.y, op.part, L.mtiles, L.T, (long long)L.R * 512, op.gamma, op.beta,
+                                              op.res, mask, pl.Tp, L.mask_step, sc, sb, op.ln_g, op.ln_b, op.hres,
+                                              static_cast<OT*>(op.out), 32);
+      SRN_CUDA(cudaGetLastError());
+      ++launches;
+    } break;
+    case OP_LAYERNORM: {
+      const long long nrows = (long long)B * L.R;
+      layernorm_kernel<OT><<<(unsigned)((nrows + 7) / 8), 256, 0, st>>>(pl.hres.template as<float>(), nrows, op.ln_g,
+                                                                        op.ln_b, pl.ln.template as<OT>());
+      SRN_CUDA(cudaGetLastError());
+      ++launches;
+    } break;
+    case OP_SOFTMAX: {
+      dim3 grid(L.T, B * 4);
+      softmax_kernel<OT><<<grid, 128, 0, st>>>(pl.sc.template as<float>(), L.T, L.Sp, 4, mask, pl.Tp, L.mask_step,
+                                               pl.P.template as<OT>());
+      SRN_CUDA(cudaGetLastError());
+      ++launches;
+    } break;
+  }
+  if (debug && op.tap.name != nullptr) {
+    // debug key = "<tag>.<tap name>" (e.g. "down0.y1"), or the bare tap name for untagged ops
+    const size_t dot = op.name.rfind('.');
+    const std::string key = (dot == std::string::npos ? std::string() : op.name.substr(0, dot + 1)) + op.tap.name;
+    Tap t = op.tap;
+    t.name = key.c_str();
+    capture_tap(pl, t, st);
+  }
+}
+
+template <typename OT>
+void Engine<OT>::run_forward(Plan<OT>& pl, int step, float* v_out, bool update_x, cudaStream_t st) {
+  for (Op& op : pl.ops) launch_op(pl, op, step, v_out, update_x, st);
+}
+
+template <typename OT>
+void Engine<OT>::stage_inputs(Plan<OT>& pl, const float* x, const float* mu, const uint8_t* mask, const float* spk,
+                              cudaMemcpyKind kind, cudaStream_t st) {
+  const int B = pl.B, T = pl.T;
+  SRN_CUDA(cudaMemcpyAsync(pl.x_state.p, x, (size_t)B * cfg_.out_channels * T * 4, kind, st));
+  SRN_CUDA(cudaMemcpyAsync(pl.mu_in.p, mu, (size_t)B * cmu_ * T * 4, kind, st));
+  SRN_CUDA(cudaMemcpy2DAsync(pl.mask.p, pl.Tp, mask, T, T, B, kind, st));
+  SRN_CUDA(cudaMemcpyAsync(pl.spk_in.p, spk, (size_t)B * cfg_.spk_embed_dim * 4, kind, st));
+}
+
+// Step-invariant work hoisted out of the Euler loop (SURVEY.md finding 10): mu columns of the packed
+// conv input, SpeakerAdapter scale / bias per resnet, and the time-embedding MLP + per-resnet time bias
+// for every step (the time path depends only on t, which the whole batch shares: decoder.py:401-402, :97).
+template <typename OT>
+void Engine<OT>::prepass(Plan<OT>& pl, const std::vector<float>& ts, const std::vector<float>& dts, cudaStream_t st) {
+  (void)dts;
+  const int B = pl.B, n = (int)ts.size();
+  const int nres = (int)resnets_.size();
+  const uint8_t* mask = pl.mask.template as<uint8_t>();
+  {
+    dim3 grid(cdiv(pl.T, 32), cdiv(cmu_, 32), B);
+    pack_cf_to_cl<OT><<<grid, dim3(32, 8), 0, st>>>(pl.mu_in.template as<float>(), cmu_, pl.T, mask, pl.Tp,
+                                                    pl.xin.template as<OT>(), (long long)pl.Tp * 256, 256,
+                                                    cfg_.out_channels);
+    SRN_CUDA(cudaGetLastError());
+    ++launches;
+  }
+  const int sd = cfg_.spk_embed_dim;
+  for (int r = 0; r < nres; ++r) {
+    gemv_kernel<<<dim3(512 / 8, B), 256, 0, st>>>(resnets_[r].ws_w, resnets_[r].ws_b, pl.spk_in.template as<float>(),
+                                                   pl.spk_scale.template as<float>() + (size_t)r * B * 512, sd, 512,
+                                                   ACT_NONE, ACT_NONE);
+    gemv_kernel<<<dim3(512 / 8, B), 256, 0, st>>>(resnets_[r].wb_w, resnets_[r].wb_b, pl.spk_in.template as<float>(),
+                                                   pl.spk_bias.template as<float>() + (size_t)r * B * 512, sd, 512,
+                                                   ACT_NONE, ACT_NONE);
+    launches += 2;
+  }
+  SRN_CUDA(cudaGetLastError());
+  const int dim = cfg_.in_channels;
+  const float e = (float)(std::log(10000.0) / (double)(dim / 2 - 1));
+  sinusoid_kernel<<<n, 128, 0, st>>>(pl.tsteps.template as<float>(), dim, e, pl.temb0.template as<float>());
+  gemv_kernel<<<dim3(2048 / 8, n), 256, 0, st>>>(time_w1_, time_b1_, pl.temb0.template as<float>(),
+                                                 pl.temb1.template as<float>(), dim, 2048, ACT_NONE, ACT_SILU);
+  gemv_kernel<<<dim3(2048 / 8, n), 256, 0, st>>>(time_w2_, time_b2_, pl.temb1.template as<float>(),
+                                                 pl.temb2.template as<float>(), 2048, 2048, ACT_NONE, ACT_NONE);
+  launches += 3;
+  for (int r = 0; r < nres; ++r) {
+    gemv_kernel<<<dim3(512 / 8, n), 256, 0, st>>>(resnets_[r].mlp_w, resnets_[r].mlp_b, pl.temb2.template as<float>(),
+                                                  pl.tb.template as<float>() + (size_t)r * pl.tb_steps * 512, 2048, 512,
+                                                  ACT_MISH, ACT_NONE);
+    ++launches;
+  }
+  SRN_CUDA(cudaGetLastError());
+}
+
+template <typename OT>
+static void ensure_step_buffers(Plan<OT>& pl, int n, int in_channels, int nres) {
+  if (n <= pl.tb_steps) return;
+  const int cap = std::max(n, 16);
+  pl.tsteps.alloc((size_t)cap * 4);
+  pl.dts.alloc((size_t)cap * 4);
+  pl.temb0.alloc((size_t)cap * in_channels * 4);
+  pl.temb1.alloc((size_t)cap * 2048 * 4);
+  pl.temb2.alloc((size_t)cap * 2048 * 4);
+  pl.tb.alloc((size_t)nres * cap * 512 * 4);
+  pl.tb_steps = cap;
+  if (pl.graph) {
+    cudaGraphExecDestroy(pl.graph);
+    pl.graph = nullptr;
+  }
+}
+
+template <typename OT>
+void Engine<OT>::estimator_forward(const float* x, const float* mu, const uint8_t* mask, const float* spk, float t,
+                                   int B, int T, float* v_out, cudaStream_t st) {
+  Plan<OT>& pl = get_plan(B, T);
+  ensure_step_buffers(pl, 1, cfg_.in_channels, (int)resnets_.size());
+  stage_inputs(pl, x, mu, mask, spk, cudaMemcpyDeviceToDevice, st);
+  const float zero = 0.f;
+  SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, &t, 4, cudaMemcpyHostToDevice, st));
+  SRN_CUDA(cudaMemcpyAsync(pl.dts.p, &zero, 4, cudaMemcpyHostToDevice, st));
+  SRN_CUDA(cudaStreamSynchronize(st));   // &t / &zero are stack temporaries
+  blend_active_ = false;
+  prepass(pl, std::vector<float>{t}, std::vector<float>{0.f}, st);
+  run_forward(pl, 0, v_out, false, st);
+}
+
+template <typename OT>
+void Engine<OT>::solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bool blend, cudaStream_t st) {
+  // flow_matching.py:79-91 in fp32: t += dt; dt = t_span[k+1] - t  (keeps the reference's last-ulp wobble)
+  std::vector<float> ts(n_steps), dts(n_steps);
+  {
+    float t = t_span[0];
+    float dt = t_span[1] - t_span[0];
+    for (int s = 1; s <= n_steps; ++s) {
+      ts[s - 1] = t;
+      dts[s - 1] = dt;
+      t = t + dt;
+      if (s < n_steps) dt = t_span[s + 1] - t;
+    }
+  }
+  ensure_step_buffers(pl, n_steps, cfg_.in_channels, (int)resnets_.size());
+  SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, ts.data(), (size_t)n_steps * 4, cudaMemcpyHostToDevice, st));
+  SRN_CUDA(cudaMemcpyAsync(pl.dts.p, dts.data(), (size_t)n_steps * 4, cudaMemcpyHostToDevice, st));
+  SRN_CUDA(cudaStreamSynchronize(st));   // ts / dts are host temporaries
+  blend_active_ = blend;
+  if (use_graph && !debug) {
+    if (pl.graph == nullptr || pl.graph_steps != n_steps || pl.graph_blend != blend) {
+      if (pl.graph) {
+        cudaGraphExecDestroy(pl.graph);
+        pl.graph = nullptr;
+      }
+      if (capture_stream_ == nullptr) SRN_CUDA(cudaStreamCreateWithFlags(&capture_stream_, cudaStreamNonBlocking));
+      const int64_t before = launches;
+      cudaGraph_t g = nullptr;
+      SRN_CUDA(cudaStreamBeginCapture(capture_stream_, cudaStreamCaptureModeThreadLocal));
+      try {
+        prepass(pl, ts, dts, capture_stream_);
+        for (int s = 0; s < n_steps; ++s) run_forward(pl, s, nullptr, true, capture_stream_);
+      } catch (...) {
+        cudaStreamEndCapture(capture_stream_, &g);
+        if (g) cudaGraphDestroy(g);
+        launches = before;
+        throw;
+      }
+      SRN_CUDA(cudaStreamEndCapture(capture_stream_, &g));
+      pl.graph_nodes = launches - before;
+      launches = before;
+      cudaError_t e = cudaGraphInstantiate(&pl.graph, g, 0);
+      cudaGraphDestroy(g);
+      if (e != cudaSuccess) fail("cudaGraphInstantiate failed: %s", cudaGetErrorString(e));
+      pl.graph_steps = n_steps;
+      pl.graph_blend = blend;
+    }
+    SRN_CUDA(cudaGraphLaunch(pl.graph, st));
+    launches += pl.graph_nodes;
+  } else {
+    prepass(pl, ts, dts, st);
+    for (int s = 0; s < n_steps; ++s) run_forward(pl, s, nullptr, true, st);
+  }
+}
+
+template <typename OT>
+void Engine<OT>::solve_euler(float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
+                             int n_steps, int B, int T, const uint8_t* blend_mask, const float* blend_src,
+                             cudaStream_t st) {
+  Plan<OT>& pl = get_plan(B, T);
+  stage_inputs(pl, x, mu, mask, spk, cudaMemcpyDeviceToDevice, st);
+  const bool blend = blend_mask != nullptr;
+  if (blend) {
+    SRN_CUDA(cudaMemcpyAsync(pl.blend_mask.p, blend_mask, (size_t)B * T, cudaMemcpyDeviceToDevice, st));
+    SRN_CUDA(cudaMemcpyAsync(pl.blend_src.p, blend_src, (size_t)B * cfg_.out_channels * T * 4, cudaMemcpyDeviceToDevice, st));
+  }
+  solve_staged(pl, t_span, n_steps, blend, st);
+  SRN_CUDA(cudaMemcpyAsync(x, pl.x_state.p, (size_t)B * cfg_.out_channels * T * 4, cudaMemcpyDeviceToDevice, st));
+}
+
+template <typename OT>
+void Engine<OT>::solve_euler_host(const float* z, const float* mu, const uint8_t* mask, const float* spk,
+                                  const float* t_span, int n_steps, int B, int T, float* mel_out, cudaStream_t st) {
+  Plan<OT>& pl = get_plan(B, T);
+  stage_inputs(pl, z, mu, mask, spk, cudaMemcpyHostToDevice, st);
+  solve_staged(pl, t_span, n_steps, false, st);
+  SRN_CUDA(cudaMemcpyAsync(mel_out, pl.x_state.p, (size_t)B * cfg_.out_channels * T * 4, cudaMemcpyDeviceToHost, st));
+  SRN_CUDA(cudaStreamSynchronize(st));
+}
+
+}  // namespace srn

@@ -1,0 +1,338 @@
+// Memory-bound row kernels of the estimator (channels-last [B][T][C] activations):
+//   pack_cf_to_cl      (B,C,T) f32 channels-first -> masked channels-last operand columns
+//   gn_apply_kernel    GroupNorm(8)+Mish(+time bias)+mask            (decoder.py:66-77, :97)
+//   gn_res_spk_ln      GroupNorm+Mish+mask + residual + SpeakerAdapter LN*scale+bias, then the
+//                      transformer's LayerNorm1 on the same row       (decoder.py:14-45, :99-100; transformer.py:286)
+//   layernorm_kernel   LayerNorm(512) affine                          (transformer.py:322)
+//   softmax_kernel     key-masked softmax rows                        (diffusers Attention / SDPA bool mask)
+//   gemv_kernel        small fp32 linears hoisted out of the step loop (time MLP, time bias, speaker scale/bias)
+// All single pass over HBM, 16-byte vector accesses, warp-shuffle reductions, fp32 math.
+#pragma once
+#include <cuda_bf16.h>
+#include <cstdint>
+
+namespace srn {
+
+constexpr int kC = 512;         // hidden width of the ssc1 decoder
+constexpr int kGroups = 8;      // GroupNorm groups (decoder.py:67)
+
+__device__ __forceinline__ float mish_f(float x) {
+  // x * tanh(softplus(x)), softplus threshold 20 as in torch
+  const float sp = x > 20.f ? x : log1pf(expf(x));
+  return x * tanhf(sp);
+}
+__device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
+
+__device__ __forceinline__ void load8(const float* p, float (&v)[8]) {
+  const float4 a = reinterpret_cast<const float4*>(p)[0];
+  const float4 b = reinterpret_cast<const float4*>(p)[1];
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void store8(float* p, const float (&v)[8]) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
+  uint4 u;
+  __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]);
+  __nv_bfloat162 b = __floats2bfloat162_rn(v[2], v[3]);
+  __nv_bfloat162 c = __floats2bfloat162_rn(v[4], v[5]);
+  __nv_bfloat162 d = __floats2bfloat162_rn(v[6], v[7]);
+  u.x = *reinterpret_cast<uint32_t*>(&a); u.y = *reinterpret_cast<uint32_t*>(&b);
+  u.z = *reinterpret_cast<uint32_t*>(&c); u.w = *reinterpret_cast<uint32_t*>(&d);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+__device__ __forceinline__ float to_f(float v) { return v; }
+__device__ __forceinline__ float to_f(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ void from_f(float* p, float v) { *p = v; }
+__device__ __forceinline__ void from_f(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// (B, C, T) f32 channels-first  ->  dst[b][t][col0 + c] = src[b][c][t] * mask[b][t]    (OT, channels-last)
+template <typename OT>
+__global__ void pack_cf_to_cl(const float* __restrict__ src, int C, int T, const uint8_t* __restrict__ mask,
+                              int mask_bstride, OT* __restrict__ dst, long long dst_bstride, int ldd, int col0) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const int t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, t = t0 + threadIdx.x;
+    tile[i][threadIdx.x] = (c < C && t < T) ? src[((long long)b * C + c) * T + t] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int t = t0 + i, c = c0 + threadIdx.x;
+    if (t < T && c < C) {
+      const float m = mask[(long long)b * mask_bstride + t] ? 1.f : 0.f;
+      from_f(dst + b * dst_bstride + (long long)t * ldd + col0 + c, tile[threadIdx.x][i] * m);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Reduce the conv epilogue's per-tile partial sums to (mean, rstd) for the 8 groups of batch b.
+// part: [B][mtiles][8][2].  Result in smem stats[16] = {mean_g, rstd_g}.  Call with >= 256 threads.
+__device__ __forceinline__ void gn_reduce_stats(const float* __restrict__ part, int b, int mtiles, int T,
+                                                float* stats /*smem [16]*/, double* red /*smem [256]*/) {
+  const int t = threadIdx.x;
+  if (t < 256) {
+    const int vi = t & 15, tl = t >> 4;
+    double acc = 0.0;
+    for (int m = tl; m < mtiles; m += 16) acc += (double)part[((long long)b * mtiles + m) * 16 + vi];
+    red[t] = acc;
+  }
+  __syncthreads();
+  if (t < 16) {
+    double acc = 0.0;
+    for (int i = 0; i < 16; ++i) acc += red[i * 16 + t];
+    red[t] = acc;
+  }
+  __syncthreads();
+  if (t < 8) {
+    const double n = 64.0 * (double)T;
+    const double mean = red[2 * t] / n;
+    double var = red[2 * t + 1] / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    stats[2 * t] = (float)mean;
+    stats[2 * t + 1] = (float)(1.0 / sqrt(var + 1e-5));
+  }
+  __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------------
+// out = (Mish(GN(y)) + tbias) * mask      (tbias may be null).  256 threads = 4 rows x 64 threads x 8 ch.
+template <typename OT>
+__global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__ y, const float* __restrict__ part,
+                                                       int mtiles, int T, long long bstride,
+                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                       const float* __restrict__ tbias, const uint8_t* __restrict__ mask,
+                                                       int mask_bstride, int mask_step, OT* __restrict__ out,
+                                                       int rows_per_block) {
+  __shared__ float stats[16];
+  __shared__ double red[256];
+  const int b = blockIdx.y;
+  gn_reduce_stats(part, b, mtiles, T, stats, red);
+  const int c = (threadIdx.x & 63) * 8;
+  const int g = c >> 6;
+  const float mean = stats[2 * g], rstd = stats[2 * g + 1];
+  float ga[8], be[8], tb[8];
+  load8(gamma + c, ga);
+  load8(beta + c, be);
+  if (tbias != nullptr) load8(tbias + c, tb);
+  else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) tb[i] = 0.f;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { ga[i] *= rstd; be[i] -= mean * ga[i]; }
+  const int r0 = blockIdx.x * rows_per_block;
+  const int r1 = min(r0 + rows_per_block, T);
+  for (int r = r0 + (threadIdx.x >> 6); r < r1; r += 4) {
+    const long long off = b * bstride + (long long)r * kC + c;
+    const float m = mask[(long long)b * mask_bstride + (long long)r * mask_step] ? 1.f : 0.f;
+    float v[8];
+    load8(y + off, v);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = (mish_f(v[i] * ga[i] + be[i]) + tb[i]) * m;
+    store8(out + off, v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// One warp per row (512 channels = 16 per lane, as two 8-wide vectors 256 apart).
+//   u   = Mish(GN(y2)) * mask + r                                  (ResnetBlock1D, decoder.py:98-99)
+//   s   = (u - mean_c(u)) / sqrt(var_c(u) + 1e-5) * scale[b] + bias[b]   (SpeakerAdapter, decoder.py:34-45)
+//   hres = s (f32 residual stream);  ln = LayerNorm(s) * g1 + b1 (OT)    (transformer.py:286)
+template <typename OT>
+__global__ void __launch_bounds__(256) gn_res_spk_ln(const float* __restrict__ y, const float* __restrict__ part,
+                                                     int mtiles, int T, long long bstride,
+                                                     const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                     const float* __restrict__ res, const uint8_t* __restrict__ mask,
+                                                     int mask_bstride, int mask_step,
+                                                     const float* __restrict__ spk_scale /*[B][512]*/,
+                                                     const float* __restrict__ spk_bias, const float* __restrict__ ln_g,
+                                                     const float* __restrict__ ln_b, float* __restrict__ hres,
+                                                     OT* __restrict__ ln_out, int rows_per_block) {
+  __shared__ float stats[16];
+  __shared__ double red[256];
+  const int b = blockIdx.y;
+  gn_reduce_stats(part, b, mtiles, T, stats, red);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int r0 = blockIdx.x * rows_per_block;
+  const int r1 = min(r0 + rows_per_block, T);
+  for (int r = r0 + warp; r < r1; r += 8) {
+    const long long rowoff = b * bstride + (long long)r * kC;
+    const float m = mask[(long long)b * mask_bstride + (long long)r * mask_step] ? 1.f : 0.f;
+    float u[16];
+#pragma unroll
+    for (int hlf = 0; hlf < 2; ++hlf) {
+      const int c = hlf * 256 + lane * 8;
+      const int g = c >> 6;
+      const float mean = stats[2 * g], rstd = stats[2 * g + 1];
+      float v[8], rr[8], ga[8], be[8];
+      load8(y + rowoff + c, v);
+      load8(res + rowoff + c, rr);
+      load8(gamma + c, ga);
+      load8(beta + c, be);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) u[hlf * 8 + i] = mish_f((v[i] - mean) * rstd * ga[i] + be[i]) * m + rr[i];
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += u[i];
+    const float mu = warp_sum(s) * (1.0f / kC);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { u[i] -= mu; q += u[i] * u[i]; }
+    const float inv = 1.0f / sqrtf(warp_sum(q) * (1.0f / kC) + 1e-5f);
+    float s2 = 0.f;
+#pragma unroll
+    for (int hlf = 0; hlf < 2; ++hlf) {
+      const int c = hlf * 256 + lane * 8;
+      float sc[8], sb[8], o[8];
+      load8(spk_scale + (long long)b * kC + c, sc);
+      load8(spk_bias + (long long)b * kC + c, sb);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        o[i] = u[hlf * 8 + i] * inv * sc[i] + sb[i];
+        u[hlf * 8 + i] = o[i];
+        s2 += o[i];
+      }
+      store8(hres + rowoff + c, o);
+    }
+    const float mu2 = warp_sum(s2) * (1.0f / kC);
+    float q2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { u[i] -= mu2; q2 += u[i] * u[i]; }
+    const float inv2 = rsqrtf(warp_sum(q2) * (1.0f / kC) + 1e-5f);
+#pragma unroll
+    for (int hlf = 0; hlf < 2; ++hlf) {
+      const int c = hlf * 256 + lane * 8;
+      float g1[8], b1[8], o[8];
+      load8(ln_g + c, g1);
+      load8(ln_b + c, b1);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = u[hlf * 8 + i] * inv2 * g1[i] + b1[i];
+      store8(ln_out + rowoff + c, o);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// LayerNorm over 512 channels, affine, eps 1e-5; one warp per row.
+template <typename OT>
+__global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, long long nrows,
+                                                        const float* __restrict__ g, const float* __restrict__ bta,
+                                                        OT* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (r >= nrows) return;
+  const long long rowoff = r * kC;
+  float u[16];
+#pragma unroll
+  for (int hlf = 0; hlf < 2; ++hlf) {
+    float v[8];
+    load8(x + rowoff + hlf * 256 + lane * 8, v);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) u[hlf * 8 + i] = v[i];
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) s += u[i];
+  const float mu = warp_sum(s) * (1.0f / kC);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { u[i] -= mu; q += u[i] * u[i]; }
+  const float inv = rsqrtf(warp_sum(q) * (1.0f / kC) + 1e-5f);
+#pragma unroll
+  for (int hlf = 0; hlf < 2; ++hlf) {
+    const int c = hlf * 256 + lane * 8;
+    float gg[8], bb[8], o[8];
+    load8(g + c, gg);
+    load8(bta + c, bb);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = u[hlf * 8 + i] * inv * gg[i] + bb[i];
+    store8(out + rowoff + c, o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// P[z][q][k] = softmax_k(scores[z][q][k]) with keys where mask[b][k*step] == 0 excluded.  One block per row.
+template <typename OT>
+__global__ void __launch_bounds__(128) softmax_kernel(const float* __restrict__ sc, int S, int ld, int HB,
+                                                      const uint8_t* __restrict__ mask, int mask_bstride,
+                                                      int mask_step, OT* __restrict__ P) {
+  __shared__ float redf[4];
+  const long long rowi = (long long)blockIdx.y * S + blockIdx.x;   // z * S + q
+  const int b = blockIdx.y / HB;
+  const float* row = sc + rowi * ld;
+  const uint8_t* mk = mask + (long long)b * mask_bstride;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float mx = -INFINITY;
+  for (int k = threadIdx.x; k < S; k += 128)
+    if (mk[(long long)k * mask_step]) mx = fmaxf(mx, row[k]);
+  mx = warp_max(mx);
+  if (lane == 0) redf[warp] = mx;
+  __syncthreads();
+  mx = fmaxf(fmaxf(redf[0], redf[1]), fmaxf(redf[2], redf[3]));
+  __syncthreads();
+  float sum = 0.f;
+  for (int k = threadIdx.x; k < S; k += 128)
+    if (mk[(long long)k * mask_step]) sum += expf(row[k] - mx);
+  sum = warp_sum(sum);
+  if (lane == 0) redf[warp] = sum;
+  __syncthreads();
+  const float inv = 1.0f / (redf[0] + redf[1] + redf[2] + redf[3]);
+  OT* prow = P + rowi * ld;
+  for (int k = threadIdx.x; k < S; k += 128) {
+    const float pv = mk[(long long)k * mask_step] ? expf(row[k] - mx) * inv : 0.f;
+    from_f(prow + k, pv);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// out[s][o] = act_out( W[o] . act_in(in[s]) + bias[o] ),  fp32, one warp per (s, o).  I % 4 == 0 not required.
+enum GemvAct : int { ACT_NONE = 0, ACT_SILU = 1, ACT_MISH = 2 };
+__device__ __forceinline__ float apply_act(float v, int a) {
+  return a == ACT_SILU ? silu_f(v) : (a == ACT_MISH ? mish_f(v) : v);
+}
+__global__ void __launch_bounds__(256) gemv_kernel(const float* __restrict__ W, const float* __restrict__ bias,
+                                                   const float* __restrict__ in, float* __restrict__ out, int I, int O,
+                                                   int act_in, int act_out) {
+  const int lane = threadIdx.x & 31;
+  const int o = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int s = blockIdx.y;
+  if (o >= O) return;
+  const float* w = W + (long long)o * I;
+  const float* x = in + (long long)s * I;
+  float acc = 0.f;
+  for (int i = lane; i < I; i += 32) acc += w[i] * apply_act(x[i], act_in);
+  acc = warp_sum(acc);
+  if (lane == 0) out[(long long)s * O + o] = apply_act(acc + (bias ? bias[o] : 0.f), act_out);
+}
+
+// emb[s][j] = sin(1000 t_s f_j), emb[s][half + j] = cos(...),  f_j = exp(-j ln(1e4)/(half-1))  (decoder.py:54-63)
+__global__ void sinusoid_kernel(const float* __restrict__ ts, int dim, float e /* ln(1e4)/(half-1) */,
+                                float* __restrict__ emb) {
+  const int s = blockIdx.x;
+  const int half = dim / 2;
+  for (int j = threadIdx.x; j < half; j += blockDim.x) {
+    const float f = expf((float)j * -e);
+    const float a = 1000.f * ts[s] * f;
+    emb[(long long)s * dim + j] = sinf(a);
+    emb[(long long)s * dim + half + j] = cosf(a);
+  }
+}
+
+}  // namespace srn
