@@ -80,6 +80,10 @@ int srn_debug_enable(SrnHandle* h, int32_t enable);
 int srn_debug_fetch(SrnHandle* h, const char* name, float* host_out, int64_t capacity, int64_t* n_out,
                     int32_t* rows_out, int32_t* cols_out);
 
+/* Per-op CUDA-event timing of one estimator forward at (B, T) on synthetic contents: writes a JSON array
+ * [{"op": name, "kernel": kind, "ms": avg, "flops": algorithmic flops, "bytes": algorithmic bytes}, ...]. */
+int srn_profile_ops(SrnHandle* h, int32_t B, int32_t T, int32_t reps, char* json_out, int64_t capacity);
+
 #ifdef __cplusplus
 }
 #endif

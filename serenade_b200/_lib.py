@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_PKG, "libserenade_b200.so")
 EXPORTED_SYMBOLS = [
     "srn_last_error", "srn_version", "srn_create", "srn_destroy", "srn_load_weight", "srn_finalize_weights",
     "srn_estimator_forward", "srn_solve_euler", "srn_solve_euler_host", "srn_launch_count", "srn_set_use_graph",
-    "srn_debug_enable", "srn_debug_fetch",
+    "srn_debug_enable", "srn_debug_fetch", "srn_profile_ops",
 ]
 
 PRECISION_BF16 = 0
@@ -55,6 +55,7 @@ def load_library() -> C.CDLL:
     lib.srn_set_use_graph.argtypes = [vp, i32]
     lib.srn_debug_enable.argtypes = [vp, i32]
     lib.srn_debug_fetch.argtypes = [vp, C.c_char_p, f32p, i64, C.POINTER(i64), C.POINTER(i32), C.POINTER(i32)]
+    lib.srn_profile_ops.argtypes = [vp, i32, i32, i32, C.c_char_p, i64]
     for name in EXPORTED_SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("srn_last_error", "srn_launch_count", "srn_version"):

@@ -75,6 +75,13 @@ class _Engine:
     def set_use_graph(self, flag: bool) -> None:
         _lib.check(self.lib.srn_set_use_graph(self.h, int(flag)), "srn_set_use_graph")
 
+    def profile_ops(self, B: int, T: int, reps: int = 5):
+        """[(op name, kernel, avg ms)] for one estimator forward at (B, T): CUDA-event timing per op."""
+        import json
+        buf = C.create_string_buffer(1 << 16)
+        _lib.check(self.lib.srn_profile_ops(self.h, B, T, reps, buf, len(buf)), "srn_profile_ops")
+        return json.loads(buf.value.decode())
+
     # test hooks -----------------------------------------------------------------------------
     def debug_enable(self, flag: bool) -> None:
         _lib.check(self.lib.srn_debug_enable(self.h, int(flag)), "srn_debug_enable")
@@ -253,7 +260,7 @@ class CFM(nn.Module):
     def decode_host(self, z, mu, mask, spks, t_span, out=None, device=None):
         """End-to-end decode from HOST tensors (pinned for speed): H2D of z/mu/mask/spk, the Euler solve and
         the D2H of the mel all happen inside the C-ABI call `srn_solve_euler_host`."""
-        device = torch.device(device if device is not None else ("cuda", torch.cuda.current_device()))
+        device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
         est = self.estimator
         est._check_inputs(z, mask, mu, spks)
         eng = est.engine(device)

@@ -175,4 +175,14 @@ SRN_EXPORT int srn_debug_fetch(SrnHandle* h, const char* name, float* host_out, 
   SRN_API_END
 }
 
+SRN_EXPORT int srn_profile_ops(SrnHandle* h, int32_t B, int32_t T, int32_t reps, char* json_out, int64_t capacity) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (json_out == nullptr || capacity < 2 || reps < 1) srn::fail("srn_profile_ops: bad arguments");
+  const std::string js = h->eng->profile_ops(B, T, reps);
+  if ((int64_t)js.size() + 1 > capacity) srn::fail("srn_profile_ops: output buffer too small (%zu needed)", js.size() + 1);
+  memcpy(json_out, js.c_str(), js.size() + 1);
+  SRN_API_END
+}
+
 }  // extern "C"

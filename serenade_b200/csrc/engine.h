@@ -31,6 +31,7 @@ class EngineBase {
                            cudaStream_t st) = 0;
   virtual void solve_euler_host(const float* z, const float* mu, const uint8_t* mask, const float* spk,
                                 const float* t_span, int n_steps, int B, int T, float* mel_out, cudaStream_t st) = 0;
+  virtual std::string profile_ops(int B, int T, int reps) = 0;
   int64_t launches = 0;
   bool use_graph = true;
   bool debug = false;

@@ -118,6 +118,7 @@ class Engine : public EngineBase {
                    cudaStream_t st) override;
   void solve_euler_host(const float* z, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
                         int n_steps, int B, int T, float* mel_out, cudaStream_t st) override;
+  std::string profile_ops(int B, int T, int reps) override;
 
  private:
   static constexpr int BK = OpTraits<OT>::kBK;

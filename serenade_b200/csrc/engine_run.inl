@@ -290,3 +290,64 @@ void Engine<OT>::solve_euler_host(const float* z, const float* mu, const uint8_t
 }
 
 }  // namespace srn
+
+namespace srn {
+
+// Per-op timing of one estimator forward (CUDA events around `reps` back-to-back launches of each op).
+// Algorithmic work: GEMM flops = 2 * valid rows * N * K (K as issued, incl. zero padding of C_in 242 -> 256);
+// row-kernel bytes = the tensors they must read and write once.
+template <typename OT>
+std::string Engine<OT>::profile_ops(int B, int T, int reps) {
+  Plan<OT>& pl = get_plan(B, T);
+  cudaStream_t st = nullptr;
+  ensure_step_buffers(pl, 1, cfg_.in_channels, (int)resnets_.size());
+  SRN_CUDA(cudaMemset(pl.mask.p, 1, pl.mask.bytes));
+  SRN_CUDA(cudaMemset(pl.tsteps.p, 0, 4));
+  SRN_CUDA(cudaMemset(pl.dts.p, 0, 4));
+  blend_active_ = false;
+  const bool dbg = debug;
+  debug = false;
+  prepass(pl, std::vector<float>{0.f}, std::vector<float>{0.f}, st);
+  run_forward(pl, 0, nullptr, true, st);
+  SRN_CUDA(cudaStreamSynchronize(st));
+  cudaEvent_t e0, e1;
+  SRN_CUDA(cudaEventCreate(&e0));
+  SRN_CUDA(cudaEventCreate(&e1));
+  std::string js = "[";
+  const size_t es = sizeof(OT);
+  for (size_t i = 0; i < pl.ops.size(); ++i) {
+    Op& op = pl.ops[i];
+    SRN_CUDA(cudaEventRecord(e0, st));
+    for (int r = 0; r < reps; ++r) launch_op(pl, op, 0, nullptr, true, st);
+    SRN_CUDA(cudaEventRecord(e1, st));
+    SRN_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    SRN_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    const Level& L = pl.lv[op.level];
+    double flops = 0, bytes = 0;
+    const char* kind = "";
+    const double rows = (double)B * L.T;
+    switch (op.kind) {
+      case OP_GEMM:
+        kind = op.bn == 256 ? "gemm_bn256" : "gemm_bn128";
+        flops = 2.0 * (double)op.gp.M * op.gp.N * ((double)op.gp.nkb * BK) * (double)(B * op.gp.HB);
+        break;
+      case OP_PACKX: kind = "pack_cf_to_cl"; bytes = (double)B * cfg_.out_channels * T * (4 + es); break;
+      case OP_GN_APPLY: kind = "gn_apply"; bytes = rows * 512 * (4 + es); break;
+      case OP_GN_RES_SPK_LN: kind = "gn_res_spk_ln"; bytes = rows * 512 * (4 + 4 + 4 + es); break;
+      case OP_LAYERNORM: kind = "layernorm"; bytes = rows * 512 * (4 + es); break;
+      case OP_SOFTMAX: kind = "softmax"; bytes = (double)B * 4 * L.T * L.T * (4 + es); break;
+    }
+    char buf[512];
+    snprintf(buf, sizeof buf, "%s{\"op\": \"%s\", \"kernel\": \"%s\", \"ms\": %.6f, \"flops\": %.6e, \"bytes\": %.6e}",
+             i ? ", " : "", op.name.c_str(), kind, ms / reps, flops, bytes);
+    js += buf;
+  }
+  js += "]";
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  debug = dbg;
+  return js;
+}
+
+}  // namespace srn
