@@ -9,10 +9,10 @@ namespace srn {
 
 template <typename OT>
 static void configure_kernels() {
-  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, 128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                gemm_smem_bytes<128, 3>()));
-  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, 256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                gemm_smem_bytes<256, 4>()));
+  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                GemmCfg<128>::kSmemBytes));
+  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                GemmCfg<256>::kSmemBytes));
 }
 
 std::unique_ptr<EngineBase> make_engine(const SrnConfig& cfg) {

@@ -124,6 +124,7 @@ class Engine : public EngineBase {
   static constexpr int BK = OpTraits<OT>::kBK;
   SrnConfig cfg_;
   int cmu_ = 0;
+  int num_sms_ = 148;
   bool finalized_ = false;
   std::map<std::string, HostTensor> host_w_;
   std::list<DevBuf> arena_;

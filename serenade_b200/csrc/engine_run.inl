@@ -4,18 +4,22 @@ namespace srn {
 static inline float to_f_host(float v) { return v; }
 static inline float to_f_host(__nv_bfloat16 v) { return __bfloat162float(v); }
 
-template <typename OT, int BN, int STAGES>
-static void launch_gemm_impl(const GemmParams& gp, dim3 grid, cudaStream_t st) {
-  constexpr int smem = gemm_smem_bytes<BN, STAGES>();
-  gemm_kernel<OT, BN, STAGES><<<grid, 192, smem, st>>>(gp);
+template <typename OT, int BN>
+static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t st) {
+  gp.ntn = (int)grid.x;
+  gp.ntm = (int)grid.y;
+  gp.nz = (int)grid.z;
+  const long long tiles = (long long)grid.x * grid.y * grid.z;
+  const unsigned ctas = (unsigned)std::min<long long>(tiles, num_sms);   // persistent: one CTA per SM
+  gemm_kernel<OT, BN><<<ctas, GemmCfg<BN>::kThreads, GemmCfg<BN>::kSmemBytes, st>>>(gp);
   SRN_CUDA(cudaGetLastError());
 }
 
 template <typename OT>
 void Engine<OT>::launch_gemm(const GemmParams& gp, int bn, dim3 grid, cudaStream_t st) {
   if (gp.nkb < 1 || gp.nseg < 1) fail("gemm with empty K");
-  if (bn == 256) launch_gemm_impl<OT, 256, 4>(gp, grid, st);
-  else launch_gemm_impl<OT, 128, 3>(gp, grid, st);
+  if (bn == 256) launch_gemm_impl<OT, 256>(gp, grid, num_sms_, st);
+  else launch_gemm_impl<OT, 128>(gp, grid, num_sms_, st);
   ++launches;
 }
 
@@ -100,9 +104,18 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
       ++launches;
     } break;
     case OP_SOFTMAX: {
-      dim3 grid(L.T, B * 4);
-      softmax_kernel<OT><<<grid, 128, 0, st>>>(pl.sc.template as<float>(), L.T, L.Sp, 4, mask, pl.Tp, L.mask_step,
-                                               pl.P.template as<OT>());
+      const long long nrows = (long long)B * 4 * L.T;
+      const unsigned grid = (unsigned)((nrows + 1) / 2);
+      const float* sc = pl.sc.template as<float>();
+      OT* P = pl.P.template as<OT>();
+#define SRN_SOFTMAX(NV) softmax_kernel<OT, NV><<<grid, 256, 0, st>>>(sc, L.T, L.Sp, 4, nrows, mask, pl.Tp, L.mask_step, P)
+      if (L.T <= 512) SRN_SOFTMAX(1);
+      else if (L.T <= 1024) SRN_SOFTMAX(2);
+      else if (L.T <= 2048) SRN_SOFTMAX(4);
+      else if (L.T <= 4096) SRN_SOFTMAX(8);
+      else if (L.T <= 8192) SRN_SOFTMAX(16);
+      else fail("sequence of %d frames exceeds the softmax kernel's 8192-key limit", L.T);
+#undef SRN_SOFTMAX
       SRN_CUDA(cudaGetLastError());
       ++launches;
     } break;

@@ -18,6 +18,9 @@ Engine<OT>::Engine(const SrnConfig& cfg) : cfg_(cfg) {
   if (cfg.in_channels % 2 != 0) fail("in_channels must be even (SinusoidalPosEmb, decoder.py:52)");
   if (cfg.spk_embed_dim < 1 || cfg.num_mid_blocks < 0) fail("bad spk_embed_dim / num_mid_blocks");
   cmu_ = cfg.in_channels - cfg.out_channels;
+  int dev = 0;
+  SRN_CUDA(cudaGetDevice(&dev));
+  SRN_CUDA(cudaDeviceGetAttribute(&num_sms_, cudaDevAttrMultiProcessorCount, dev));
 }
 
 template <typename OT>

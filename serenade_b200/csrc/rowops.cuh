@@ -269,35 +269,72 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
 
 // ------------------------------------------------------------------------------------------------
 // P[z][q][k] = softmax_k(scores[z][q][k]) with keys where mask[b][k*step] == 0 excluded.  One block per row.
-template <typename OT>
-__global__ void __launch_bounds__(128) softmax_kernel(const float* __restrict__ sc, int S, int ld, int HB,
-                                                      const uint8_t* __restrict__ mask, int mask_bstride,
-                                                      int mask_step, OT* __restrict__ P) {
-  __shared__ float redf[4];
-  const long long rowi = (long long)blockIdx.y * S + blockIdx.x;   // z * S + q
-  const int b = blockIdx.y / HB;
-  const float* row = sc + rowi * ld;
+// Single pass over HBM: each 128-thread half-block owns one row and keeps it in registers (NV float4 per thread,
+// S <= 512 * NV); scores are read once (4 B/elem) and P written once.  ld must be a multiple of 4.
+__device__ __forceinline__ void store4(float* p, float a, float b, float c, float d) {
+  *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+}
+__device__ __forceinline__ void store4(__nv_bfloat16* p, float a, float b, float c, float d) {
+  __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&lo);
+  u.y = *reinterpret_cast<uint32_t*>(&hi);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+
+template <typename OT, int NV>
+__global__ void __launch_bounds__(256) softmax_kernel(const float* __restrict__ sc, int S, int ld, int HB,
+                                                      long long nrows, const uint8_t* __restrict__ mask,
+                                                      int mask_bstride, int mask_step, OT* __restrict__ P) {
+  __shared__ float redf[2][4];
+  const int half = threadIdx.x >> 7, t = threadIdx.x & 127;
+  const int lane = threadIdx.x & 31, warp = (threadIdx.x >> 5) & 3;
+  const long long rowi = (long long)blockIdx.x * 2 + half;        // z * S + q
+  const bool live = rowi < nrows;
+  const long long rr = live ? rowi : 0;
+  const int b = (int)((rr / S) / HB);
+  const float* row = sc + rr * ld;
   const uint8_t* mk = mask + (long long)b * mask_bstride;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float v[NV][4];
   float mx = -INFINITY;
-  for (int k = threadIdx.x; k < S; k += 128)
-    if (mk[(long long)k * mask_step]) mx = fmaxf(mx, row[k]);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int k = (i * 128 + t) * 4;
+    float4 x4 = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    if (live && k < S) x4 = *reinterpret_cast<const float4*>(row + k);   // k + 3 < ld always (ld % 4 == 0)
+    v[i][0] = x4.x; v[i][1] = x4.y; v[i][2] = x4.z; v[i][3] = x4.w;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const bool ok = live && (k + j < S) && mk[(long long)(k + j) * mask_step] != 0;
+      v[i][j] = ok ? v[i][j] : -INFINITY;
+      mx = fmaxf(mx, v[i][j]);
+    }
+  }
   mx = warp_max(mx);
-  if (lane == 0) redf[warp] = mx;
+  if (lane == 0) redf[half][warp] = mx;
   __syncthreads();
-  mx = fmaxf(fmaxf(redf[0], redf[1]), fmaxf(redf[2], redf[3]));
+  mx = fmaxf(fmaxf(redf[half][0], redf[half][1]), fmaxf(redf[half][2], redf[half][3]));
   __syncthreads();
+  if (mx == -INFINITY) mx = 0.f;          // fully masked row: all probabilities 0 instead of NaN
   float sum = 0.f;
-  for (int k = threadIdx.x; k < S; k += 128)
-    if (mk[(long long)k * mask_step]) sum += expf(row[k] - mx);
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      v[i][j] = expf(v[i][j] - mx);       // exp(-inf) = 0 for masked / out-of-range keys
+      sum += v[i][j];
+    }
   sum = warp_sum(sum);
-  if (lane == 0) redf[warp] = sum;
+  if (lane == 0) redf[half][warp] = sum;
   __syncthreads();
-  const float inv = 1.0f / (redf[0] + redf[1] + redf[2] + redf[3]);
+  const float tot = redf[half][0] + redf[half][1] + redf[half][2] + redf[half][3];
+  const float inv = tot > 0.f ? 1.0f / tot : 0.f;
+  if (!live) return;
   OT* prow = P + rowi * ld;
-  for (int k = threadIdx.x; k < S; k += 128) {
-    const float pv = mk[(long long)k * mask_step] ? expf(row[k] - mx) * inv : 0.f;
-    from_f(prow + k, pv);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int k = (i * 128 + t) * 4;
+    if (k < S) store4(prow + k, v[i][0] * inv, v[i][1] * inv, v[i][2] * inv, v[i][3] * inv);   // pad cols < ld
   }
 }
 
