@@ -9,7 +9,8 @@ static thread_local std::string g_last_error;
 void set_last_error(const std::string& msg) { g_last_error = msg; }
 
 CUtensorMap make_tmap_3d(const void* base, int elem_bytes, uint64_t inner, uint64_t rows, uint64_t batch,
-                         uint64_t ld_elems, uint64_t bstride_elems, uint32_t box_inner, uint32_t box_rows) {
+                         uint64_t ld_elems, uint64_t bstride_elems, uint32_t box_inner, uint32_t box_rows,
+                         bool swizzle128) {
   using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                 const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                 CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -23,7 +24,7 @@ CUtensorMap make_tmap_3d(const void* base, int elem_bytes, uint64_t inner, uint6
   }
   if (reinterpret_cast<uintptr_t>(base) % 16 != 0) fail("TMA base address not 16-byte aligned");
   if ((ld_elems * elem_bytes) % 16 != 0 || (bstride_elems * elem_bytes) % 16 != 0) fail("TMA stride not a multiple of 16 bytes");
-  if (box_inner * elem_bytes != 128) fail("TMA box inner extent must be 128 bytes (SWIZZLE_128B)");
+  if (swizzle128 && box_inner * elem_bytes != 128) fail("TMA box inner extent must be 128 bytes (SWIZZLE_128B)");
   CUtensorMap m;
   memset(&m, 0, sizeof m);
   cuuint64_t dims[3] = {inner, rows, batch};
@@ -32,7 +33,7 @@ CUtensorMap make_tmap_3d(const void* base, int elem_bytes, uint64_t inner, uint6
   cuuint32_t estr[3] = {1, 1, 1};
   const CUtensorMapDataType dt = elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   CUresult r = encode(&m, dt, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                      swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) fail("cuTensorMapEncodeTiled failed with CUresult %d (inner=%llu rows=%llu batch=%llu ld=%llu)", (int)r,
                               (unsigned long long)inner, (unsigned long long)rows, (unsigned long long)batch,
                               (unsigned long long)ld_elems);

@@ -58,6 +58,7 @@ struct DevBuf {
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency).
 CUtensorMap make_tmap_3d(const void* base, int elem_bytes, uint64_t inner, uint64_t rows, uint64_t batch,
-                         uint64_t ld_elems, uint64_t bstride_elems, uint32_t box_inner, uint32_t box_rows);
+                         uint64_t ld_elems, uint64_t bstride_elems, uint32_t box_inner, uint32_t box_rows,
+                         bool swizzle128 = true);
 
 }  // namespace srn

@@ -42,16 +42,24 @@ void set_A(GemmParams& gp, int idx, const OT* ptr, int cols, int rows, long long
 }
 template <typename OT>
 void set_B_weight(GemmParams& gp, const OT* W, int N, int K, int bn) {
-  gp.mapB = make_tmap_3d(W, sizeof(OT), K, N, 1, K, (uint64_t)N * K, OpTraits<OT>::kBK, bn);
+  gp.mapB = make_tmap_3d(W, sizeof(OT), K, N, 1, K, (uint64_t)N * K, OpTraits<OT>::kBK, bn / 2);   // each CTA of a pair loads half the B rows
   gp.b_batch_mode = 0;
+}
+// Output store map: 32-row x 128-byte boxes, SWIZZLE_128B (see gemm_epilogue.cuh)
+template <typename T>
+void set_D(GemmParams& gp, const T* ptr, int cols, int rows, long long bstride, int ld, int nbatch) {
+  gp.mapD = make_tmap_3d(ptr, sizeof(T), cols, rows, nbatch, ld, (uint64_t)bstride, 128 / sizeof(T), 32);
 }
 inline void add_seg(GemmParams& gp, int src, int col0, int shift, int nblk) {
   if (gp.nseg >= 6) fail("too many K segments");
   gp.seg[gp.nseg++] = KSeg{src, col0, shift, nblk};
   gp.nkb += nblk;
 }
+// row_tiles = number of 256-row pair tiles; one CTA pair per SM pair (74 on a B200)
 inline int pick_bn(int N, long long row_tiles) {
-  return (N % 256 == 0 && (long long)(N / 256) * row_tiles >= 148) ? 256 : 128;
+  const long long nt256 = (N + 255) / 256;
+  const bool little_waste = nt256 * 256 * 10 <= (long long)N * 11;
+  return (little_waste && nt256 * row_tiles >= 74) ? 256 : 128;
 }
 }  // namespace
 
@@ -86,6 +94,7 @@ void Engine<OT>::add_resnet(Plan<OT>& pl, int ridx, int level, const OT* src0, i
     gp.out_bstride = hs;
     gp.ldo = 512;
     gp.gn_part = gn ? pl.gnpart.template as<float>() : nullptr;
+    set_D<float>(gp, out, 512, L.T, hs, 512, B);
     op.grid = dim3(512 / op.bn, L.mtiles, B);
     op.tap = Tap{nullptr, out, 0, L.T, 512, 512, hs, B, 0};
     op.level = level;
@@ -167,6 +176,8 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.out2 = vt;
     gp.out2_bstride = (long long)2048 * Sp;
     gp.ld2 = Sp;
+    set_D<OT>(gp, qk, 4096, S, gp.out_bstride, 4096, B);
+    gp.mapD2 = make_tmap_3d(vt, sizeof(OT), S, 2048, B, Sp, (uint64_t)2048 * Sp, 32, 32, false);
     op.grid = dim3(6144 / op.bn, L.mtiles, B);
     op.tap = Tap{"qk", qk, 1, S, 4096, 4096, gp.out_bstride, B, 0};
     push(op, "qkv");
@@ -175,12 +186,12 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     Op op;
     op.gp = base_gemm(pl, level);
     GemmParams& gp = op.gp;
-    op.bn = 128;
+    op.bn = pick_bn(S, tiles * H);
     gp.HB = H;
     set_A<OT>(gp, 0, qk, 4096, S, L.R, 4096, B);
     gp.a_hcol = 512;
     add_seg(gp, 0, 0, 0, 512 / BK);
-    gp.mapB = make_tmap_3d(qk, sizeof(OT), 4096, S, B, 4096, (uint64_t)L.R * 4096, BK, op.bn);
+    gp.mapB = make_tmap_3d(qk, sizeof(OT), 4096, S, B, 4096, (uint64_t)L.R * 4096, BK, op.bn / 2);
     gp.b_col0 = 2048;
     gp.b_hcol = 512;
     gp.b_batch_mode = 1;
@@ -191,6 +202,8 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.out_bstride = (long long)H * S * Sp;
     gp.out_hstride = (long long)S * Sp;
     gp.ldo = Sp;
+    set_D<float>(gp, sc, S, S, (long long)S * Sp, Sp, B * H);
+    gp.d_zbatch = 1;
     op.grid = dim3(cdiv(S, op.bn), L.mtiles, B * H);
     op.tap = Tap{"sc", sc, 0, S, S, Sp, (long long)S * Sp, B * H, 0};
     push(op, "scores");
@@ -213,7 +226,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.a_zbatch = 1;
     add_seg(gp, 0, 0, 0, cdiv(S, BK));
     op.bn = pick_bn(512, tiles * H);
-    gp.mapB = make_tmap_3d(vt, sizeof(OT), S, 2048, B, Sp, (uint64_t)2048 * Sp, BK, op.bn);
+    gp.mapB = make_tmap_3d(vt, sizeof(OT), S, 2048, B, Sp, (uint64_t)2048 * Sp, BK, op.bn / 2);
     gp.b_hrow = 512;
     gp.b_batch_mode = 1;
     gp.N = 512;
@@ -222,6 +235,8 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.out_bstride = (long long)L.R * 2048;
     gp.out_hstride = 512;
     gp.ldo = 2048;
+    set_D<OT>(gp, ao, 2048, S, gp.out_bstride, 2048, B);
+    gp.d_hcol = 512;
     op.grid = dim3(512 / op.bn, L.mtiles, B * H);
     op.tap = Tap{"ao", ao, 1, S, 2048, 2048, gp.out_bstride, B, 0};
     push(op, "pv");
@@ -243,6 +258,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.out = hres;
     gp.out_bstride = gp.resid_bstride;
     gp.ldo = 512;
+    set_D<float>(gp, hres, 512, S, gp.out_bstride, 512, B);
     op.grid = dim3(512 / op.bn, L.mtiles, B);
     op.tap = Tap{"h_attn", hres, 0, S, 512, 512, gp.out_bstride, B, 0};
     push(op, "attn_out");
@@ -263,7 +279,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     GemmParams& gp = op.gp;
     set_A<OT>(gp, 0, ln, 512, S, L.R, 512, B);
     add_seg(gp, 0, 0, 0, 512 / BK);
-    op.bn = pick_bn(4096, tiles);
+    op.bn = 256;   // the GEGLU epilogue packs 4 chunks (128 accumulator columns) per 128-byte output row
     set_B_weight<OT>(gp, w.wgl, 4096, 512, op.bn);
     gp.N = 4096;
     gp.epi = EPI_GEGLU;
@@ -271,6 +287,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.out = gg;
     gp.out_bstride = (long long)L.R * 2048;
     gp.ldo = 2048;
+    set_D<OT>(gp, gg, 2048, S, gp.out_bstride, 2048, B);
     op.grid = dim3(4096 / op.bn, L.mtiles, B);
     op.tap = Tap{"gg", gg, 1, S, 2048, 2048, gp.out_bstride, B, 0};
     push(op, "geglu");
@@ -295,6 +312,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.rowmask = pl.mask.template as<uint8_t>();
     gp.mask_bstride = pl.Tp;
     gp.mask_step = L.mask_step;
+    set_D<OT>(gp, out_hc, 512, S, gp.out_bstride, 512, B);
     op.grid = dim3(512 / op.bn, L.mtiles, B);
     op.tap = Tap{"tfm", out_hc, 1, S, 512, 512, gp.out_bstride, B, 0};
     push(op, "ff_out");
@@ -306,14 +324,14 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
   const int B = pl.B, T = pl.T, H = 4, C = 512;
   const int T2 = (T + 1) / 2;
   pl.Tp = 2 * T2;
-  pl.lv[0] = Level{T, pl.Tp, round_up(T, 8), cdiv(T, 128), 1};
-  pl.lv[1] = Level{T2, T2, round_up(T2, 8), cdiv(T2, 128), 2};
+  pl.lv[0] = Level{T, pl.Tp, round_up(T, 8), cdiv(T, 256), 1};
+  pl.lv[1] = Level{T2, T2, round_up(T2, 8), cdiv(T2, 256), 2};
   const size_t rows = (size_t)B * pl.Tp;
   const size_t es = sizeof(OT);
   pl.xin.alloc(rows * 256 * es);
   pl.y.alloc(rows * C * 4);
   pl.r.alloc(rows * C * 4);
-  pl.gnpart.alloc((size_t)B * pl.lv[0].mtiles * 16 * 4);
+  pl.gnpart.alloc((size_t)B * 2 * pl.lv[0].mtiles * 16 * 4);   // one (sum, sumsq) x 8 groups per 128-row tile
   pl.a1.alloc(rows * C * es);
   pl.hres.alloc(rows * C * 4);
   pl.ln.alloc(rows * C * es);
@@ -373,6 +391,7 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
     gp.rowmask = mask;
     gp.mask_bstride = pl.Tp;
     gp.mask_step = pl.lv[out_level].mask_step;
+    set_D<OT>(gp, dst, 512, L.T, gp.out_bstride, 512, B);
     op.grid = dim3(512 / op.bn, L.mtiles, B);
     op.tap = Tap{"out", dst, 1, L.T, 512, 512, gp.out_bstride, B, 0};
     pl.ops.push_back(op);
@@ -406,6 +425,7 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
     gp.rowmask = mask;
     gp.mask_bstride = pl.Tp;
     gp.mask_step = 2;
+    set_D<OT>(gp, cv, 512, T2, gp.out_bstride, 512, B);
     op.grid = dim3(512 / op.bn, L.mtiles, B);
     op.tap = Tap{"out", cv, 1, T2, 512, 512, gp.out_bstride, B, 0};
     pl.ops.push_back(op);
@@ -451,6 +471,7 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
     gp.mask_bstride = pl.Tp;
     gp.mask_step = 2;
     gp.mask_off = par;
+    set_D<OT>(gp, cv + par * 512, 512, T2, gp.out_bstride, 1024, B);
     op.grid = dim3(512 / op.bn, L.mtiles, B);
     if (par == 1) op.tap = Tap{"out", cv, 1, T, 512, 512, (long long)pl.Tp * 512, B, 0};
     pl.ops.push_back(op);
@@ -479,6 +500,7 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
     gp.out_bstride = (long long)pl.Tp * 512;
     gp.ldo = 512;
     gp.gn_part = pl.gnpart.template as<float>();
+    set_D<float>(gp, pl.y.template as<float>(), 512, T, gp.out_bstride, 512, B);
     op.grid = dim3(512 / op.bn, L.mtiles, B);
     pl.ops.push_back(op);
   }
@@ -514,6 +536,7 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
     gp.mask_step = 1;
     gp.x_in = pl.x_state.template as<float>();
     gp.T_cf = T;
+    gp.mapD = gp.mapA[0];     // unused by EPI_EULER (direct channels-first stores); keeps the descriptor prefetch valid
     op.grid = dim3(1, pl.lv[0].mtiles, B);
     pl.euler_op = (int)pl.ops.size();
     pl.ops.push_back(op);

@@ -6,13 +6,27 @@ static inline float to_f_host(__nv_bfloat16 v) { return __bfloat162float(v); }
 
 template <typename OT, int BN>
 static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t st) {
+  static const int dbg_mode = getenv("SRN_GEMM_DBG") ? atoi(getenv("SRN_GEMM_DBG")) : 0;
+  gp.dbg_mode = dbg_mode;
   gp.ntn = (int)grid.x;
   gp.ntm = (int)grid.y;
   gp.nz = (int)grid.z;
-  const long long tiles = (long long)grid.x * grid.y * grid.z;
-  const unsigned ctas = (unsigned)std::min<long long>(tiles, num_sms);   // persistent: one CTA per SM
-  gemm_kernel<OT, BN><<<ctas, GemmCfg<BN>::kThreads, GemmCfg<BN>::kSmemBytes, st>>>(gp);
-  SRN_CUDA(cudaGetLastError());
+  const long long tiles = (long long)grid.x * grid.y * grid.z;                 // 256 x BN tiles, one per CTA pair
+  const unsigned pairs = (unsigned)std::min<long long>(tiles, num_sms / 2);    // persistent: one pair per SM pair
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof cfg);
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(GemmCfg<BN>::kThreads);
+  cfg.dynamicSmemBytes = GemmCfg<BN>::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr;
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = 2;
+  attr.val.clusterDim.y = 1;
+  attr.val.clusterDim.z = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
+  SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, BN>, gp));
 }
 
 template <typename OT>
@@ -81,7 +95,7 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
       const float* tb = op.use_tbias ? pl.tb.template as<float>() + ((size_t)op.resnet_idx * pl.tb_steps + step) * 512
                                      : nullptr;
       dim3 grid(cdiv(L.T, 32), B);
-      gn_apply_kernel<OT><<<grid, 256, 0, st>>>(op.y, op.part, L.mtiles, L.T, (long long)L.R * 512, op.gamma, op.beta,
+      gn_apply_kernel<OT><<<grid, 256, 0, st>>>(op.y, op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma, op.beta,
                                                 tb, mask, pl.Tp, L.mask_step, static_cast<OT*>(op.out), 32);
       SRN_CUDA(cudaGetLastError());
       ++launches;
@@ -90,7 +104,7 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
       dim3 grid(cdiv(L.T, 32), B);
       const float* sc = pl.spk_scale.template as<float>() + (size_t)op.resnet_idx * B * 512;
       const float* sb = pl.spk_bias.template as<float>() + (size_t)op.resnet_idx * B * 512;
-      gn_res_spk_ln<OT><<<grid, 256, 0, st>>>(op.y, op.part, L.mtiles, L.T, (long long)L.R * 512, op.gamma, op.beta,
+      gn_res_spk_ln<OT><<<grid, 256, 0, st>>>(op.y, op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma, op.beta,
                                               op.res, mask, pl.Tp, L.mask_step, sc, sb, op.ln_g, op.ln_b, op.hres,
                                               static_cast<OT*>(op.out), 32);
       SRN_CUDA(cudaGetLastError());

@@ -36,6 +36,8 @@ struct KSeg {
 struct GemmParams {
   CUtensorMap mapA[2];
   CUtensorMap mapB;
+  CUtensorMap mapD;    // output tile store: box = 32 rows x 128 bytes, SWIZZLE_128B (all epilogues but EULER)
+  CUtensorMap mapD2;   // EPI_QKV: V^T store, box = 32 (d rows) x 32 (s, contiguous), no swizzle
   KSeg seg[6];
   int nseg;
   int nkb;          // total K blocks
@@ -77,6 +79,9 @@ struct GemmParams {
   const uint8_t* blend_mask;   // optional infill blend (B, T_cf): x_out = blend_src where non-zero
   const float* blend_src;
   int T_cf;         // row length of the channels-first tensors
+  int d_hcol;       // output column offset per h (elements), e.g. 512 for the per-head attention output
+  int d_zbatch;     // output batch coordinate: 1 -> z, 0 -> b
+  int dbg_mode;     // profiling experiments only: 1 = skip TMA loads, 2 = skip MMA issue (results are garbage)
 };
 
 template <typename OT>

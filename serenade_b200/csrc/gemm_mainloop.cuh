@@ -1,0 +1,193 @@
+// The __global__ kernel: role dispatch, TMA/MMA pipelines, epilogue tile loop.  Included by gemm_kernel.cuh.
+#pragma once
+
+namespace srn {
+
+template <typename OT, int BN>
+__global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
+  using TR = OpTraits<OT>;
+  using CFG = GemmCfg<BN>;
+  constexpr int STAGES = CFG::kStages;
+  constexpr int BK = TR::kBK;
+  constexpr int NCH = BN / 32;          // 32-column chunks per tile
+  constexpr int NG = BN / 64;           // GroupNorm groups per tile
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + CFG::kBarOff);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;     // [2] accumulator stage ready for the epilogue
+  uint64_t* tempty_bar = tfull_bar + 2;         // [2] accumulator stage drained by the epilogue
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  float* gn_red = reinterpret_cast<float*>(smem + CFG::kRedOff);   // [2 buffers][4 quarters][NG][2]
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int tiles_mn = p.ntn * p.ntm;
+  const int total_tiles = tiles_mn * p.nz;
+  const uint32_t rank = cluster_ctarank();      // 0 = leader of the pair
+  const int pair0 = blockIdx.x >> 1;
+  const int npairs = gridDim.x >> 1;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&p.mapA[0]);
+    tma_prefetch_desc(&p.mapA[1]);
+    tma_prefetch_desc(&p.mapB);
+    tma_prefetch_desc(&p.mapD);
+  }
+  if (warp == 1 && elect_one()) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], 16);    // one arrival per epilogue warp of both CTAs (leader's copy is used)
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc_2sm<CFG::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      // ------------------------------------------------------------ TMA producer
+      uint32_t stage = 0, phase = 0;
+      for (int tile = pair0; tile < total_tiles; tile += npairs) {
+        const int z = tile / tiles_mn;
+        const int rem = tile - z * tiles_mn;
+        const int m0 = (rem / p.ntn) * 256 + (int)rank * 128;
+        const int n0 = (rem % p.ntn) * BN;
+        const int b = z / p.HB;
+        const int h = z - b * p.HB;
+        const int a_batch = p.a_zbatch ? z : b;
+        const int b_batch = p.b_batch_mode == 0 ? 0 : (p.b_batch_mode == 1 ? b : z);
+        const int b_row = n0 + (int)rank * (BN / 2) + h * p.b_hrow;
+        int seg = 0, j = 0;
+        for (int kb = 0; kb < p.nkb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * CFG::kStageBytes;
+          uint8_t* sb = sa + CFG::kABytes;
+          // both CTAs' bytes complete on the LEADER's full barrier; only the leader arms it (for both)
+          const uint32_t fb = map_to_cta(&full_bar[stage], 0);
+          const KSeg sg = p.seg[seg];
+          if (p.dbg_mode == 1) {
+            if (rank == 0) mbar_arrive(&full_bar[stage]);
+          } else {
+            if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * CFG::kStageBytes);
+            tma_load_3d_2sm(sa, &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol, m0 + sg.shift, a_batch);
+            tma_load_3d_2sm(sb, &p.mapB, fb, p.b_col0 + kb * BK + h * p.b_hcol, b_row, b_batch);
+          }
+          if (++j == sg.nblk) { j = 0; ++seg; }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0 && elect_one()) {
+      // ------------------------------------------------------------ MMA issuer (leader CTA only, M = 256)
+      constexpr uint32_t idesc = make_idesc(TR::kFmt, 256, BN);
+      uint32_t stage = 0, phase = 0;
+      uint32_t it = 0;
+      for (int tile = pair0; tile < total_tiles; tile += npairs, ++it) {
+        const uint32_t as = it & 1;
+        mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + as * BN;
+        for (int kb = 0; kb < p.nkb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * CFG::kStageBytes);
+          const uint64_t da = make_kmajor_sw128_desc(sa);
+          const uint64_t db = make_kmajor_sw128_desc(sa + CFG::kABytes);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)   // 4 x 32 bytes of K per 128-byte swizzled row
+            if (p.dbg_mode != 2) umma_pair<TR::kTF32>(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          tc_commit_pair(&empty_bar[stage]);     // frees the stage in both CTAs
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        tc_commit_pair(&tfull_bar[as]);          // both CTAs' epilogues may drain their half
+      }
+    }
+  } else {
+    // -------------------------------------------------------------- epilogue (8 warps)
+    const int q = warp & 3;                 // TMEM lane quarter this warp may access (warp id % 4)
+    const int sub = (warp - 2) >> 2;        // which half of the tile's columns
+    Stager st;
+    st.base = smem_u32(smem + CFG::kStgOff + (warp - 2) * 8192);
+    st.buf = 0;
+    st.fill = 0;
+    uint32_t it = 0;
+    for (int tile = pair0; tile < total_tiles; tile += npairs, ++it) {
+      const int z = tile / tiles_mn;
+      const int rem = tile - z * tiles_mn;
+      const int mt = (rem / p.ntn) * 2 + (int)rank;     // 128-row tile index inside the batch entry
+      const int m0 = mt * 128;
+      const int n0 = (rem % p.ntn) * BN;
+      const int b = z / p.HB;
+      const int h = z - b * p.HB;
+      const uint32_t as = it & 1;
+      const int row0 = m0 + q * 32;
+      const int row = row0 + lane;
+      const bool row_ok = row < p.M;
+      float mk = 1.0f;
+      if (p.rowmask != nullptr && row_ok)
+        mk = p.rowmask[(long long)b * p.mask_bstride + (long long)row * p.mask_step + p.mask_off] ? 1.0f : 0.0f;
+      float* red = gn_red + as * (4 * NG * 2);
+      mbar_wait(&tfull_bar[as], (it >> 1) & 1);
+      tc_fence_after();
+      float gs = 0.f, gss = 0.f;
+#pragma unroll 1
+      for (int cc = 0; cc < NCH / 2; ++cc) {
+        const int c = sub * (NCH / 2) + cc;
+        const int nc = n0 + c * 32;
+        if (nc >= p.N) break;                  // warp-uniform
+        uint32_t raw[32];
+        tmem_ld_32x32b_x32(tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN + c * 32), raw);
+        tmem_ld_wait();
+        float v[32];
+        const bool full_chunk = nc + 32 <= p.N;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float bi = 0.f;
+          if (p.bias != nullptr && (full_chunk || nc + i < p.N)) bi = __ldg(p.bias + nc + i);
+          v[i] = __uint_as_float(raw[i]) * p.alpha + bi;
+        }
+        epilogue_chunk<OT>(p, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss);
+        if (p.gn_part != nullptr && (c & 1)) {   // a 64-channel group is complete
+          const float s = warp_sum_f(gs), ss = warp_sum_f(gss);
+          if (lane == 0) {
+            red[(q * NG + (c >> 1)) * 2 + 0] = s;
+            red[(q * NG + (c >> 1)) * 2 + 1] = ss;
+          }
+          gs = 0.f; gss = 0.f;
+        }
+      }
+      // release the accumulator stage to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(map_to_cta(&tempty_bar[as], 0));
+      if (p.gn_part != nullptr) {
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps only
+        const int t = threadIdx.x - 64;
+        if (t < NG * 2) {
+          const int g = t >> 1, w = t & 1;
+          const float s = red[(0 * NG + g) * 2 + w] + red[(1 * NG + g) * 2 + w] + red[(2 * NG + g) * 2 + w] +
+                          red[(3 * NG + g) * 2 + w];
+          const int group = (n0 >> 6) + g;
+          p.gn_part[(((long long)b * (2 * p.ntm) + mt) * 8 + group) * 2 + w] = s;
+        }
+      }
+    }
+    if (lane == 0) tma_store_wait_all();     // smem boxes must outlive their bulk stores
+  }
+  __syncwarp();
+  tc_fence_before();
+  cluster_sync_all();        // the peer may still be reading this CTA's smem / signalling its barriers
+  if (warp == 2) tmem_dealloc_2sm<CFG::kTmemCols>(tmem_base);
+}
+
+}  // namespace srn
