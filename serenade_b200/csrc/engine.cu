@@ -7,12 +7,28 @@
 
 namespace srn {
 
+template <typename OT, int BN, int EPI>
+static void configure_one() {
+  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                GemmCfg<BN>::kSmemBytes));
+  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
+}
+
+template <typename OT, int BN>
+static void configure_bn() {
+  configure_one<OT, BN, EPI_STORE_F32>();
+  configure_one<OT, BN, EPI_STORE_OT>();
+  configure_one<OT, BN, EPI_RESID_F32>();
+  configure_one<OT, BN, EPI_RESID_OT>();
+  configure_one<OT, BN, EPI_GEGLU>();
+  configure_one<OT, BN, EPI_QKV>();
+  configure_one<OT, BN, EPI_EULER>();
+}
+
 template <typename OT>
 static void configure_kernels() {
-  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                GemmCfg<128>::kSmemBytes));
-  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                GemmCfg<256>::kSmemBytes));
+  configure_bn<OT, 128>();
+  configure_bn<OT, 256>();
 }
 
 std::unique_ptr<EngineBase> make_engine(const SrnConfig& cfg) {

@@ -4,10 +4,8 @@ namespace srn {
 static inline float to_f_host(float v) { return v; }
 static inline float to_f_host(__nv_bfloat16 v) { return __bfloat162float(v); }
 
-template <typename OT, int BN>
+template <typename OT, int BN, int EPI>
 static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t st) {
-  static const int dbg_mode = getenv("SRN_GEMM_DBG") ? atoi(getenv("SRN_GEMM_DBG")) : 0;
-  gp.dbg_mode = dbg_mode;
   gp.ntn = (int)grid.x;
   gp.ntm = (int)grid.y;
   gp.nz = (int)grid.z;
@@ -26,14 +24,28 @@ static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t
   attr.val.clusterDim.z = 1;
   cfg.attrs = &attr;
   cfg.numAttrs = 1;
-  SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, BN>, gp));
+  SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, BN, EPI>, gp));
+}
+
+template <typename OT, int BN>
+static void launch_gemm_bn(const GemmParams& gp, dim3 grid, int num_sms, cudaStream_t st) {
+  switch (gp.epi) {
+    case EPI_STORE_F32: launch_gemm_impl<OT, BN, EPI_STORE_F32>(gp, grid, num_sms, st); break;
+    case EPI_STORE_OT: launch_gemm_impl<OT, BN, EPI_STORE_OT>(gp, grid, num_sms, st); break;
+    case EPI_RESID_F32: launch_gemm_impl<OT, BN, EPI_RESID_F32>(gp, grid, num_sms, st); break;
+    case EPI_RESID_OT: launch_gemm_impl<OT, BN, EPI_RESID_OT>(gp, grid, num_sms, st); break;
+    case EPI_GEGLU: launch_gemm_impl<OT, BN, EPI_GEGLU>(gp, grid, num_sms, st); break;
+    case EPI_QKV: launch_gemm_impl<OT, BN, EPI_QKV>(gp, grid, num_sms, st); break;
+    case EPI_EULER: launch_gemm_impl<OT, BN, EPI_EULER>(gp, grid, num_sms, st); break;
+    default: fail("unknown GEMM epilogue %d", gp.epi);
+  }
 }
 
 template <typename OT>
 void Engine<OT>::launch_gemm(const GemmParams& gp, int bn, dim3 grid, cudaStream_t st) {
   if (gp.nkb < 1 || gp.nseg < 1) fail("gemm with empty K");
-  if (bn == 256) launch_gemm_impl<OT, 256>(gp, grid, num_sms_, st);
-  else launch_gemm_impl<OT, 128>(gp, grid, num_sms_, st);
+  if (bn == 256) launch_gemm_bn<OT, 256>(gp, grid, num_sms_, st);
+  else launch_gemm_bn<OT, 128>(gp, grid, num_sms_, st);
   ++launches;
 }
 

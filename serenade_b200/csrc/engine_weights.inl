@@ -209,7 +209,11 @@ void Engine<OT>::finalize_weights() {
   final_g_ = up_f32(hw("final_block.block.1.weight", {C}).data);
   final_be_ = up_f32(hw("final_block.block.1.bias", {C}).data);
   proj_w_ = up_ot(hw("final_proj.weight", {cfg_.out_channels, C, 1}).data);
-  proj_b_ = up_f32(hw("final_proj.bias", {cfg_.out_channels}).data);
+  {
+    std::vector<float> pb = hw("final_proj.bias", {cfg_.out_channels}).data;
+    pb.resize(128, 0.f);          // the epilogue reads bias in whole 32-column chunks
+    proj_b_ = up_f32(pb);
+  }
   const size_t expected = 4 + resnets_.size() * 16 + tfms_.size() * 13 + 4 * 2 + 4 + 2;
   if (host_w_.size() != expected)
     fail("state dict has %zu tensors, the decoder expects %zu (unexpected extra keys?)", host_w_.size(), expected);

@@ -8,6 +8,8 @@
 //   warp 1      tcgen05.mma issuer (leader CTA, one elected lane), two TMEM accumulator stages
 //   warps 2..9  epilogue: TMEM -> registers -> fused epilogue -> swizzled smem box -> TMA store, overlapped
 //               with the next tile's main loop through the tmem_full / tmem_empty barriers
+// The epilogue mode is a template parameter: ncu showed the epilogue warps latency-bound on ~520 instructions
+// per 32-column chunk when the mode was a runtime switch with per-element predicates.
 #pragma once
 
 #include "gemm_epilogue.cuh"
@@ -29,84 +31,78 @@ struct GemmCfg {
   static_assert(kStgOff % 1024 == 0, "staging boxes must be 1024-byte aligned for SWIZZLE_128B");
 };
 
-// One 32-column chunk of one accumulator row: bias/alpha were already applied to v.
-template <typename OT>
+// One 32-column chunk of one accumulator row (bias / alpha already applied to v).
+template <typename OT, int EPI>
 __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[32], Stager& st, int lane, int b, int h,
                                                int z, int row, int row0, int nc, bool row_ok, float mk, float& gs,
                                                float& gss) {
   const int batch = p.d_zbatch ? z : b;
-  switch (p.epi) {
-    case EPI_STORE_F32: {
-      if (p.gn_part != nullptr && row_ok) {
+  constexpr int kOtCols = 128 / (int)sizeof(OT);     // output columns per 128-byte staging row
+  if constexpr (EPI == EPI_STORE_F32) {
+    if (p.gn_part != nullptr && row_ok) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) { gs += v[i]; gss += v[i] * v[i]; }
+      for (int i = 0; i < 32; ++i) { gs += v[i]; gss = fmaf(v[i], v[i], gss); }
+    }
+    stager_acquire(st, lane);
+    stager_put<float, 32>(st, lane, v);
+    stager_flush(st, lane, &p.mapD, nc + h * p.d_hcol, row0, batch);
+  } else if constexpr (EPI == EPI_STORE_OT) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] *= mk;
+    stager_acquire(st, lane);
+    stager_put<OT, 32>(st, lane, v);
+    stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols + h * p.d_hcol, row0, batch);
+  } else if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_RESID_OT) {
+    if (row_ok) {
+      const float4* rs = reinterpret_cast<const float4*>(p.resid + b * p.resid_bstride + (long long)row * p.ldr + nc);
+      float4 r4[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) r4[i] = rs[i];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        v[4 * i + 0] += r4[i].x; v[4 * i + 1] += r4[i].y; v[4 * i + 2] += r4[i].z; v[4 * i + 3] += r4[i].w;
       }
-      stager_acquire(st, lane);
+    }
+    stager_acquire(st, lane);
+    if constexpr (EPI == EPI_RESID_F32) {
       stager_put<float, 32>(st, lane, v);
-      stager_flush(st, lane, &p.mapD, nc + h * p.d_hcol, row0, batch);
-    } break;
-    case EPI_STORE_OT: {
+      stager_flush(st, lane, &p.mapD, nc, row0, batch);
+    } else {
 #pragma unroll
       for (int i = 0; i < 32; ++i) v[i] *= mk;
+      stager_put<OT, 32>(st, lane, v);
+      stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols, row0, batch);
+    }
+  } else if constexpr (EPI == EPI_GEGLU) {
+    float o[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) o[i] = v[2 * i] * gelu_erf(v[2 * i + 1]);
+    stager_acquire(st, lane);
+    stager_put<OT, 16>(st, lane, o);
+    stager_flush(st, lane, &p.mapD, (nc >> 1) + 16 - kOtCols, row0, batch);
+  } else if constexpr (EPI == EPI_QKV) {
+    if (nc < p.split_n) {
       stager_acquire(st, lane);
       stager_put<OT, 32>(st, lane, v);
-      stager_flush(st, lane, &p.mapD, nc + 32 - 128 / (int)sizeof(OT) + h * p.d_hcol, row0, batch);
-    } break;
-    case EPI_RESID_F32:
-    case EPI_RESID_OT: {
-      if (row_ok) {
-        const float* rs = p.resid + b * p.resid_bstride + (long long)row * p.ldr + nc;
+      stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols, row0, batch);
+    } else {
+      stager_store_transposed<OT>(st, lane, v, &p.mapD2, row0, nc - p.split_n, batch);
+    }
+  } else if constexpr (EPI == EPI_EULER) {
+    if (row_ok) {
+      const long long base = ((long long)b * p.N + nc) * p.T_cf + row;
+      const float dt = p.dt_ptr != nullptr ? __ldg(p.dt_ptr) : p.dt;
+      const bool blend = p.blend_mask != nullptr && p.blend_mask[(long long)b * p.T_cf + row] != 0;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float4 r4 = reinterpret_cast<const float4*>(rs)[i];
-          v[4 * i + 0] += r4.x; v[4 * i + 1] += r4.y; v[4 * i + 2] += r4.z; v[4 * i + 3] += r4.w;
+      for (int i = 0; i < 32; ++i) {
+        if (nc + i < p.N) {
+          const float vv = v[i] * mk;
+          const long long idx = base + (long long)i * p.T_cf;
+          if (p.v_out != nullptr) p.v_out[idx] = vv;
+          if (p.x_out != nullptr) p.x_out[idx] = blend ? p.blend_src[idx] : p.x_in[idx] + dt * vv;
         }
       }
-      stager_acquire(st, lane);
-      if (p.epi == EPI_RESID_F32) {
-        stager_put<float, 32>(st, lane, v);
-        stager_flush(st, lane, &p.mapD, nc, row0, batch);
-      } else {
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] *= mk;
-        stager_put<OT, 32>(st, lane, v);
-        stager_flush(st, lane, &p.mapD, nc + 32 - 128 / (int)sizeof(OT), row0, batch);
-      }
-    } break;
-    case EPI_GEGLU: {
-      float o[16];
-#pragma unroll
-      for (int i = 0; i < 16; ++i) o[i] = v[2 * i] * gelu_erf(v[2 * i + 1]);
-      stager_acquire(st, lane);
-      stager_put<OT, 16>(st, lane, o);
-      stager_flush(st, lane, &p.mapD, (nc >> 1) + 16 - 128 / (int)sizeof(OT), row0, batch);
-    } break;
-    case EPI_QKV: {
-      if (nc < p.split_n) {
-        stager_acquire(st, lane);
-        stager_put<OT, 32>(st, lane, v);
-        stager_flush(st, lane, &p.mapD, nc + 32 - 128 / (int)sizeof(OT), row0, batch);
-      } else {
-        stager_store_transposed<OT>(st, lane, v, &p.mapD2, row0, nc - p.split_n, batch);
-      }
-    } break;
-    case EPI_EULER: {
-      if (row_ok) {
-        const long long base = ((long long)b * p.N + nc) * p.T_cf + row;
-        const float dt = p.dt_ptr != nullptr ? __ldg(p.dt_ptr) : p.dt;
-        const bool blend = p.blend_mask != nullptr && p.blend_mask[(long long)b * p.T_cf + row] != 0;
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          if (nc + i < p.N) {
-            const float vv = v[i] * mk;
-            const long long idx = base + (long long)i * p.T_cf;
-            if (p.v_out != nullptr) p.v_out[idx] = vv;
-            if (p.x_out != nullptr) p.x_out[idx] = blend ? p.blend_src[idx] : p.x_in[idx] + dt * vv;
-          }
-        }
-      }
-    } break;
-    default: break;
+    }
   }
 }
 

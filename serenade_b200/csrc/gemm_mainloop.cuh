@@ -3,7 +3,7 @@
 
 namespace srn {
 
-template <typename OT, int BN>
+template <typename OT, int BN, int EPI>
 __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
   using TR = OpTraits<OT>;
   using CFG = GemmCfg<BN>;
@@ -74,13 +74,9 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           // both CTAs' bytes complete on the LEADER's full barrier; only the leader arms it (for both)
           const uint32_t fb = map_to_cta(&full_bar[stage], 0);
           const KSeg sg = p.seg[seg];
-          if (p.dbg_mode == 1) {
-            if (rank == 0) mbar_arrive(&full_bar[stage]);
-          } else {
-            if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * CFG::kStageBytes);
-            tma_load_3d_2sm(sa, &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol, m0 + sg.shift, a_batch);
-            tma_load_3d_2sm(sb, &p.mapB, fb, p.b_col0 + kb * BK + h * p.b_hcol, b_row, b_batch);
-          }
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * CFG::kStageBytes);
+          tma_load_3d_2sm(sa, &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol, m0 + sg.shift, a_batch);
+          tma_load_3d_2sm(sb, &p.mapB, fb, p.b_col0 + kb * BK + h * p.b_hcol, b_row, b_batch);
           if (++j == sg.nblk) { j = 0; ++seg; }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -105,7 +101,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           const uint64_t db = make_kmajor_sw128_desc(sa + CFG::kABytes);
 #pragma unroll
           for (int k = 0; k < 4; ++k)   // 4 x 32 bytes of K per 128-byte swizzled row
-            if (p.dbg_mode != 2) umma_pair<TR::kTF32>(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            umma_pair<TR::kTF32>(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
           tc_commit_pair(&empty_bar[stage]);     // frees the stage in both CTAs
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -120,6 +116,9 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     st.base = smem_u32(smem + CFG::kStgOff + (warp - 2) * 8192);
     st.buf = 0;
     st.fill = 0;
+    const bool has_bias = p.bias != nullptr;
+    const bool has_alpha = p.alpha != 1.0f;
+    const uint32_t tepi_addr = map_to_cta(&tempty_bar[0], 0);
     uint32_t it = 0;
     for (int tile = pair0; tile < total_tiles; tile += npairs, ++it) {
       const int z = tile / tiles_mn;
@@ -137,48 +136,69 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       if (p.rowmask != nullptr && row_ok)
         mk = p.rowmask[(long long)b * p.mask_bstride + (long long)row * p.mask_step + p.mask_off] ? 1.0f : 0.0f;
       float* red = gn_red + as * (4 * NG * 2);
+      const int c_first = sub * (NCH / 2);
+      int nvalid = (p.N - (n0 + c_first * 32) + 31) / 32;     // chunks of this warp that start inside N
+      nvalid = nvalid < 0 ? 0 : (nvalid > NCH / 2 ? NCH / 2 : nvalid);
+      const uint32_t trow = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN + c_first * 32);
       mbar_wait(&tfull_bar[as], (it >> 1) & 1);
       tc_fence_after();
       float gs = 0.f, gss = 0.f;
+      uint32_t raw[32];
+      if (nvalid > 0) tmem_ld_32x32b_x32(trow, raw);
 #pragma unroll 1
-      for (int cc = 0; cc < NCH / 2; ++cc) {
-        const int c = sub * (NCH / 2) + cc;
+      for (int cc = 0; cc < nvalid; ++cc) {
+        const int c = c_first + cc;
         const int nc = n0 + c * 32;
-        if (nc >= p.N) break;                  // warp-uniform
-        uint32_t raw[32];
-        tmem_ld_32x32b_x32(tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN + c * 32), raw);
         tmem_ld_wait();
         float v[32];
-        const bool full_chunk = nc + 32 <= p.N;
+        if (has_bias) {
+          const float4* b4 = reinterpret_cast<const float4*>(p.bias + nc);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float bi = 0.f;
-          if (p.bias != nullptr && (full_chunk || nc + i < p.N)) bi = __ldg(p.bias + nc + i);
-          v[i] = __uint_as_float(raw[i]) * p.alpha + bi;
-        }
-        epilogue_chunk<OT>(p, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss);
-        if (p.gn_part != nullptr && (c & 1)) {   // a 64-channel group is complete
-          const float s = warp_sum_f(gs), ss = warp_sum_f(gss);
-          if (lane == 0) {
-            red[(q * NG + (c >> 1)) * 2 + 0] = s;
-            red[(q * NG + (c >> 1)) * 2 + 1] = ss;
+          for (int i = 0; i < 8; ++i) {
+            const float4 bb = __ldg(b4 + i);
+            v[4 * i + 0] = __uint_as_float(raw[4 * i + 0]) + bb.x;
+            v[4 * i + 1] = __uint_as_float(raw[4 * i + 1]) + bb.y;
+            v[4 * i + 2] = __uint_as_float(raw[4 * i + 2]) + bb.z;
+            v[4 * i + 3] = __uint_as_float(raw[4 * i + 3]) + bb.w;
           }
-          gs = 0.f; gss = 0.f;
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
+        }
+        if (cc + 1 < nvalid) tmem_ld_32x32b_x32(trow + (cc + 1) * 32, raw);   // overlaps with this chunk's epilogue
+        if constexpr (EPI == EPI_STORE_F32) {
+          if (has_alpha) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] *= p.alpha;
+          }
+        }
+        epilogue_chunk<OT, EPI>(p, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss);
+        if constexpr (EPI == EPI_STORE_F32) {
+          if (p.gn_part != nullptr && (c & 1)) {   // a 64-channel group is complete
+            const float s = warp_sum_f(gs), ss = warp_sum_f(gss);
+            if (lane == 0) {
+              red[(q * NG + (c >> 1)) * 2 + 0] = s;
+              red[(q * NG + (c >> 1)) * 2 + 1] = ss;
+            }
+            gs = 0.f; gss = 0.f;
+          }
         }
       }
       // release the accumulator stage to the MMA warp
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(map_to_cta(&tempty_bar[as], 0));
-      if (p.gn_part != nullptr) {
-        asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps only
-        const int t = threadIdx.x - 64;
-        if (t < NG * 2) {
-          const int g = t >> 1, w = t & 1;
-          const float s = red[(0 * NG + g) * 2 + w] + red[(1 * NG + g) * 2 + w] + red[(2 * NG + g) * 2 + w] +
-                          red[(3 * NG + g) * 2 + w];
-          const int group = (n0 >> 6) + g;
-          p.gn_part[(((long long)b * (2 * p.ntm) + mt) * 8 + group) * 2 + w] = s;
+      if (lane == 0) mbar_arrive_cluster(tepi_addr + as * 8);
+      if constexpr (EPI == EPI_STORE_F32) {
+        if (p.gn_part != nullptr) {
+          asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps only
+          const int t = threadIdx.x - 64;
+          if (t < NG * 2) {
+            const int g = t >> 1, w = t & 1;
+            const float s = red[(0 * NG + g) * 2 + w] + red[(1 * NG + g) * 2 + w] + red[(2 * NG + g) * 2 + w] +
+                            red[(3 * NG + g) * 2 + w];
+            const int group = (n0 >> 6) + g;
+            p.gn_part[(((long long)b * (2 * p.ntm) + mt) * 8 + group) * 2 + w] = s;
+          }
         }
       }
     }

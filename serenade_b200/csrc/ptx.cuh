@@ -179,7 +179,10 @@ __device__ __forceinline__ uint32_t map_to_cta(const void* p, uint32_t rank) {
   return out;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  // default semantics (as CUTLASS ClusterBarrier::arrive): the explicit .release.cluster form compiled to
+  // MEMBAR.ALL + ERRBAR, the single hottest stall of the epilogue in ncu; TMEM reads are ordered by
+  // tcgen05.wait::ld + tcgen05.fence::before_thread_sync before this arrive.
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load issued by either CTA of a pair; the transaction bytes complete on the barrier at `bar_cluster_addr`
 // (a shared::cluster address, normally the leader CTA's full barrier).
