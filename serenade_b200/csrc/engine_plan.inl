@@ -57,9 +57,13 @@ inline void add_seg(GemmParams& gp, int src, int col0, int shift, int nblk) {
 }
 // row_tiles = number of 256-row pair tiles; one CTA pair per SM pair (74 on a B200)
 inline int pick_bn(int N, long long row_tiles) {
-  const long long nt256 = (N + 255) / 256;
+  const long long nt256 = (N + 255) / 256, nt128 = (N + 127) / 128;
   const bool little_waste = nt256 * 256 * 10 <= (long long)N * 11;
-  return (little_waste && nt256 * row_tiles >= 74) ? 256 : 128;
+  if (!little_waste) return 128;
+  // waves x relative cost of one tile (a 256 x 128 tile costs a bit more than half a 256 x 256 one)
+  const double c256 = (double)((nt256 * row_tiles + 73) / 74) * 1.0;
+  const double c128 = (double)((nt128 * row_tiles + 73) / 74) * 0.58;
+  return c256 <= c128 ? 256 : 128;
 }
 }  // namespace
 

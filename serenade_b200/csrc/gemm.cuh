@@ -105,7 +105,18 @@ __device__ __forceinline__ float warp_sum_f(float v) {
   return v;
 }
 
-__device__ __forceinline__ float gelu_erf(float g) { return 0.5f * g * (1.0f + erff(g * 0.70710678118654752440f)); }
+// Exact-erf GELU (diffusers GEGLU uses F.gelu, erf form).  erf by Abramowitz-Stegun 7.1.26 (|abs err| <= 1.5e-7):
+// the GEGLU epilogue runs 16 of these per 32-column chunk and was instruction-bound on erff.
+__device__ __forceinline__ float gelu_erf(float g) {
+  const float x = fabsf(g) * 0.70710678118654752440f;
+  const float t = __fdividef(1.0f, fmaf(0.3275911f, x, 1.0f));
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float e = 1.0f - poly * t * __expf(-x * x);      // erf(|g| / sqrt 2)
+  return 0.5f * g * (1.0f + copysignf(e, g));
+}
 
 template <typename OT>
 __device__ __forceinline__ void store_row32(OT* dst, const float (&v)[32]);

@@ -17,9 +17,12 @@ constexpr int kC = 512;         // hidden width of the ssc1 decoder
 constexpr int kGroups = 8;      // GroupNorm groups (decoder.py:67)
 
 __device__ __forceinline__ float mish_f(float x) {
-  // x * tanh(softplus(x)), softplus threshold 20 as in torch
-  const float sp = x > 20.f ? x : log1pf(expf(x));
-  return x * tanhf(sp);
+  // x * tanh(softplus(x)) with w = e^x: tanh(ln(1 + w)) = (w^2 + 2w) / (w^2 + 2w + 2)  -- one exp and one
+  // division instead of expf + log1pf + tanhf (the row kernels were instruction-bound on those, not HBM-bound).
+  // x > 20: tanh(softplus(x)) == 1 in fp32 (torch's softplus threshold); x << 0: n -> 2w keeps full relative precision.
+  const float w = __expf(fminf(x, 20.f));
+  const float n = w * (w + 2.0f);
+  return x > 20.f ? x : x * __fdividef(n, n + 2.0f);
 }
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
 
@@ -138,6 +141,7 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__
   for (int i = 0; i < 8; ++i) { ga[i] *= rstd; be[i] -= mean * ga[i]; }
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(r0 + rows_per_block, T);
+#pragma unroll 4
   for (int r = r0 + (threadIdx.x >> 6); r < r1; r += 4) {
     const long long off = b * bstride + (long long)r * kC + c;
     const float m = mask[(long long)b * mask_bstride + (long long)r * mask_step] ? 1.f : 0.f;
@@ -171,6 +175,7 @@ __global__ void __launch_bounds__(256) gn_res_spk_ln(const float* __restrict__ y
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(r0 + rows_per_block, T);
+#pragma unroll 2
   for (int r = r0 + warp; r < r1; r += 8) {
     const long long rowoff = b * bstride + (long long)r * kC;
     const float m = mask[(long long)b * mask_bstride + (long long)r * mask_step] ? 1.f : 0.f;
