@@ -175,7 +175,6 @@ __global__ void __launch_bounds__(256) gn_res_spk_ln(const float* __restrict__ y
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(r0 + rows_per_block, T);
-#pragma unroll 2
   for (int r = r0 + warp; r < r1; r += 8) {
     const long long rowoff = b * bstride + (long long)r * kC;
     const float m = mask[(long long)b * mask_bstride + (long long)r * mask_step] ? 1.f : 0.f;
