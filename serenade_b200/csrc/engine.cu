@@ -23,6 +23,9 @@ static void configure_bn() {
   configure_one<OT, BN, EPI_GEGLU>();
   configure_one<OT, BN, EPI_QKV>();
   configure_one<OT, BN, EPI_EULER>();
+  configure_one<OT, BN, EPI_ROWMAX>();
+  configure_one<OT, BN, EPI_EXP>();
+  configure_one<OT, BN, EPI_PV>();
 }
 
 template <typename OT>

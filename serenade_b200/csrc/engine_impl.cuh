@@ -40,7 +40,7 @@ struct ConvW {
   float* b = nullptr;
 };
 
-enum OpKind : int { OP_GEMM, OP_PACKX, OP_GN_APPLY, OP_GN_RES_SPK_LN, OP_LAYERNORM, OP_SOFTMAX };
+enum OpKind : int { OP_GEMM, OP_PACKX, OP_GN_APPLY, OP_GN_RES_SPK_LN, OP_LAYERNORM };
 
 struct Tap {
   const char* name = nullptr;   // debug tensor name (null = none)
@@ -88,7 +88,7 @@ template <typename OT>
 struct Plan {
   int B = 0, T = 0, Tp = 0;
   Level lv[2];
-  DevBuf xin, y, r, gnpart, a1, hres, ln, qk, vt, sc, P, ao, gg, hid0, hid1, hc, cv;
+  DevBuf xin, y, r, gnpart, a1, hres, ln, qk, vt, smax, ssum, P, ao, gg, hid0, hid1, hc, cv;
   DevBuf x_state, mask, spk_in, mu_in, spk_scale, spk_bias, tsteps, dts, temb0, temb1, temb2, tb;
   DevBuf blend_mask, blend_src;
   int tb_steps = 0;

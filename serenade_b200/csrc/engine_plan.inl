@@ -155,7 +155,6 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
   OT* P = pl.P.template as<OT>();
   OT* ao = pl.ao.template as<OT>();
   OT* gg = pl.gg.template as<OT>();
-  float* sc = pl.sc.template as<float>();
   float* hres = pl.hres.template as<float>();
   auto push = [&](Op& op, const char* nm) {
     op.kind = OP_GEMM;
@@ -186,11 +185,19 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     op.tap = Tap{"qk", qk, 1, S, 4096, 4096, gp.out_bstride, B, 0};
     push(op, "qkv");
   }
-  {  // scores[b,h] = Q K^T / sqrt(d)
+  // Attention without a score matrix in HBM.  Q K^T runs twice on the tensor cores: pass 1 keeps only per-row
+  // maxima (key-masked), pass 2 recomputes the tile, writes P~ = exp(s - rowmax) in operand precision and partial
+  // row sums; P~ V then divides by the row sum in its epilogue.  Replaces scores f32 write + read and the softmax
+  // kernel (12 B per score) by 2 + 2 B per score; 1/sqrt(d), the key mask and the normalisation follow
+  // F.scaled_dot_product_attention with a boolean key mask.
+  const int sc_bn = pick_bn(S, tiles * H);
+  const int stat_n = cdiv(S, 64);          // one (max, sum) partial per row per 64-key slice
+  if ((size_t)B * H * stat_n * L.Sp * 4 > pl.smax.bytes) fail("softmax statistics buffer too small");
+  for (int pass = 0; pass < 2; ++pass) {
     Op op;
     op.gp = base_gemm(pl, level);
     GemmParams& gp = op.gp;
-    op.bn = pick_bn(S, tiles * H);
+    op.bn = sc_bn;
     gp.HB = H;
     set_A<OT>(gp, 0, qk, 4096, S, L.R, 4096, B);
     gp.a_hcol = 512;
@@ -200,27 +207,27 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.b_hcol = 512;
     gp.b_batch_mode = 1;
     gp.N = S;
-    gp.epi = EPI_STORE_F32;
+    gp.epi = pass == 0 ? EPI_ROWMAX : EPI_EXP;
     gp.alpha = 1.0f / sqrtf(512.0f);
-    gp.out = sc;
+    gp.stat_max = pl.smax.template as<float>();
+    gp.stat_sum = pl.ssum.template as<float>();
+    gp.stat_n = stat_n;
+    gp.stat_ld = L.Sp;
+    gp.keymask = pl.mask.template as<uint8_t>();
+    gp.keymask_bstride = pl.Tp;
+    gp.keymask_step = L.mask_step;
+    gp.out = P;
     gp.out_bstride = (long long)H * S * Sp;
     gp.out_hstride = (long long)S * Sp;
     gp.ldo = Sp;
-    set_D<float>(gp, sc, S, S, (long long)S * Sp, Sp, B * H);
+    if (pass == 0) gp.mapD = gp.mapA[0];      // no tensor output; keeps the descriptor prefetch valid
+    else set_D<OT>(gp, P, S, S, (long long)S * Sp, Sp, B * H);
     gp.d_zbatch = 1;
     op.grid = dim3(cdiv(S, op.bn), L.mtiles, B * H);
-    op.tap = Tap{"sc", sc, 0, S, S, Sp, (long long)S * Sp, B * H, 0};
-    push(op, "scores");
+    if (pass == 1) op.tap = Tap{"P", P, 1, S, S, Sp, (long long)S * Sp, B * H, 0};
+    push(op, pass == 0 ? "rowmax" : "expscores");
   }
-  {
-    Op op;
-    op.kind = OP_SOFTMAX;
-    op.name = tag + ".softmax";
-    op.level = level;
-    op.tap = Tap{"P", P, 1, S, S, Sp, (long long)S * Sp, B * H, 0};
-    pl.ops.push_back(op);
-  }
-  {  // O[b, :, h*512:(h+1)*512] = P[b,h] V[b,h]
+  {  // O[b, :, h*512:(h+1)*512] = (P~[b,h] V[b,h]) / rowsum
     Op op;
     op.gp = base_gemm(pl, level);
     GemmParams& gp = op.gp;
@@ -234,7 +241,10 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.b_hrow = 512;
     gp.b_batch_mode = 1;
     gp.N = 512;
-    gp.epi = EPI_STORE_OT;
+    gp.epi = EPI_PV;
+    gp.stat_sum = pl.ssum.template as<float>();
+    gp.stat_n = stat_n;
+    gp.stat_ld = L.Sp;
     gp.out = ao;
     gp.out_bstride = (long long)L.R * 2048;
     gp.out_hstride = 512;
@@ -341,7 +351,11 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
   pl.ln.alloc(rows * C * es);
   pl.qk.alloc(rows * 4096 * es);
   pl.vt.alloc((size_t)B * 2048 * pl.lv[0].Sp * es);
-  pl.sc.alloc((size_t)B * H * T * pl.lv[0].Sp * 4);
+  {  // softmax statistics: one (max, sum) partial per row per 128-column (or 64-column) slice of the score GEMM
+    const size_t n128 = 2 * (size_t)cdiv(T, 128);
+    pl.smax.alloc((size_t)B * H * n128 * pl.lv[0].Sp * 4);
+    pl.ssum.alloc((size_t)B * H * n128 * pl.lv[0].Sp * 4);
+  }
   pl.P.alloc((size_t)B * H * T * pl.lv[0].Sp * es);
   pl.ao.alloc(rows * 2048 * es);
   pl.gg.alloc(rows * 2048 * es);

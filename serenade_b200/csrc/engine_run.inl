@@ -4,6 +4,31 @@ namespace srn {
 static inline float to_f_host(float v) { return v; }
 static inline float to_f_host(__nv_bfloat16 v) { return __bfloat162float(v); }
 
+// Every kernel is launched with programmatic stream serialization (see ptx.cuh: pdl_wait): the next kernel's
+// launch latency and prologue hide under this kernel's tail, also inside the captured CUDA graph.
+static bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("SRN_DISABLE_PDL");
+    return !(e != nullptr && e[0] == '1');
+  }();
+  return on;
+}
+
+template <typename... KArgs, typename... Args>
+static void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof cfg);
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.stream = st;
+  cudaLaunchAttribute attr;
+  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr.val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  SRN_CUDA(cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...));
+}
+
 template <typename OT, int BN, int EPI>
 static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t st) {
   gp.ntn = (int)grid.x;
@@ -17,13 +42,15 @@ static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t
   cfg.blockDim = dim3(GemmCfg<BN>::kThreads);
   cfg.dynamicSmemBytes = GemmCfg<BN>::kSmemBytes;
   cfg.stream = st;
-  cudaLaunchAttribute attr;
-  attr.id = cudaLaunchAttributeClusterDimension;
-  attr.val.clusterDim.x = 2;
-  attr.val.clusterDim.y = 1;
-  attr.val.clusterDim.z = 1;
-  cfg.attrs = &attr;
-  cfg.numAttrs = 1;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, BN, EPI>, gp));
 }
 
@@ -37,6 +64,9 @@ static void launch_gemm_bn(const GemmParams& gp, dim3 grid, int num_sms, cudaStr
     case EPI_GEGLU: launch_gemm_impl<OT, BN, EPI_GEGLU>(gp, grid, num_sms, st); break;
     case EPI_QKV: launch_gemm_impl<OT, BN, EPI_QKV>(gp, grid, num_sms, st); break;
     case EPI_EULER: launch_gemm_impl<OT, BN, EPI_EULER>(gp, grid, num_sms, st); break;
+    case EPI_ROWMAX: launch_gemm_impl<OT, BN, EPI_ROWMAX>(gp, grid, num_sms, st); break;
+    case EPI_EXP: launch_gemm_impl<OT, BN, EPI_EXP>(gp, grid, num_sms, st); break;
+    case EPI_PV: launch_gemm_impl<OT, BN, EPI_PV>(gp, grid, num_sms, st); break;
     default: fail("unknown GEMM epilogue %d", gp.epi);
   }
 }
@@ -98,51 +128,30 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
     } break;
     case OP_PACKX: {
       dim3 grid(cdiv(pl.T, 32), cdiv(cfg_.out_channels, 32), B);
-      pack_cf_to_cl<OT><<<grid, dim3(32, 8), 0, st>>>(pl.x_state.template as<float>(), cfg_.out_channels, pl.T, mask, pl.Tp,
-                                                      pl.xin.template as<OT>(), (long long)pl.Tp * 256, 256, 0);
-      SRN_CUDA(cudaGetLastError());
+      launch_k(pack_cf_to_cl<OT>, grid, dim3(32, 8), st, pl.x_state.template as<float>(), cfg_.out_channels, pl.T, mask,
+               pl.Tp, pl.xin.template as<OT>(), (long long)pl.Tp * 256, 256, 0);
       ++launches;
     } break;
     case OP_GN_APPLY: {
       const float* tb = op.use_tbias ? pl.tb.template as<float>() + ((size_t)op.resnet_idx * pl.tb_steps + step) * 512
                                      : nullptr;
       dim3 grid(cdiv(L.T, 32), B);
-      gn_apply_kernel<OT><<<grid, 256, 0, st>>>(op.y, op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma, op.beta,
-                                                tb, mask, pl.Tp, L.mask_step, static_cast<OT*>(op.out), 32);
-      SRN_CUDA(cudaGetLastError());
+      launch_k(gn_apply_kernel<OT>, grid, dim3(256), st, op.y, op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma,
+               op.beta, tb, mask, pl.Tp, L.mask_step, static_cast<OT*>(op.out), 32);
       ++launches;
     } break;
     case OP_GN_RES_SPK_LN: {
       dim3 grid(cdiv(L.T, 32), B);
       const float* sc = pl.spk_scale.template as<float>() + (size_t)op.resnet_idx * B * 512;
       const float* sb = pl.spk_bias.template as<float>() + (size_t)op.resnet_idx * B * 512;
-      gn_res_spk_ln<OT><<<grid, 256, 0, st>>>(op.y, op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma, op.beta,
-                                              op.res, mask, pl.Tp, L.mask_step, sc, sb, op.ln_g, op.ln_b, op.hres,
-                                              static_cast<OT*>(op.out), 32);
-      SRN_CUDA(cudaGetLastError());
+      launch_k(gn_res_spk_ln<OT>, grid, dim3(256), st, op.y, op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma,
+               op.beta, op.res, mask, pl.Tp, L.mask_step, sc, sb, op.ln_g, op.ln_b, op.hres, static_cast<OT*>(op.out), 32);
       ++launches;
     } break;
     case OP_LAYERNORM: {
       const long long nrows = (long long)B * L.R;
-      layernorm_kernel<OT><<<(unsigned)((nrows + 7) / 8), 256, 0, st>>>(pl.hres.template as<float>(), nrows, op.ln_g,
-                                                                        op.ln_b, pl.ln.template as<OT>());
-      SRN_CUDA(cudaGetLastError());
-      ++launches;
-    } break;
-    case OP_SOFTMAX: {
-      const long long nrows = (long long)B * 4 * L.T;
-      const unsigned grid = (unsigned)((nrows + 1) / 2);
-      const float* sc = pl.sc.template as<float>();
-      OT* P = pl.P.template as<OT>();
-#define SRN_SOFTMAX(NV) softmax_kernel<OT, NV><<<grid, 256, 0, st>>>(sc, L.T, L.Sp, 4, nrows, mask, pl.Tp, L.mask_step, P)
-      if (L.T <= 512) SRN_SOFTMAX(1);
-      else if (L.T <= 1024) SRN_SOFTMAX(2);
-      else if (L.T <= 2048) SRN_SOFTMAX(4);
-      else if (L.T <= 4096) SRN_SOFTMAX(8);
-      else if (L.T <= 8192) SRN_SOFTMAX(16);
-      else fail("sequence of %d frames exceeds the softmax kernel's 8192-key limit", L.T);
-#undef SRN_SOFTMAX
-      SRN_CUDA(cudaGetLastError());
+      launch_k(layernorm_kernel<OT>, dim3((unsigned)((nrows + 7) / 8)), dim3(256), st, pl.hres.template as<float>(), nrows,
+               op.ln_g, op.ln_b, pl.ln.template as<OT>());
       ++launches;
     } break;
   }
@@ -182,35 +191,33 @@ void Engine<OT>::prepass(Plan<OT>& pl, const std::vector<float>& ts, const std::
   const uint8_t* mask = pl.mask.template as<uint8_t>();
   {
     dim3 grid(cdiv(pl.T, 32), cdiv(cmu_, 32), B);
-    pack_cf_to_cl<OT><<<grid, dim3(32, 8), 0, st>>>(pl.mu_in.template as<float>(), cmu_, pl.T, mask, pl.Tp,
-                                                    pl.xin.template as<OT>(), (long long)pl.Tp * 256, 256,
-                                                    cfg_.out_channels);
-    SRN_CUDA(cudaGetLastError());
+    launch_k(pack_cf_to_cl<OT>, grid, dim3(32, 8), st, pl.mu_in.template as<float>(), cmu_, pl.T, mask, pl.Tp,
+             pl.xin.template as<OT>(), (long long)pl.Tp * 256, 256, cfg_.out_channels);
     ++launches;
   }
   const int sd = cfg_.spk_embed_dim;
   for (int r = 0; r < nres; ++r) {
-    gemv_kernel<<<dim3(512 / 8, B), 256, 0, st>>>(resnets_[r].ws_w, resnets_[r].ws_b, pl.spk_in.template as<float>(),
-                                                   pl.spk_scale.template as<float>() + (size_t)r * B * 512, sd, 512,
-                                                   ACT_NONE, ACT_NONE);
-    gemv_kernel<<<dim3(512 / 8, B), 256, 0, st>>>(resnets_[r].wb_w, resnets_[r].wb_b, pl.spk_in.template as<float>(),
-                                                   pl.spk_bias.template as<float>() + (size_t)r * B * 512, sd, 512,
-                                                   ACT_NONE, ACT_NONE);
+    launch_k(gemv_kernel, dim3(512 / 8, B), dim3(256), st, resnets_[r].ws_w, resnets_[r].ws_b,
+             pl.spk_in.template as<float>(), pl.spk_scale.template as<float>() + (size_t)r * B * 512, sd, 512,
+             (int)ACT_NONE, (int)ACT_NONE);
+    launch_k(gemv_kernel, dim3(512 / 8, B), dim3(256), st, resnets_[r].wb_w, resnets_[r].wb_b,
+             pl.spk_in.template as<float>(), pl.spk_bias.template as<float>() + (size_t)r * B * 512, sd, 512,
+             (int)ACT_NONE, (int)ACT_NONE);
     launches += 2;
   }
   SRN_CUDA(cudaGetLastError());
   const int dim = cfg_.in_channels;
   const float e = (float)(std::log(10000.0) / (double)(dim / 2 - 1));
-  sinusoid_kernel<<<n, 128, 0, st>>>(pl.tsteps.template as<float>(), dim, e, pl.temb0.template as<float>());
-  gemv_kernel<<<dim3(2048 / 8, n), 256, 0, st>>>(time_w1_, time_b1_, pl.temb0.template as<float>(),
-                                                 pl.temb1.template as<float>(), dim, 2048, ACT_NONE, ACT_SILU);
-  gemv_kernel<<<dim3(2048 / 8, n), 256, 0, st>>>(time_w2_, time_b2_, pl.temb1.template as<float>(),
-                                                 pl.temb2.template as<float>(), 2048, 2048, ACT_NONE, ACT_NONE);
+  launch_k(sinusoid_kernel, dim3(n), dim3(128), st, pl.tsteps.template as<float>(), dim, e, pl.temb0.template as<float>());
+  launch_k(gemv_kernel, dim3(2048 / 8, n), dim3(256), st, time_w1_, time_b1_, pl.temb0.template as<float>(),
+           pl.temb1.template as<float>(), dim, 2048, (int)ACT_NONE, (int)ACT_SILU);
+  launch_k(gemv_kernel, dim3(2048 / 8, n), dim3(256), st, time_w2_, time_b2_, pl.temb1.template as<float>(),
+           pl.temb2.template as<float>(), 2048, 2048, (int)ACT_NONE, (int)ACT_NONE);
   launches += 3;
   for (int r = 0; r < nres; ++r) {
-    gemv_kernel<<<dim3(512 / 8, n), 256, 0, st>>>(resnets_[r].mlp_w, resnets_[r].mlp_b, pl.temb2.template as<float>(),
-                                                  pl.tb.template as<float>() + (size_t)r * pl.tb_steps * 512, 2048, 512,
-                                                  ACT_MISH, ACT_NONE);
+    launch_k(gemv_kernel, dim3(512 / 8, n), dim3(256), st, resnets_[r].mlp_w, resnets_[r].mlp_b,
+             pl.temb2.template as<float>(), pl.tb.template as<float>() + (size_t)r * pl.tb_steps * 512, 2048, 512,
+             (int)ACT_MISH, (int)ACT_NONE);
     ++launches;
   }
   SRN_CUDA(cudaGetLastError());
@@ -375,7 +382,6 @@ std::string Engine<OT>::profile_ops(int B, int T, int reps) {
       case OP_GN_APPLY: kind = "gn_apply"; bytes = rows * 512 * (4 + es); break;
       case OP_GN_RES_SPK_LN: kind = "gn_res_spk_ln"; bytes = rows * 512 * (4 + 4 + 4 + es); break;
       case OP_LAYERNORM: kind = "layernorm"; bytes = rows * 512 * (4 + es); break;
-      case OP_SOFTMAX: kind = "softmax"; bytes = (double)B * 4 * L.T * L.T * (4 + es); break;
     }
     char buf[512];
     snprintf(buf, sizeof buf, "%s{\"op\": \"%s\", \"kernel\": \"%s\", \"ms\": %.6f, \"flops\": %.6e, \"bytes\": %.6e}",

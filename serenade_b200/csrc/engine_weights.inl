@@ -4,7 +4,14 @@ namespace srn {
 template <typename OT>
 inline OT to_ot(float v);
 template <>
-inline float to_ot<float>(float v) { return v; }
+inline float to_ot<float>(float v) {
+  // TF32 operands: round to nearest-even here; the tensor core would otherwise TRUNCATE the low 13 mantissa bits
+  uint32_t u;
+  memcpy(&u, &v, 4);
+  if ((u & 0x7f800000u) != 0x7f800000u) u = (u + 0xfffu + ((u >> 13) & 1u)) & ~0x1fffu;
+  memcpy(&v, &u, 4);
+  return v;
+}
 template <>
 inline __nv_bfloat16 to_ot<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
 

@@ -24,6 +24,10 @@ enum EpiMode : int {
   EPI_GEGLU = 4,       // out OT[n/2] = (acc[2i]+b) * gelu_erf(acc[2i+1]+b)   (interleaved weights)
   EPI_QKV = 5,         // n <  split: OT row-major store; n >= split: transposed store into V^T
   EPI_EULER = 6,       // channels-first f32: v = (acc+bias)*mask ; x_out = x_in + dt * v
+  // Attention without a materialised score matrix (two passes over Q K^T, then P~ V):
+  EPI_ROWMAX = 7,      // no tensor output: stat_max[z][key slice of 64][row] = max over the slice's valid keys of acc*alpha
+  EPI_EXP = 8,         // out OT = exp(acc*alpha - rowmax) (0 at masked keys), stat_sum[...] = partial row sums (f32)
+  EPI_PV = 9,          // out OT = acc / rowsum
 };
 
 struct KSeg {
@@ -82,6 +86,15 @@ struct GemmParams {
   int d_hcol;       // output column offset per h (elements), e.g. 512 for the per-head attention output
   int d_zbatch;     // output batch coordinate: 1 -> z, 0 -> b
   int dbg_mode;     // profiling experiments only: 1 = skip TMA loads, 2 = skip MMA issue (results are garbage)
+  // EPI_ROWMAX / EPI_EXP / EPI_PV: per-row softmax statistics, one entry per 64-key slice:
+  // stat[(z * stat_n + j) * stat_ld + row], j < stat_n = ceil(keys / 64)
+  float* stat_max;
+  float* stat_sum;
+  int stat_n;
+  int stat_ld;
+  const uint8_t* keymask;   // (B, keys): key k of batch b takes part iff keymask[b*keymask_bstride + k*keymask_step] != 0
+  int keymask_bstride;
+  int keymask_step;
 };
 
 template <typename OT>

@@ -32,12 +32,25 @@ struct GemmCfg {
 };
 
 // One 32-column chunk of one accumulator row (bias / alpha already applied to v).
+// Softmax modes: `racc` is this thread's running row max (ROWMAX) or row sum (EXP), `rowc` the row constant
+// (EXP: rowmax * log2 e, PV: 1 / rowsum), `keybits` bit i = key column nc + i takes part.
 template <typename OT, int EPI>
 __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[32], Stager& st, int lane, int b, int h,
                                                int z, int row, int row0, int nc, bool row_ok, float mk, float& gs,
-                                               float& gss) {
+                                               float& gss, float& racc, float rowc, uint32_t keybits) {
   const int batch = p.d_zbatch ? z : b;
   constexpr int kOtCols = 128 / (int)sizeof(OT);     // output columns per 128-byte staging row
+  // fp32-stored operand tensors are consumed as TF32: round to nearest here (the tensor core truncates)
+  auto round_op = [](float (&w)[32]) {
+    if constexpr (sizeof(OT) == 4) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        uint32_t u;
+        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(w[i]));
+        w[i] = __uint_as_float(u);
+      }
+    }
+  };
   if constexpr (EPI == EPI_STORE_F32) {
     if (p.gn_part != nullptr && row_ok) {
 #pragma unroll
@@ -49,6 +62,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
   } else if constexpr (EPI == EPI_STORE_OT) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] *= mk;
+    round_op(v);
     stager_acquire(st, lane);
     stager_put<OT, 32>(st, lane, v);
     stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols + h * p.d_hcol, row0, batch);
@@ -70,6 +84,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     } else {
 #pragma unroll
       for (int i = 0; i < 32; ++i) v[i] *= mk;
+      round_op(v);
       stager_put<OT, 32>(st, lane, v);
       stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols, row0, batch);
     }
@@ -77,10 +92,19 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     float o[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) o[i] = v[2 * i] * gelu_erf(v[2 * i + 1]);
+    if constexpr (sizeof(OT) == 4) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        uint32_t u;
+        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(o[i]));
+        o[i] = __uint_as_float(u);
+      }
+    }
     stager_acquire(st, lane);
     stager_put<OT, 16>(st, lane, o);
     stager_flush(st, lane, &p.mapD, (nc >> 1) + 16 - kOtCols, row0, batch);
   } else if constexpr (EPI == EPI_QKV) {
+    round_op(v);
     if (nc < p.split_n) {
       stager_acquire(st, lane);
       stager_put<OT, 32>(st, lane, v);
@@ -88,6 +112,29 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     } else {
       stager_store_transposed<OT>(st, lane, v, &p.mapD2, row0, nc - p.split_n, batch);
     }
+  } else if constexpr (EPI == EPI_ROWMAX) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if ((keybits >> i) & 1u) racc = fmaxf(racc, v[i] * p.alpha);
+  } else if constexpr (EPI == EPI_EXP) {
+    const float sc = p.alpha * 1.4426950408889634f;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const float e = exp2f(fmaf(v[i], sc, -rowc));
+      v[i] = ((keybits >> i) & 1u) ? e : 0.f;
+      racc += v[i];
+    }
+    round_op(v);
+    stager_acquire(st, lane);
+    stager_put<OT, 32>(st, lane, v);
+    stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols, row0, batch);
+  } else if constexpr (EPI == EPI_PV) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] *= rowc;
+    round_op(v);
+    stager_acquire(st, lane);
+    stager_put<OT, 32>(st, lane, v);
+    stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols + h * p.d_hcol, row0, batch);
   } else if constexpr (EPI == EPI_EULER) {
     if (row_ok) {
       const long long base = ((long long)b * p.N + nc) * p.T_cf + row;

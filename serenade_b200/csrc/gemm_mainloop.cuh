@@ -29,6 +29,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   const int pair0 = blockIdx.x >> 1;
   const int npairs = gridDim.x >> 1;
 
+  pdl_launch_dependents();
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&p.mapA[0]);
     tma_prefetch_desc(&p.mapA[1]);
@@ -51,6 +52,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();     // everything above overlapped with the previous kernel's tail
 
   if (warp == 0) {
     if (elect_one()) {
@@ -139,10 +141,27 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       const int c_first = sub * (NCH / 2);
       int nvalid = (p.N - (n0 + c_first * 32) + 31) / 32;     // chunks of this warp that start inside N
       nvalid = nvalid < 0 ? 0 : (nvalid > NCH / 2 ? NCH / 2 : nvalid);
+      // 2-byte outputs fill one 128-byte staging row per TWO chunks: never stop on a half-filled box (N = keys
+      // need not be a multiple of 64 for EPI_EXP; columns >= N hold exact zeros and are clipped by the store)
+      if constexpr (sizeof(OT) == 2 && EPI == EPI_EXP) nvalid = (nvalid + 1) & ~1;
       const uint32_t trow = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN + c_first * 32);
       mbar_wait(&tfull_bar[as], (it >> 1) & 1);
       tc_fence_after();
       float gs = 0.f, gss = 0.f;
+      // softmax modes: per-row constants from the statistics of the earlier pass(es)
+      float racc = EPI == EPI_ROWMAX ? -INFINITY : 0.f, rowc = 0.f;
+      if constexpr (EPI == EPI_EXP || EPI == EPI_PV) {
+        if (row_ok) {
+          const float* sp = (EPI == EPI_EXP ? p.stat_max : p.stat_sum) + (long long)z * p.stat_n * p.stat_ld + row;
+          float a = EPI == EPI_EXP ? -INFINITY : 0.f;
+          for (int j = 0; j < p.stat_n; ++j) {
+            const float s = sp[(long long)j * p.stat_ld];
+            a = EPI == EPI_EXP ? fmaxf(a, s) : a + s;
+          }
+          if constexpr (EPI == EPI_EXP) rowc = (a == -INFINITY ? 0.f : a) * 1.4426950408889634f;   // fully masked row: P = 0
+          else rowc = a > 0.f ? 1.0f / a : 0.f;
+        }
+      }
       uint32_t raw[32];
       if (nvalid > 0) tmem_ld_32x32b_x32(trow, raw);
 #pragma unroll 1
@@ -172,7 +191,23 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
             for (int i = 0; i < 32; ++i) v[i] *= p.alpha;
           }
         }
-        epilogue_chunk<OT, EPI>(p, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss);
+        uint32_t keybits = 0;
+        if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
+          const int key = nc + lane;
+          const bool kv = key < p.N &&
+                          p.keymask[(long long)b * p.keymask_bstride + (long long)key * p.keymask_step] != 0;
+          keybits = __ballot_sync(0xffffffffu, kv);
+        }
+        epilogue_chunk<OT, EPI>(p, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss, racc, rowc, keybits);
+        if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
+          // one partial per 64-key slice, whatever the tile shape: the order in which the row sum is formed (here
+          // and in the P~ V epilogue) is then independent of BN, i.e. of the batch size the plan was built for
+          if ((cc & 1) || cc + 1 == nvalid) {
+            if (row_ok)
+              (EPI == EPI_ROWMAX ? p.stat_max : p.stat_sum)[((long long)z * p.stat_n + (nc >> 6)) * p.stat_ld + row] = racc;
+            racc = EPI == EPI_ROWMAX ? -INFINITY : 0.f;
+          }
+        }
         if constexpr (EPI == EPI_STORE_F32) {
           if (p.gn_part != nullptr && (c & 1)) {   // a 64-channel group is complete
             const float s = warp_sum_f(gs), ss = warp_sum_f(gss);

@@ -20,6 +20,14 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// Every kernel of the library is launched with programmatic stream serialization: it lets the NEXT kernel of the
+// stream start (its prologue runs under this kernel's tail) and blocks at pdl_wait() until the PREVIOUS kernel
+// has completed and its memory is visible.  Every kernel calls pdl_wait() before its first dependent global
+// access, so completion stays transitive along the stream.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---------------------------------------------------------------- mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

@@ -11,6 +11,8 @@
 #include <cuda_bf16.h>
 #include <cstdint>
 
+#include "ptx.cuh"
+
 namespace srn {
 
 constexpr int kC = 512;         // hidden width of the ssc1 decoder
@@ -50,6 +52,21 @@ __device__ __forceinline__ float to_f(__nv_bfloat16 v) { return __bfloat162float
 __device__ __forceinline__ void from_f(float* p, float v) { *p = v; }
 __device__ __forceinline__ void from_f(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
 
+// Operand stores: tensors that feed a GEMM as TF32 are rounded to nearest here (the tensor core truncates fp32
+// inputs to TF32, which is biased and twice the error); bf16 operands round in the conversion.
+__device__ __forceinline__ float tf32_rn(float v) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
+  return __uint_as_float(u);
+}
+__device__ __forceinline__ void store8_op(float* p, const float (&v)[8]) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(tf32_rn(v[0]), tf32_rn(v[1]), tf32_rn(v[2]), tf32_rn(v[3]));
+  reinterpret_cast<float4*>(p)[1] = make_float4(tf32_rn(v[4]), tf32_rn(v[5]), tf32_rn(v[6]), tf32_rn(v[7]));
+}
+__device__ __forceinline__ void store8_op(__nv_bfloat16* p, const float (&v)[8]) { store8(p, v); }
+__device__ __forceinline__ void from_f_op(float* p, float v) { *p = tf32_rn(v); }
+__device__ __forceinline__ void from_f_op(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -67,6 +84,8 @@ template <typename OT>
 __global__ void pack_cf_to_cl(const float* __restrict__ src, int C, int T, const uint8_t* __restrict__ mask,
                               int mask_bstride, OT* __restrict__ dst, long long dst_bstride, int ldd, int col0) {
   __shared__ float tile[32][33];
+  pdl_launch_dependents();
+  pdl_wait();
   const int b = blockIdx.z;
   const int t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
@@ -78,7 +97,7 @@ __global__ void pack_cf_to_cl(const float* __restrict__ src, int C, int T, const
     const int t = t0 + i, c = c0 + threadIdx.x;
     if (t < T && c < C) {
       const float m = mask[(long long)b * mask_bstride + t] ? 1.f : 0.f;
-      from_f(dst + b * dst_bstride + (long long)t * ldd + col0 + c, tile[threadIdx.x][i] * m);
+      from_f_op(dst + b * dst_bstride + (long long)t * ldd + col0 + c, tile[threadIdx.x][i] * m);
     }
   }
 }
@@ -124,6 +143,8 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__
                                                        int rows_per_block) {
   __shared__ float stats[16];
   __shared__ double red[256];
+  pdl_launch_dependents();
+  pdl_wait();
   const int b = blockIdx.y;
   gn_reduce_stats(part, b, mtiles, T, stats, red);
   const int c = (threadIdx.x & 63) * 8;
@@ -149,7 +170,7 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__
     load8(y + off, v);
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] = (mish_f(v[i] * ga[i] + be[i]) + tb[i]) * m;
-    store8(out + off, v);
+    store8_op(out + off, v);
   }
 }
 
@@ -170,6 +191,8 @@ __global__ void __launch_bounds__(256) gn_res_spk_ln(const float* __restrict__ y
                                                      OT* __restrict__ ln_out, int rows_per_block) {
   __shared__ float stats[16];
   __shared__ double red[256];
+  pdl_launch_dependents();
+  pdl_wait();
   const int b = blockIdx.y;
   gn_reduce_stats(part, b, mtiles, T, stats, red);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -228,7 +251,7 @@ __global__ void __launch_bounds__(256) gn_res_spk_ln(const float* __restrict__ y
       load8(ln_b + c, b1);
 #pragma unroll
       for (int i = 0; i < 8; ++i) o[i] = u[hlf * 8 + i] * inv2 * g1[i] + b1[i];
-      store8(ln_out + rowoff + c, o);
+      store8_op(ln_out + rowoff + c, o);
     }
   }
 }
@@ -239,6 +262,8 @@ template <typename OT>
 __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, long long nrows,
                                                         const float* __restrict__ g, const float* __restrict__ bta,
                                                         OT* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (r >= nrows) return;
@@ -267,7 +292,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
     load8(bta + c, bb);
 #pragma unroll
     for (int i = 0; i < 8; ++i) o[i] = u[hlf * 8 + i] * inv * gg[i] + bb[i];
-    store8(out + rowoff + c, o);
+    store8_op(out + rowoff + c, o);
   }
 }
 
@@ -275,8 +300,8 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
 // P[z][q][k] = softmax_k(scores[z][q][k]) with keys where mask[b][k*step] == 0 excluded.  One block per row.
 // Single pass over HBM: each 128-thread half-block owns one row and keeps it in registers (NV float4 per thread,
 // S <= 512 * NV); scores are read once (4 B/elem) and P written once.  ld must be a multiple of 4.
-__device__ __forceinline__ void store4(float* p, float a, float b, float c, float d) {
-  *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+__device__ __forceinline__ void store4(float* p, float a, float b, float c, float d) {   // P is a GEMM operand
+  *reinterpret_cast<float4*>(p) = make_float4(tf32_rn(a), tf32_rn(b), tf32_rn(c), tf32_rn(d));
 }
 __device__ __forceinline__ void store4(__nv_bfloat16* p, float a, float b, float c, float d) {
   __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
@@ -291,6 +316,8 @@ __global__ void __launch_bounds__(256) softmax_kernel(const float* __restrict__ 
                                                       long long nrows, const uint8_t* __restrict__ mask,
                                                       int mask_bstride, int mask_step, OT* __restrict__ P) {
   __shared__ float redf[2][4];
+  pdl_launch_dependents();
+  pdl_wait();
   const int half = threadIdx.x >> 7, t = threadIdx.x & 127;
   const int lane = threadIdx.x & 31, warp = (threadIdx.x >> 5) & 3;
   const long long rowi = (long long)blockIdx.x * 2 + half;        // z * S + q
@@ -351,6 +378,8 @@ __device__ __forceinline__ float apply_act(float v, int a) {
 __global__ void __launch_bounds__(256) gemv_kernel(const float* __restrict__ W, const float* __restrict__ bias,
                                                    const float* __restrict__ in, float* __restrict__ out, int I, int O,
                                                    int act_in, int act_out) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int o = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int s = blockIdx.y;
@@ -366,6 +395,8 @@ __global__ void __launch_bounds__(256) gemv_kernel(const float* __restrict__ W, 
 // emb[s][j] = sin(1000 t_s f_j), emb[s][half + j] = cos(...),  f_j = exp(-j ln(1e4)/(half-1))  (decoder.py:54-63)
 __global__ void sinusoid_kernel(const float* __restrict__ ts, int dim, float e /* ln(1e4)/(half-1) */,
                                 float* __restrict__ emb) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int s = blockIdx.x;
   const int half = dim / 2;
   for (int j = threadIdx.x; j < half; j += blockDim.x) {

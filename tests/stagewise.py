@@ -86,7 +86,7 @@ def fine_reference(sd, batch, t):
 BLOCK_ORDER = ["down0.resnet", "down0.tfm", "down0.out", "down1.resnet", "down1.tfm", "down1.out",
                "mid0.resnet", "mid0.tfm", "mid1.resnet", "mid1.tfm", "up0.resnet", "up0.tfm", "up0.out",
                "up1.resnet", "up1.tfm", "up1.out", "final_block"]
-FINE_ORDER = ["xin", "down0.y1", "down0.r", "down0.a1", "down0.y2", "down0.resnet", "down0.qk", "down0.sc",
+FINE_ORDER = ["xin", "down0.y1", "down0.r", "down0.a1", "down0.y2", "down0.resnet", "down0.qk",
               "down0.P", "down0.ao", "down0.h_attn", "down0.ln3", "down0.gg"]
 # outputs that the CUDA path stores already masked (every consumer masks them anyway)
 MASKED_TAPS = {"tfm", "out"}
@@ -106,13 +106,15 @@ def compare(cfm, sd, batch, t, fine=True):
             for name in FINE_ORDER:
                 got = eng.debug_fetch(name)
                 want = ref[name]
-                valid = level_mask(batch, want.shape[1]) if name not in ("down0.sc", "down0.P") else None
-                if name in ("down0.sc", "down0.P"):
-                    # compare valid query rows and valid keys only
-                    B = batch.mask.shape[0]
+                valid = level_mask(batch, want.shape[1]) if name != "down0.P" else None
+                if name == "down0.P":
+                    # the CUDA path keeps P~ = exp(s - rowmax) unnormalised (the row sum is divided out in the
+                    # P~ V epilogue): normalise here; compare valid query rows and valid keys only
                     m = batch.mask[:, 0].float()
                     mm = (m.unsqueeze(2) * m.unsqueeze(1)).repeat_interleave(4, dim=0)
-                    rows.append((name, rel(got * mm, want * mm), "valid q,k"))
+                    got = got * mm
+                    got = got / got.sum(-1, keepdim=True).clamp_min(1e-30)
+                    rows.append((name, rel(got * mm, want * mm), "valid q,k, rows normalised on the host"))
                 else:
                     rows.append((name, rel(got * valid, want * valid), "valid rows"))
         stages = oracle_stages(sd, batch, t)
