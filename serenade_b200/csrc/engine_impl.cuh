@@ -144,6 +144,7 @@ class Engine : public EngineBase {
   const HostTensor& hw(const std::string& key, std::initializer_list<int64_t> dims);
   float* up_f32(const std::vector<float>& v);
   OT* up_ot(const std::vector<float>& v);
+  OT* up_w(const std::vector<float>& v, int N, int K);
   ResnetW<OT> pack_resnet(const std::string& p, int cin);
   TfmW<OT> pack_tfm(const std::string& p);
   OT* pack_conv3(const HostTensor& w, int cin, int cin_pad, float* /*unused*/ = nullptr);

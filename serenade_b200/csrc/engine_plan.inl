@@ -40,10 +40,21 @@ void set_A(GemmParams& gp, int idx, const OT* ptr, int cols, int rows, long long
   gp.mapA[idx] = make_tmap_3d(ptr, sizeof(OT), cols, rows, nbatch, ld, (uint64_t)alloc_rows * ld, OpTraits<OT>::kBK, 128);
   if (idx == 0) gp.mapA[1] = gp.mapA[0];
 }
+// Call after every add_seg of the op.  TF32 mode: the packed weight rows are [hi | lo] (engine_weights.inl: up_w),
+// so the K loop runs twice over the same A segments while the B column keeps advancing: A.hi + A.lo.
 template <typename OT>
 void set_B_weight(GemmParams& gp, const OT* W, int N, int K, int bn) {
-  gp.mapB = make_tmap_3d(W, sizeof(OT), K, N, 1, K, (uint64_t)N * K, OpTraits<OT>::kBK, bn / 2);   // each CTA of a pair loads half the B rows
+  if (gp.nkb * OpTraits<OT>::kBK != K) fail("set_B_weight: K = %d but the A segments cover %d", K, gp.nkb * OpTraits<OT>::kBK);
+  const int Kw = OpTraits<OT>::kTF32 ? 2 * K : K;
+  gp.mapB = make_tmap_3d(W, sizeof(OT), Kw, N, 1, Kw, (uint64_t)N * Kw, OpTraits<OT>::kBK, bn / 2);   // each CTA of a pair loads half the B rows
   gp.b_batch_mode = 0;
+  if (OpTraits<OT>::kTF32) {
+    const int n = gp.nseg;
+    if (2 * n > 12) fail("too many K segments");
+    for (int i = 0; i < n; ++i) gp.seg[n + i] = gp.seg[i];
+    gp.nseg = 2 * n;
+    gp.nkb *= 2;
+  }
 }
 // Output store map: 32-row x 128-byte boxes, SWIZZLE_128B (see gemm_epilogue.cuh)
 template <typename T>
@@ -51,7 +62,7 @@ void set_D(GemmParams& gp, const T* ptr, int cols, int rows, long long bstride, 
   gp.mapD = make_tmap_3d(ptr, sizeof(T), cols, rows, nbatch, ld, (uint64_t)bstride, 128 / sizeof(T), 32);
 }
 inline void add_seg(GemmParams& gp, int src, int col0, int shift, int nblk) {
-  if (gp.nseg >= 6) fail("too many K segments");
+  if (gp.nseg >= 12) fail("too many K segments");
   gp.seg[gp.nseg++] = KSeg{src, col0, shift, nblk};
   gp.nkb += nblk;
 }

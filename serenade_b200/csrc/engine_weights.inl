@@ -82,6 +82,27 @@ OT* Engine<OT>::up_ot(const std::vector<float>& v) {
   return arena_.back().template as<OT>();
 }
 
+// GEMM weight [N][K], K-major.  bf16 mode: rounded to bf16.  TF32 mode: every row is stored as [hi | lo] with
+// hi = tf32(w), lo = tf32(w - hi), and the GEMM runs its K loop twice (A.hi + A.lo, see set_B_weight): the weights
+// then carry ~21 mantissa bits and only the activation operand is rounded to TF32.
+template <typename OT>
+OT* Engine<OT>::up_w(const std::vector<float>& v, int N, int K) {
+  if ((size_t)N * K != v.size()) fail("up_w: %d x %d does not match %zu values", N, K, v.size());
+  if constexpr (!OpTraits<OT>::kTF32) {
+    return up_ot(v);
+  } else {
+    std::vector<float> sp((size_t)N * 2 * K);
+    for (int n = 0; n < N; ++n)
+      for (int k = 0; k < K; ++k) {
+        const float w = v[(size_t)n * K + k];
+        const float hi = to_ot<float>(w);
+        sp[(size_t)n * 2 * K + k] = hi;
+        sp[(size_t)n * 2 * K + K + k] = to_ot<float>(w - hi);
+      }
+    return up_f32(sp);
+  }
+}
+
 // Conv1d weight (O, I, 3) -> [O][3][cin_pad]: K index = tap * cin_pad + i  (tap 0 multiplies x[t-1]).
 template <typename OT>
 OT* Engine<OT>::pack_conv3(const HostTensor& w, int cin, int cin_pad, float*) {
@@ -90,7 +111,7 @@ OT* Engine<OT>::pack_conv3(const HostTensor& w, int cin, int cin_pad, float*) {
   for (int o = 0; o < O; ++o)
     for (int i = 0; i < cin; ++i)
       for (int k = 0; k < 3; ++k) p[((size_t)o * 3 + k) * cin_pad + i] = w.data[((size_t)o * cin + i) * 3 + k];
-  return up_ot(p);
+  return up_w(p, O, 3 * cin_pad);
 }
 
 template <typename OT>
@@ -111,7 +132,7 @@ ResnetW<OT> Engine<OT>::pack_resnet(const std::string& p, int cin) {
     std::vector<float> pk((size_t)C * r.cin_pad, 0.f);
     for (int o = 0; o < C; ++o)
       for (int i = 0; i < cin; ++i) pk[(size_t)o * r.cin_pad + i] = w.data[(size_t)o * cin + i];
-    r.wr = up_ot(pk);
+    r.wr = up_w(pk, C, r.cin_pad);
   }
   r.br = up_f32(hw(p + ".res_conv.bias", {C}).data);
   r.mlp_w = up_f32(hw(p + ".mlp.1.weight", {C, te}).data);
@@ -138,9 +159,9 @@ TfmW<OT> Engine<OT>::pack_tfm(const std::string& p) {
       const HostTensor& w = hw(p + n, {inner, C});
       qkv.insert(qkv.end(), w.data.begin(), w.data.end());
     }
-    t.wqkv = up_ot(qkv);
+    t.wqkv = up_w(qkv, 3 * inner, C);
   }
-  t.wo = up_ot(hw(p + ".attn1.to_out.0.weight", {C, inner}).data);
+  t.wo = up_w(hw(p + ".attn1.to_out.0.weight", {C, inner}).data, C, inner);
   t.bo = up_f32(hw(p + ".attn1.to_out.0.bias", {C}).data);
   {
     // GEGLU: rows [0, ffi) are the value half, [ffi, 2 ffi) the gate half (chunk(2, dim=-1)).
@@ -154,10 +175,10 @@ TfmW<OT> Engine<OT>::pack_tfm(const std::string& p) {
       bi[2 * i] = bb.data[i];
       bi[2 * i + 1] = bb.data[ffi + i];
     }
-    t.wgl = up_ot(wi);
+    t.wgl = up_w(wi, 2 * ffi, C);
     t.bgl = up_f32(bi);
   }
-  t.wf = up_ot(hw(p + ".ff.net.2.weight", {C, ffi}).data);
+  t.wf = up_w(hw(p + ".ff.net.2.weight", {C, ffi}).data, C, ffi);
   t.bf = up_f32(hw(p + ".ff.net.2.bias", {C}).data);
   return t;
 }
@@ -205,8 +226,8 @@ void Engine<OT>::finalize_weights() {
         od[(size_t)o * 2 * C + i] = wk[2];
         od[(size_t)o * 2 * C + C + i] = wk[0];
       }
-    up_conv_[0].w = up_ot(ev);
-    up_conv_[0].w_odd = up_ot(od);
+    up_conv_[0].w = up_w(ev, C, 2 * C);
+    up_conv_[0].w_odd = up_w(od, C, 2 * C);
     up_conv_[0].b = up_f32(hw("up_blocks.0.2.conv.bias", {C}).data);
   }
   up_conv_[1].w = pack_conv3(hw("up_blocks.1.2.weight", {C, C, 3}), C, C);
@@ -215,7 +236,7 @@ void Engine<OT>::finalize_weights() {
   final_conv_.b = up_f32(hw("final_block.block.0.bias", {C}).data);
   final_g_ = up_f32(hw("final_block.block.1.weight", {C}).data);
   final_be_ = up_f32(hw("final_block.block.1.bias", {C}).data);
-  proj_w_ = up_ot(hw("final_proj.weight", {cfg_.out_channels, C, 1}).data);
+  proj_w_ = up_w(hw("final_proj.weight", {cfg_.out_channels, C, 1}).data, cfg_.out_channels, C);
   {
     std::vector<float> pb = hw("final_proj.bias", {cfg_.out_channels}).data;
     pb.resize(128, 0.f);          // the epilogue reads bias in whole 32-column chunks

@@ -42,7 +42,7 @@ struct GemmParams {
   CUtensorMap mapB;
   CUtensorMap mapD;    // output tile store: box = 32 rows x 128 bytes, SWIZZLE_128B (all epilogues but EULER)
   CUtensorMap mapD2;   // EPI_QKV: V^T store, box = 32 (d rows) x 32 (s, contiguous), no swizzle
-  KSeg seg[6];
+  KSeg seg[12];
   int nseg;
   int nkb;          // total K blocks
   int ntn, ntm, nz; // tile grid: N tiles, M tiles, batch entries (persistent CTAs loop over ntn*ntm*nz tiles)

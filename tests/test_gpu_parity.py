@@ -16,6 +16,7 @@ pytestmark = pytest.mark.gpu
 
 BF16_STEP_TOL = 2e-2
 BF16_FINAL_TOL = 1e-2
+TF32_STEP_TOL = 1e-3      # the north star's per-step gate
 
 
 @pytest.fixture(scope="module")
@@ -83,6 +84,27 @@ def test_golden_vectors_bf16(name, cfm_jitter, cfm_stock, dev):
     assert ex < BF16_FINAL_TOL
     pad = ~b.mask.expand_as(x)
     assert torch.equal(x[pad], b.z[pad])             # x keeps its noise at padded frames
+
+
+@pytest.fixture(scope="module")
+def cfm_tf32(jitter_sd, stock_sd):
+    return {True: _make_cfm(jitter_sd, "tf32"), False: _make_cfm(stock_sd, "tf32")}
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_golden_vectors_per_step_gate_tf32(name, cfm_tf32, dev):
+    """North-star gate: per-step estimator output within 1e-3 rel-L2 of the reference (TF32-class mode:
+    activations rounded to nearest TF32, weights carried as hi + lo TF32 pairs, fp32 accumulation)."""
+    import serenade_b200 as S
+    spec, v_ref, x_ref = load_golden(name)
+    cfm = cfm_tf32[bool(spec["jitter"])]
+    b = S.make_batch(spec["lengths"], n_steps=spec["n_steps"], seed=spec["seed"])
+    v = cfm.estimator(b.z.to(dev), b.mask.to(dev), b.mu.to(dev), torch.tensor(spec["t"]), b.spks.to(dev)).cpu()
+    x = cfm.solve_euler(b.z.to(dev), b.t_span.to(dev), b.mu.to(dev), b.mask.to(dev), b.spks.to(dev)).cpu()
+    ev, ex = rel_l2(v, v_ref), rel_l2(x, x_ref)
+    _report(f"golden_tf32_{name}.txt", f"{name} (tf32 mode): per-step rel_l2={ev:.3e} final rel_l2={ex:.3e}")
+    assert ev < TF32_STEP_TOL
+    assert ex < TF32_STEP_TOL
 
 
 def test_solver_matches_oracle_mixed_lengths(cfm_jitter, jitter_sd, dev):
