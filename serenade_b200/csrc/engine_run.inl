@@ -363,8 +363,12 @@ std::string Engine<OT>::profile_ops(int B, int T, int reps) {
   const size_t es = sizeof(OT);
   for (size_t i = 0; i < pl.ops.size(); ++i) {
     Op& op = pl.ops[i];
+    static const int dbg_mode = getenv("SRN_DBG_MODE") ? atoi(getenv("SRN_DBG_MODE")) : 0;
+    const int saved_mode = op.gp.dbg_mode;
+    op.gp.dbg_mode = dbg_mode;
     SRN_CUDA(cudaEventRecord(e0, st));
     for (int r = 0; r < reps; ++r) launch_op(pl, op, 0, nullptr, true, st);
+    op.gp.dbg_mode = saved_mode;
     SRN_CUDA(cudaEventRecord(e1, st));
     SRN_CUDA(cudaEventSynchronize(e1));
     float ms = 0.f;

@@ -85,7 +85,8 @@ struct GemmParams {
   int T_cf;         // row length of the channels-first tensors
   int d_hcol;       // output column offset per h (elements), e.g. 512 for the per-head attention output
   int d_zbatch;     // output batch coordinate: 1 -> z, 0 -> b
-  int dbg_mode;     // profiling experiments only: 1 = skip TMA loads, 2 = skip MMA issue (results are garbage)
+  int dbg_mode;     // profiling experiments only (SRN_DBG_MODE, srn_profile_ops): bit 0 = no TMA loads, bit 1 = no MMAs,
+                    // bit 2 = no epilogue (results are garbage)
   // EPI_ROWMAX / EPI_EXP / EPI_PV: per-row softmax statistics, one entry per 64-key slice:
   // stat[(z * stat_n + j) * stat_ld + row], j < stat_n = ceil(keys / 64)
   float* stat_max;

@@ -25,7 +25,8 @@ struct GemmCfg {
   static constexpr int kStgOff = kStages * kStageBytes;       // epilogue staging: 8 warps x 2 x 4 KB
   static constexpr int kBarOff = kStgOff + 8 * 8192;          // barriers + tmem slot (256 B)
   static constexpr int kRedOff = kBarOff + 256;               // GroupNorm partial reduction scratch (256 B)
-  static constexpr int kSmemBytes = kRedOff + 256 + 1024;     // + alignment slack
+  static constexpr int kBiasOff = kRedOff + 256;              // per epilogue warp: its bias slice (8 x 512 B)
+  static constexpr int kSmemBytes = kBiasOff + 8 * 512 + 1024;     // + alignment slack
   static constexpr int kThreads = 320;
   static constexpr int kTmemCols = 2 * BN;
   static_assert(kStgOff % 1024 == 0, "staging boxes must be 1024-byte aligned for SWIZZLE_128B");
@@ -66,17 +67,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     stager_acquire(st, lane);
     stager_put<OT, 32>(st, lane, v);
     stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols + h * p.d_hcol, row0, batch);
-  } else if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_RESID_OT) {
-    if (row_ok) {
-      const float4* rs = reinterpret_cast<const float4*>(p.resid + b * p.resid_bstride + (long long)row * p.ldr + nc);
-      float4 r4[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) r4[i] = rs[i];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        v[4 * i + 0] += r4[i].x; v[4 * i + 1] += r4[i].y; v[4 * i + 2] += r4[i].z; v[4 * i + 3] += r4[i].w;
-      }
-    }
+  } else if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_RESID_OT) {     // residual already added by the caller
     stager_acquire(st, lane);
     if constexpr (EPI == EPI_RESID_F32) {
       stager_put<float, 32>(st, lane, v);
@@ -120,7 +111,8 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     const float sc = p.alpha * 1.4426950408889634f;
 #pragma unroll
     for (int i = 0; i < 32; ++i) {
-      const float e = exp2f(fmaf(v[i], sc, -rowc));
+      float e;
+      asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fmaf(v[i], sc, -rowc)));
       v[i] = ((keybits >> i) & 1u) ? e : 0.f;
       racc += v[i];
     }
@@ -140,13 +132,21 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
       const long long base = ((long long)b * p.N + nc) * p.T_cf + row;
       const float dt = p.dt_ptr != nullptr ? __ldg(p.dt_ptr) : p.dt;
       const bool blend = p.blend_mask != nullptr && p.blend_mask[(long long)b * p.T_cf + row] != 0;
+      // x_in and x_out are the same buffer: issue all loads of the chunk before the first store, otherwise every
+      // load waits behind the previous (possibly aliasing) store and the chunk costs 32 serial memory latencies
+      float xin[32];
+      if (p.x_out != nullptr) {
+        const float* src = blend ? p.blend_src : p.x_in;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) xin[i] = nc + i < p.N ? src[base + (long long)i * p.T_cf] : 0.f;
+      }
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
         if (nc + i < p.N) {
           const float vv = v[i] * mk;
           const long long idx = base + (long long)i * p.T_cf;
           if (p.v_out != nullptr) p.v_out[idx] = vv;
-          if (p.x_out != nullptr) p.x_out[idx] = blend ? p.blend_src[idx] : p.x_in[idx] + dt * vv;
+          if (p.x_out != nullptr) p.x_out[idx] = blend ? xin[i] : xin[i] + dt * vv;
         }
       }
     }

@@ -76,9 +76,13 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           // both CTAs' bytes complete on the LEADER's full barrier; only the leader arms it (for both)
           const uint32_t fb = map_to_cta(&full_bar[stage], 0);
           const KSeg sg = p.seg[seg];
-          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * CFG::kStageBytes);
-          tma_load_3d_2sm(sa, &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol, m0 + sg.shift, a_batch);
-          tma_load_3d_2sm(sb, &p.mapB, fb, p.b_col0 + kb * BK + h * p.b_hcol, b_row, b_batch);
+          if (p.dbg_mode & 1) {          // profiling experiment: no operand traffic (results are garbage)
+            if (rank == 0) mbar_arrive(&full_bar[stage]);
+          } else {
+            if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * CFG::kStageBytes);
+            tma_load_3d_2sm(sa, &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol, m0 + sg.shift, a_batch);
+            tma_load_3d_2sm(sb, &p.mapB, fb, p.b_col0 + kb * BK + h * p.b_hcol, b_row, b_batch);
+          }
           if (++j == sg.nblk) { j = 0; ++seg; }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -101,9 +105,11 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           const uint32_t sa = smem_u32(smem + stage * CFG::kStageBytes);
           const uint64_t da = make_kmajor_sw128_desc(sa);
           const uint64_t db = make_kmajor_sw128_desc(sa + CFG::kABytes);
+          if (!(p.dbg_mode & 2)) {       // (dbg_mode & 2: profiling experiment without MMAs)
 #pragma unroll
-          for (int k = 0; k < 4; ++k)   // 4 x 32 bytes of K per 128-byte swizzled row
-            umma_pair<TR::kTF32>(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            for (int k = 0; k < 4; ++k)   // 4 x 32 bytes of K per 128-byte swizzled row
+              umma_pair<TR::kTF32>(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          }
           tc_commit_pair(&empty_bar[stage]);     // frees the stage in both CTAs
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -120,6 +126,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     st.fill = 0;
     const bool has_bias = p.bias != nullptr;
     const bool has_alpha = p.alpha != 1.0f;
+    float* bias_s = reinterpret_cast<float*>(smem + CFG::kBiasOff) + (warp - 2) * 128;   // this warp's bias slice
     const uint32_t tepi_addr = map_to_cta(&tempty_bar[0], 0);
     uint32_t it = 0;
     for (int tile = pair0; tile < total_tiles; tile += npairs, ++it) {
@@ -145,15 +152,15 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       // need not be a multiple of 64 for EPI_EXP; columns >= N hold exact zeros and are clipped by the store)
       if constexpr (sizeof(OT) == 2 && EPI == EPI_EXP) nvalid = (nvalid + 1) & ~1;
       const uint32_t trow = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN + c_first * 32);
-      mbar_wait(&tfull_bar[as], (it >> 1) & 1);
-      tc_fence_after();
+      // ---- everything that does not depend on the accumulator is fetched BEFORE waiting for it: with two epilogue
+      // warps per scheduler any global-load latency left inside the chunk loop is fully exposed (ncu: long_sb)
       float gs = 0.f, gss = 0.f;
-      // softmax modes: per-row constants from the statistics of the earlier pass(es)
       float racc = EPI == EPI_ROWMAX ? -INFINITY : 0.f, rowc = 0.f;
-      if constexpr (EPI == EPI_EXP || EPI == EPI_PV) {
+      if constexpr (EPI == EPI_EXP || EPI == EPI_PV) {     // per-row constants from the statistics of the earlier pass
         if (row_ok) {
           const float* sp = (EPI == EPI_EXP ? p.stat_max : p.stat_sum) + (long long)z * p.stat_n * p.stat_ld + row;
           float a = EPI == EPI_EXP ? -INFINITY : 0.f;
+#pragma unroll 4
           for (int j = 0; j < p.stat_n; ++j) {
             const float s = sp[(long long)j * p.stat_ld];
             a = EPI == EPI_EXP ? fmaxf(a, s) : a + s;
@@ -162,8 +169,44 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           else rowc = a > 0.f ? 1.0f / a : 0.f;
         }
       }
+      uint32_t keybits[NCH / 2];
+      if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
+#pragma unroll
+        for (int cc = 0; cc < NCH / 2; ++cc) {
+          const int key = n0 + (c_first + cc) * 32 + lane;
+          const bool kv = key < p.N &&
+                          p.keymask[(long long)b * p.keymask_bstride + (long long)key * p.keymask_step] != 0;
+          keybits[cc] = __ballot_sync(0xffffffffu, kv);
+        }
+      }
+      if (has_bias) {       // this warp's bias slice -> smem (read back as broadcasts, one vector per 4 columns)
+        const int col = n0 + c_first * 32 + lane * 4;
+        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (lane < NCH * 4 && col < p.N) bv = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+        __syncwarp();       // the previous tile's reads of this slice are done
+        if (lane < NCH * 4) *reinterpret_cast<float4*>(bias_s + lane * 4) = bv;
+        __syncwarp();
+      }
+      constexpr bool kResid = EPI == EPI_RESID_F32 || EPI == EPI_RESID_OT;
+      float4 r4[kResid ? 8 : 1];
+      const float4* rs = nullptr;
+      if constexpr (kResid) {
+        rs = reinterpret_cast<const float4*>(p.resid + b * p.resid_bstride + (long long)row * p.ldr + n0 + c_first * 32);
+        if (row_ok && nvalid > 0) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) r4[i] = rs[i];
+        }
+      }
+      if (p.dbg_mode & 4) nvalid = 0;    // profiling experiment without the epilogue
+      mbar_wait(&tfull_bar[as], (it >> 1) & 1);
+      tc_fence_after();
       uint32_t raw[32];
       if (nvalid > 0) tmem_ld_32x32b_x32(trow, raw);
+      else {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(tepi_addr + as * 8);
+      }
 #pragma unroll 1
       for (int cc = 0; cc < nvalid; ++cc) {
         const int c = c_first + cc;
@@ -171,10 +214,9 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         tmem_ld_wait();
         float v[32];
         if (has_bias) {
-          const float4* b4 = reinterpret_cast<const float4*>(p.bias + nc);
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            const float4 bb = __ldg(b4 + i);
+            const float4 bb = *reinterpret_cast<const float4*>(bias_s + cc * 32 + i * 4);
             v[4 * i + 0] = __uint_as_float(raw[4 * i + 0]) + bb.x;
             v[4 * i + 1] = __uint_as_float(raw[4 * i + 1]) + bb.y;
             v[4 * i + 2] = __uint_as_float(raw[4 * i + 2]) + bb.z;
@@ -184,21 +226,38 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
         }
-        if (cc + 1 < nvalid) tmem_ld_32x32b_x32(trow + (cc + 1) * 32, raw);   // overlaps with this chunk's epilogue
+        if (cc + 1 < nvalid) {
+          tmem_ld_32x32b_x32(trow + (cc + 1) * 32, raw);   // overlaps with this chunk's epilogue
+        } else {
+          // the last accumulator chunk is in registers: hand the TMEM stage back to the MMA warp now
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(tepi_addr + as * 8);
+        }
+        if constexpr (kResid) {
+          if (row_ok) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              v[4 * i + 0] += r4[i].x; v[4 * i + 1] += r4[i].y; v[4 * i + 2] += r4[i].z; v[4 * i + 3] += r4[i].w;
+            }
+            if (cc + 1 < nvalid) {            // next chunk's residual: in flight during this chunk's stores
+#pragma unroll
+              for (int i = 0; i < 8; ++i) r4[i] = rs[(cc + 1) * 8 + i];
+            }
+          }
+        }
         if constexpr (EPI == EPI_STORE_F32) {
           if (has_alpha) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] *= p.alpha;
           }
         }
-        uint32_t keybits = 0;
+        uint32_t kbits = 0;
         if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
-          const int key = nc + lane;
-          const bool kv = key < p.N &&
-                          p.keymask[(long long)b * p.keymask_bstride + (long long)key * p.keymask_step] != 0;
-          keybits = __ballot_sync(0xffffffffu, kv);
+#pragma unroll
+          for (int j = 0; j < NCH / 2; ++j) kbits = j == cc ? keybits[j] : kbits;    // keeps keybits[] in registers
         }
-        epilogue_chunk<OT, EPI>(p, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss, racc, rowc, keybits);
+        epilogue_chunk<OT, EPI>(p, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss, racc, rowc, kbits);
         if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
           // one partial per 64-key slice, whatever the tile shape: the order in which the row sum is formed (here
           // and in the P~ V epilogue) is then independent of BN, i.e. of the batch size the plan was built for
@@ -219,10 +278,6 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           }
         }
       }
-      // release the accumulator stage to the MMA warp
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(tepi_addr + as * 8);
       if constexpr (EPI == EPI_STORE_F32) {
         if (p.gn_part != nullptr) {
           asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps only
