@@ -38,6 +38,17 @@ CPU_SAMPLE_B = 16       # cpu_baseline leg of our arm: the whole 16-clip batch o
 REF_SAMPLE_B = 4        # --impl reference: clips per timed step (bounded so that K + W steps end within minutes)
 
 
+def _dram_traffic_per_step():
+    """DRAM bytes (read + write) of one timed step, summed over its kernels, from the committed ncu launch list
+    (profiles/r01_traffic.json, written by tools/launch_summary.py from the same bench command under ncu)."""
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    try:
+        d = json.load(open(p))
+        return float(d["dram_bytes_per_step"]), d.get("source", p)
+    except Exception:
+        return None, None
+
+
 def _peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -62,7 +73,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
@@ -223,6 +234,7 @@ def run_ours(args):
         gemm_fl = sum(o["flops"] for o in ops if o["kernel"].startswith("gemm"))
         row_ms = sum(o["ms"] for o in ops if not o["kernel"].startswith("gemm"))
         row_by = sum(o["bytes"] for o in ops if not o["kernel"].startswith("gemm"))
+        traffic, traffic_src = _dram_traffic_per_step()
         threads = os.cpu_count() or 1
         cpu_fps, cpu_s = _cpu_decode_sample(threads)
         line = {
@@ -237,7 +249,10 @@ def run_ours(args):
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
-                         "frac": achieved / peaks["tf_sustained"], "traffic": None,
+                         "frac": achieved / peaks["tf_sustained"], "traffic": traffic, "traffic_source": traffic_src,
+                         "launch": "one CUDA-graph launch = one step (10 Euler steps x 16 clips); gemm_kernel is the "
+                                   "dominant kernel (its share of the step is gemm_share_of_step)",
+                         "gemm_share_of_step": gemm_ms / (gemm_ms + row_ms) if gemm_ms else None,
                          "peak_source": peaks["source"] + " (sustained bf16; whole Euler solve, SURVEY 8d F(L))",
                          "gemm_kernel": {"tflops_isolated": gemm_fl / (gemm_ms / 1e3) / 1e12 if gemm_ms else None,
                                          "ms_per_estimator_call": gemm_ms,

@@ -9,7 +9,9 @@ import os
 from typing import Optional
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libserenade_b200.so")
+# SRN_LIB_VARIANT=<name> loads an experiment build (python -m serenade_b200.build --variant <name> -DX=1)
+_VARIANT = os.environ.get("SRN_LIB_VARIANT", "")
+LIB_PATH = os.path.join(_PKG, f"libserenade_b200_{_VARIANT}.so" if _VARIANT else "libserenade_b200.so")
 
 EXPORTED_SYMBOLS = [
     "srn_last_error", "srn_version", "srn_create", "srn_destroy", "srn_load_weight", "srn_finalize_weights",

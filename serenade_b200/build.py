@@ -38,17 +38,29 @@ def _source_hash() -> str:
     return h.hexdigest()
 
 
-def build_library(force: bool = False, verbose: bool = False) -> str:
+def build_library(force: bool = False, verbose: bool = False, variant: str = "", defines=()) -> str:
+    """Builds libserenade_b200.so.  `variant` / `defines` build an experiment copy libserenade_b200_<variant>.so
+    with extra -D flags (selected at run time with SRN_LIB_VARIANT=<variant>; A/B timing on one GPU box)."""
+    if variant:
+        return _build(os.path.join(PKG, f"libserenade_b200_{variant}.so"), os.path.join(PKG, "build", variant),
+                      [f"-D{d}" for d in defines], True, verbose)
     want = _source_hash()
     if not force and os.path.exists(LIB) and os.path.exists(STAMP) and open(STAMP).read().strip() == want:
         return LIB
+    _build(LIB, os.path.join(PKG, "build"), [], force, verbose)
+    with open(STAMP, "w") as f:
+        f.write(want)
+    return LIB
+
+
+def _build(lib: str, objdir: str, extra, force: bool, verbose: bool) -> str:
     nvcc = _nvcc()
-    os.makedirs(os.path.join(PKG, "build"), exist_ok=True)
+    os.makedirs(objdir, exist_ok=True)
     objs = []
     procs = []
     for src in SOURCES:
-        obj = os.path.join(PKG, "build", src.replace(".cu", ".o"))
-        cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        obj = os.path.join(objdir, src.replace(".cu", ".o"))
+        cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
             print(" ".join(cmd), flush=True)
@@ -60,14 +72,14 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
             print(out)
         if p.returncode != 0:
             raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + (out or ""))
-    cmd = [nvcc, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
+    cmd = [nvcc, "-shared", "-o", lib, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout)
-    with open(STAMP, "w") as f:
-        f.write(want)
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":
-    print(build_library(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    var = sys.argv[sys.argv.index("--variant") + 1] if "--variant" in sys.argv else ""
+    defs = [a[2:] for a in sys.argv if a.startswith("-D")]
+    print(build_library(force="--force" in sys.argv, verbose="-v" in sys.argv, variant=var, defines=defs))

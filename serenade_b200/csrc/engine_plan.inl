@@ -60,6 +60,7 @@ void set_B_weight(GemmParams& gp, const OT* W, int N, int K, int bn) {
 template <typename T>
 void set_D(GemmParams& gp, const T* ptr, int cols, int rows, long long bstride, int ld, int nbatch) {
   gp.mapD = make_tmap_3d(ptr, sizeof(T), cols, rows, nbatch, ld, (uint64_t)bstride, 128 / sizeof(T), 32);
+  gp.out_cols = cols;
 }
 inline void add_seg(GemmParams& gp, int src, int col0, int shift, int nblk) {
   if (gp.nseg >= 12) fail("too many K segments");

@@ -65,6 +65,7 @@ struct GemmParams {
   void* out;
   long long out_bstride, out_hstride;  // elements
   int ldo;
+  int out_cols;     // inner extent of the output tensor (columns >= out_cols are never written)
   const float* resid;
   long long resid_bstride;
   int ldr;

@@ -51,19 +51,46 @@ __device__ __forceinline__ void stager_put(Stager& s, int lane, const float (&v)
   s.fill += kBytes;
 }
 
-// When the 128-byte rows are complete: make the writes visible to the async proxy and store the box.
-// col = first output column (elements) of the box, row0 = first row, batch = batch coordinate.
-__device__ __forceinline__ void stager_flush(Stager& s, int lane, const CUtensorMap* map, int col, int row0, int batch) {
+// When the 128-byte rows are complete: store the box.  col = first output column (elements) of the box,
+// row0 = first row, batch = batch coordinate.
+//   default: make the writes visible to the async proxy and issue one TMA bulk store of the 32 x 128 B box;
+//   SRN_DIRECT_STORE: read the box back transposed (conflict-free) and write it with 16-byte st.global, four
+//   full 128-byte lines per warp instruction, rows >= M and columns >= the tensor's extent predicated off.
+#ifndef SRN_DIRECT_STORE
+#define SRN_DIRECT_STORE 0
+#endif
+template <typename OutT>
+__device__ __forceinline__ void stager_flush(Stager& s, int lane, const GemmParams& p, int col, int row0, int batch) {
   if (s.fill < 128) return;
+#if SRN_DIRECT_STORE
+  __syncwarp();
+  constexpr int kPiece = 16 / (int)sizeof(OutT);
+  const int pc = lane & 7;
+  const int colp = col + pc * kPiece;
+  const bool col_ok = colp < ((p.out_cols + kPiece - 1) / kPiece) * kPiece;
+  OutT* g = static_cast<OutT*>(p.out) + (long long)batch * (p.d_zbatch ? p.out_hstride : p.out_bstride) + colp;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int r = (lane >> 3) + 4 * j;
+    uint32_t a, b, c, d;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(a), "=r"(b), "=r"(c), "=r"(d)
+                 : "r"(s.box() + r * 128 + ((pc ^ (r & 7)) << 4)));
+    if (col_ok && row0 + r < p.M)
+      *reinterpret_cast<uint4*>(g + (long long)(row0 + r) * p.ldo) = make_uint4(a, b, c, d);
+  }
+  __syncwarp();
+#else
   fence_proxy_async();
   __syncwarp();
   if (lane == 0) {
     asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
-                     reinterpret_cast<uint64_t>(map)),
+                     reinterpret_cast<uint64_t>(&p.mapD)),
                  "r"(s.box()), "r"(col), "r"(row0), "r"(batch)
                  : "memory");
     tma_store_commit();
   }
+#endif
   s.buf ^= 1;
   s.fill = 0;
 }

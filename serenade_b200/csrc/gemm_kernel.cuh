@@ -59,25 +59,25 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     }
     stager_acquire(st, lane);
     stager_put<float, 32>(st, lane, v);
-    stager_flush(st, lane, &p.mapD, nc + h * p.d_hcol, row0, batch);
+    stager_flush<float>(st, lane, p, nc + h * p.d_hcol, row0, batch);
   } else if constexpr (EPI == EPI_STORE_OT) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] *= mk;
     round_op(v);
     stager_acquire(st, lane);
     stager_put<OT, 32>(st, lane, v);
-    stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols + h * p.d_hcol, row0, batch);
+    stager_flush<OT>(st, lane, p, nc + 32 - kOtCols + h * p.d_hcol, row0, batch);
   } else if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_RESID_OT) {     // residual already added by the caller
     stager_acquire(st, lane);
     if constexpr (EPI == EPI_RESID_F32) {
       stager_put<float, 32>(st, lane, v);
-      stager_flush(st, lane, &p.mapD, nc, row0, batch);
+      stager_flush<float>(st, lane, p, nc, row0, batch);
     } else {
 #pragma unroll
       for (int i = 0; i < 32; ++i) v[i] *= mk;
       round_op(v);
       stager_put<OT, 32>(st, lane, v);
-      stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols, row0, batch);
+      stager_flush<OT>(st, lane, p, nc + 32 - kOtCols, row0, batch);
     }
   } else if constexpr (EPI == EPI_GEGLU) {
     float o[16];
@@ -93,13 +93,13 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     }
     stager_acquire(st, lane);
     stager_put<OT, 16>(st, lane, o);
-    stager_flush(st, lane, &p.mapD, (nc >> 1) + 16 - kOtCols, row0, batch);
+    stager_flush<OT>(st, lane, p, (nc >> 1) + 16 - kOtCols, row0, batch);
   } else if constexpr (EPI == EPI_QKV) {
     round_op(v);
     if (nc < p.split_n) {
       stager_acquire(st, lane);
       stager_put<OT, 32>(st, lane, v);
-      stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols, row0, batch);
+      stager_flush<OT>(st, lane, p, nc + 32 - kOtCols, row0, batch);
     } else {
       stager_store_transposed<OT>(st, lane, v, &p.mapD2, row0, nc - p.split_n, batch);
     }
@@ -119,14 +119,14 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     round_op(v);
     stager_acquire(st, lane);
     stager_put<OT, 32>(st, lane, v);
-    stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols, row0, batch);
+    stager_flush<OT>(st, lane, p, nc + 32 - kOtCols, row0, batch);
   } else if constexpr (EPI == EPI_PV) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] *= rowc;
     round_op(v);
     stager_acquire(st, lane);
     stager_put<OT, 32>(st, lane, v);
-    stager_flush(st, lane, &p.mapD, nc + 32 - kOtCols + h * p.d_hcol, row0, batch);
+    stager_flush<OT>(st, lane, p, nc + 32 - kOtCols + h * p.d_hcol, row0, batch);
   } else if constexpr (EPI == EPI_EULER) {
     if (row_ok) {
       const long long base = ((long long)b * p.N + nc) * p.T_cf + row;

@@ -19,12 +19,12 @@ timeout 600 python bench.py > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo 
 tail -c 2500 $O/${TAG}_bench.json
 timeout 300 python tools/profile_ops.py 16 1000 $O/${TAG}_ops_c2.txt > /dev/null 2>&1; echo "ops rc=$?"
 if [ "$WHAT" = "all" ]; then
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/${TAG}_launches.csv \
+timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 2000 --csv --log-file $O/${TAG}_launches.csv \
     python bench.py --steps 1 --warmup 3 > $O/${TAG}_ncu_launch.log 2>&1; echo "ncu-launch rc=$?"
 # full captures of the second (warm) eager estimator call: 30 GEMM launches, 14 row-kernel launches
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_kernel --launch-skip 61 --launch-count 30 -f \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_kernel --launch-skip 73 --launch-count 30 -f \
     -o $O/${TAG}_gemm_full python tools/one_forward.py 16 1000 2 > $O/${TAG}_ncu_gemm.log 2>&1; echo "ncu-gemm rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'gn_|softmax|layernorm|pack_cf' --launch-skip 21 --launch-count 14 -f \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'gn_|layernorm|pack_cf' --launch-skip 21 --launch-count 12 -f \
     -o $O/${TAG}_row_full python tools/one_forward.py 16 1000 2 > $O/${TAG}_ncu_row.log 2>&1; echo "ncu-row rc=$?"
 for r in gemm row; do
   ncu -i $O/${TAG}_${r}_full.ncu-rep --page raw --csv > $O/${TAG}_${r}_full_raw.csv 2>/dev/null
