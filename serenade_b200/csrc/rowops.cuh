@@ -179,6 +179,7 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__
 //   u   = Mish(GN(y2)) * mask + r                                  (ResnetBlock1D, decoder.py:98-99)
 //   s   = (u - mean_c(u)) / sqrt(var_c(u) + 1e-5) * scale[b] + bias[b]   (SpeakerAdapter, decoder.py:34-45)
 //   hres = s (f32 residual stream);  ln = LayerNorm(s) * g1 + b1 (OT)    (transformer.py:286)
+// (forcing 3 or 4 resident blocks per SM through __launch_bounds__ was measured: no faster, 3 spills and is slower)
 template <typename OT>
 __global__ void __launch_bounds__(256) gn_res_spk_ln(const float* __restrict__ y, const float* __restrict__ part,
                                                      int mtiles, int T, long long bstride,
