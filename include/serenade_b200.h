@@ -45,7 +45,7 @@ int srn_create(const SrnConfig* cfg, SrnHandle** out);
 int srn_destroy(SrnHandle* h);
 
 /* Copy one parameter of the reference state dict (key relative to `cfm_decoder.`, i.e.
- * "estimator.down_blocks.0.0.block1.block.0.weight"), f32, HOST memory, dims in torch order. */
+ * "estimator.down_blocks.0.0.block1.block.0.weight"), f32, HOST memory, dims in torch order (ndim <= 4). */
 int srn_load_weight(SrnHandle* h, const char* key, const float* host_data, int32_t ndim, const int64_t* dims);
 /* Validate that every expected key arrived with the expected shape, repack (K-major conv taps, fused QKV,
  * interleaved GEGLU, split transposed-conv parities, operand dtype) and upload. */
@@ -67,6 +67,15 @@ int srn_solve_euler(SrnHandle* h, float* x_inout, const float* mu, const uint8_t
 int srn_solve_euler_host(SrnHandle* h, const float* z_host, const float* mu_host, const uint8_t* mask_host,
                          const float* spk_host, const float* t_span_host, int32_t n_steps, int32_t B, int32_t T,
                          float* mel_out_host, void* stream);
+
+/* ---- Conditioning front half of Serenade.inference (reference serenade/models/serenade.py:181-206).  Available when
+ * the state dict passed to srn_load_weight also held the `encoder.*` and `gst.*` keys of the Serenade model (keys as
+ * in the reference state dict, e.g. "encoder.model.1.weight_v", "gst.ref_enc.convs.0.weight"; 0-d tensors such as
+ * BatchNorm's num_batches_tracked are not sent).  DEVICE pointers, f32.
+ *   srn_content_encode: enc = Serenade.encoder(x)      (Conv1dResnet, serenade.py:224-376)   x (B, L, in_dim) -> (B, L, 80)
+ *   srn_style_encode:   spk = Serenade.gst(ref_logmel) (StyleEncoder, modules/gst/style_encoder.py) (B, L, 80) -> (B, 256) */
+int srn_content_encode(SrnHandle* h, const float* x, int32_t B, int32_t L, float* enc_out, void* stream);
+int srn_style_encode(SrnHandle* h, const float* logmel, int32_t B, int32_t L, float* style_out, void* stream);
 
 /* Number of kernels of this library launched since the handle was created. */
 int64_t srn_launch_count(const SrnHandle* h);

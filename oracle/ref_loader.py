@@ -132,3 +132,42 @@ def build_reference_cfm(in_channels=242, out_channels=80, spk_embed_dim=256,
     return fm.CFM(in_channels=in_channels, out_channels=out_channels, spk_embed_dim=spk_embed_dim,
                   decoder_channels=decoder_channels,
                   decoder_attention_head_dim=decoder_attention_head_dim).eval()
+
+
+def load_reference_serenade():
+    """Returns the reference `serenade.models.serenade` module (exposes Serenade, Conv1dResnet) with the real
+    StyleEncoder / attention / masking files loaded by path (their package __init__ files pull in h5py etc.)."""
+    if "srn" in _cache:
+        return _cache["srn"]
+    load_reference()
+    def mod(name):
+        if name not in sys.modules:
+            m = types.ModuleType(name)
+            m.__path__ = []
+            sys.modules[name] = m
+    for pkg in ("serenade.utils", "serenade.modules", "serenade.modules.gst"):
+        mod(pkg)
+    if "typeguard" not in sys.modules:
+        try:
+            import typeguard  # noqa: F401
+        except Exception:
+            tg = types.ModuleType("typeguard")
+            tg.typechecked = lambda f: f
+            sys.modules["typeguard"] = tg
+    out = None
+    for dotted, rel in (("serenade.utils.masking", "serenade/utils/masking.py"),
+                        ("serenade.modules.gst.attention", "serenade/modules/gst/attention.py"),
+                        ("serenade.modules.gst.style_encoder", "serenade/modules/gst/style_encoder.py"),
+                        ("serenade.models.serenade", "serenade/models/serenade.py")):
+        spec = importlib.util.spec_from_file_location(dotted, os.path.join(REFERENCE_ROOT, rel))
+        m = importlib.util.module_from_spec(spec)
+        sys.modules[dotted] = m
+        spec.loader.exec_module(m)
+        out = m
+    _cache["srn"] = out
+    return out
+
+
+def build_reference_serenade(**kw):
+    """Serenade() with the ssc1 recipe's parameters (conf/serenade.yaml: all constructor defaults)."""
+    return load_reference_serenade().Serenade(**kw).eval()

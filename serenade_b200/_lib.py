@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_PKG, f"libserenade_b200_{_VARIANT}.so" if _VARIANT else
 EXPORTED_SYMBOLS = [
     "srn_last_error", "srn_version", "srn_create", "srn_destroy", "srn_load_weight", "srn_finalize_weights",
     "srn_estimator_forward", "srn_solve_euler", "srn_solve_euler_host", "srn_launch_count", "srn_set_use_graph",
-    "srn_debug_enable", "srn_debug_fetch", "srn_profile_ops",
+    "srn_debug_enable", "srn_debug_fetch", "srn_profile_ops", "srn_content_encode", "srn_style_encode",
 ]
 
 PRECISION_BF16 = 0
@@ -58,6 +58,8 @@ def load_library() -> C.CDLL:
     lib.srn_debug_enable.argtypes = [vp, i32]
     lib.srn_debug_fetch.argtypes = [vp, C.c_char_p, f32p, i64, C.POINTER(i64), C.POINTER(i32), C.POINTER(i32)]
     lib.srn_profile_ops.argtypes = [vp, i32, i32, i32, C.c_char_p, i64]
+    lib.srn_content_encode.argtypes = [vp, f32p, i32, i32, f32p, vp]
+    lib.srn_style_encode.argtypes = [vp, f32p, i32, i32, f32p, vp]
     for name in EXPORTED_SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("srn_last_error", "srn_launch_count", "srn_version"):

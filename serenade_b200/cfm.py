@@ -127,6 +127,7 @@ class Decoder(nn.Module):
         self.initialize_weights()
         self._engine: Optional[_Engine] = None
         self._synced_version = None
+        self._extra_state = None      # set by models.Serenade: callable -> {key: tensor} of encoder.* / gst.* weights
 
     def initialize_weights(self):
         """Same distributions as reference decoder.py:366-382 (+ torch defaults for the ConvTranspose1d)."""
@@ -146,7 +147,10 @@ class Decoder(nn.Module):
 
     # ---------------------------------------------------------------- engine plumbing
     def _weights_version(self):
-        return tuple(p._version for p in self.parameters()) + tuple(p.data_ptr() for p in self.parameters())
+        ts = list(self.parameters())
+        if self._extra_state is not None:
+            ts += list(self._extra_state().values())
+        return tuple(p._version for p in ts) + tuple(p.data_ptr() for p in ts)
 
     def engine(self, device: torch.device) -> _Engine:
         device = torch.device(device)
@@ -163,6 +167,8 @@ class Decoder(nn.Module):
             self._synced_version = None
         if self._synced_version != ver:
             sd = {"estimator." + k: v for k, v in self.state_dict().items()}
+            if self._extra_state is not None:
+                sd.update(self._extra_state())
             self._engine.load_state_dict(sd)
             self._synced_version = ver
         return self._engine

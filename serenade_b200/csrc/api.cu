@@ -145,6 +145,22 @@ SRN_EXPORT int srn_solve_euler_host(SrnHandle* h, const float* z_host, const flo
   SRN_API_END
 }
 
+SRN_EXPORT int srn_content_encode(SrnHandle* h, const float* x, int32_t B, int32_t L, float* out, void* stream) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (x == nullptr || out == nullptr) srn::fail("srn_content_encode: null pointer");
+  h->eng->content_encode(x, B, L, out, static_cast<cudaStream_t>(stream));
+  SRN_API_END
+}
+
+SRN_EXPORT int srn_style_encode(SrnHandle* h, const float* logmel, int32_t B, int32_t L, float* out, void* stream) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (logmel == nullptr || out == nullptr) srn::fail("srn_style_encode: null pointer");
+  h->eng->style_encode(logmel, B, L, out, static_cast<cudaStream_t>(stream));
+  SRN_API_END
+}
+
 SRN_EXPORT int64_t srn_launch_count(const SrnHandle* h) { return (h && h->eng) ? h->eng->launches : -1; }
 
 SRN_EXPORT int srn_set_use_graph(SrnHandle* h, int32_t enable) {

@@ -4,6 +4,7 @@
 #include "engine_weights.inl"
 #include "engine_plan.inl"
 #include "engine_run.inl"
+#include "engine_frontend.inl"
 
 namespace srn {
 

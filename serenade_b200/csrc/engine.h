@@ -32,6 +32,8 @@ class EngineBase {
   virtual void solve_euler_host(const float* z, const float* mu, const uint8_t* mask, const float* spk,
                                 const float* t_span, int n_steps, int B, int T, float* mel_out, cudaStream_t st) = 0;
   virtual std::string profile_ops(int B, int T, int reps) = 0;
+  virtual void content_encode(const float* x, int B, int L, float* out, cudaStream_t st) = 0;
+  virtual void style_encode(const float* mel, int B, int L, float* out, cudaStream_t st) = 0;
   int64_t launches = 0;
   bool use_graph = true;
   bool debug = false;

@@ -8,6 +8,7 @@
 
 #include "engine.h"
 #include "rowops.cuh"
+#include "frontops.cuh"
 
 namespace srn {
 
@@ -119,6 +120,8 @@ class Engine : public EngineBase {
   void solve_euler_host(const float* z, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
                         int n_steps, int B, int T, float* mel_out, cudaStream_t st) override;
   std::string profile_ops(int B, int T, int reps) override;
+  void content_encode(const float* x, int B, int L, float* out, cudaStream_t st) override;
+  void style_encode(const float* mel, int B, int L, float* out, cudaStream_t st) override;
 
  private:
   static constexpr int BK = OpTraits<OT>::kBK;
@@ -136,6 +139,22 @@ class Engine : public EngineBase {
   float *final_g_ = nullptr, *final_be_ = nullptr;
   OT* proj_w_ = nullptr;
   float* proj_b_ = nullptr;
+  // conditioning front half (engine_frontend.inl); optional: present only if encoder.* / gst.* weights were loaded
+  struct FrontW {
+    bool present = false;
+    int in_dim = 0, in_pad = 0, enc_out = 0;
+    OT* w_in = nullptr;   float* b_in = nullptr;          // k7 conv [512][7 * in_pad]
+    struct { OT* w3 = nullptr; float* b3 = nullptr; OT* w1sc = nullptr; float* b1sc = nullptr; } blk[2];
+    OT* w_out = nullptr;  float* b_out = nullptr;         // k7 conv [80][7 * 512]
+    OT* gw[6] = {};       float* gb[6] = {};              // GST convs, BatchNorm folded: [Cout][Kp]
+    int gc[7] = {}, gkp[6] = {}, gst_f = 0, ntok = 0;
+    float *w_ihT = nullptr, *b_ih = nullptr, *w_hhT = nullptr, *b_hh = nullptr;
+    float *wq = nullptr, *bq = nullptr, *kmat = nullptr, *vmat = nullptr, *wo = nullptr, *bo = nullptr;
+  } front_;
+  DevBuf fb_xpad_, fb_h_, fb_h2_, fb_apad_, fb_e_, fb_col_, fb_act0_, fb_act1_;
+  void pack_frontend();
+  void front_gemm(GemmParams& gp, const OT* W, int N, int K, const float* bias, int M, int nbatch, bool f32_out,
+                  void* out, long long out_bstride, int ldo, float slope, cudaStream_t st);
   std::list<Plan<OT>> plans_;
   bool blend_active_ = false;
   cudaStream_t capture_stream_ = nullptr;

@@ -29,6 +29,7 @@ GemmParams Engine<OT>::base_gemm(const Plan<OT>& pl, int level) const {
   memset(&gp, 0, sizeof gp);
   gp.HB = 1;
   gp.alpha = 1.0f;
+  gp.act_slope = 1.0f;
   gp.M = pl.lv[level].T;
   gp.mask_step = 1;
   return gp;
@@ -50,7 +51,7 @@ void set_B_weight(GemmParams& gp, const OT* W, int N, int K, int bn) {
   gp.b_batch_mode = 0;
   if (OpTraits<OT>::kTF32) {
     const int n = gp.nseg;
-    if (2 * n > 12) fail("too many K segments");
+    if (2 * n > 16) fail("too many K segments");
     for (int i = 0; i < n; ++i) gp.seg[n + i] = gp.seg[i];
     gp.nseg = 2 * n;
     gp.nkb *= 2;
@@ -63,7 +64,7 @@ void set_D(GemmParams& gp, const T* ptr, int cols, int rows, long long bstride, 
   gp.out_cols = cols;
 }
 inline void add_seg(GemmParams& gp, int src, int col0, int shift, int nblk) {
-  if (gp.nseg >= 12) fail("too many K segments");
+  if (gp.nseg >= 16) fail("too many K segments");
   gp.seg[gp.nseg++] = KSeg{src, col0, shift, nblk};
   gp.nkb += nblk;
 }

@@ -38,7 +38,7 @@ Engine<OT>::~Engine() {
 
 template <typename OT>
 void Engine<OT>::load_weight(const std::string& key, const float* data, int ndim, const int64_t* dims) {
-  if (ndim < 1 || ndim > 3) fail("weight %s: ndim %d not supported", key.c_str(), ndim);
+  if (ndim < 1 || ndim > 4) fail("weight %s: ndim %d not supported", key.c_str(), ndim);
   HostTensor t;
   size_t n = 1;
   for (int i = 0; i < ndim; ++i) {
@@ -53,8 +53,9 @@ void Engine<OT>::load_weight(const std::string& key, const float* data, int ndim
 
 template <typename OT>
 const HostTensor& Engine<OT>::hw(const std::string& key, std::initializer_list<int64_t> dims) {
-  auto it = host_w_.find("estimator." + key);
-  if (it == host_w_.end()) fail("missing weight 'estimator.%s'", key.c_str());
+  const bool front = key.compare(0, 8, "encoder.") == 0 || key.compare(0, 4, "gst.") == 0;
+  auto it = host_w_.find(front ? key : "estimator." + key);
+  if (it == host_w_.end()) fail("missing weight '%s%s'", front ? "" : "estimator.", key.c_str());
   if (it->second.dims != std::vector<int64_t>(dims)) {
     std::string got, want;
     for (auto d : it->second.dims) got += std::to_string(d) + ",";
@@ -243,8 +244,11 @@ void Engine<OT>::finalize_weights() {
     proj_b_ = up_f32(pb);
   }
   const size_t expected = 4 + resnets_.size() * 16 + tfms_.size() * 13 + 4 * 2 + 4 + 2;
-  if (host_w_.size() != expected)
-    fail("state dict has %zu tensors, the decoder expects %zu (unexpected extra keys?)", host_w_.size(), expected);
+  size_t n_est = 0;
+  for (const auto& kv : host_w_) n_est += kv.first.compare(0, 10, "estimator.") == 0;
+  if (n_est != expected)
+    fail("state dict has %zu estimator tensors, the decoder expects %zu (unexpected extra keys?)", n_est, expected);
+  pack_frontend();      // optional encoder.* / gst.* weights of the conditioning front half
   host_w_.clear();
   SRN_CUDA(cudaDeviceSynchronize());
   finalized_ = true;

@@ -42,7 +42,7 @@ struct GemmParams {
   CUtensorMap mapB;
   CUtensorMap mapD;    // output tile store: box = 32 rows x 128 bytes, SWIZZLE_128B (all epilogues but EULER)
   CUtensorMap mapD2;   // EPI_QKV: V^T store, box = 32 (d rows) x 32 (s, contiguous), no swizzle
-  KSeg seg[12];
+  KSeg seg[16];
   int nseg;
   int nkb;          // total K blocks
   int ntn, ntm, nz; // tile grid: N tiles, M tiles, batch entries (persistent CTAs loop over ntn*ntm*nz tiles)
@@ -57,6 +57,7 @@ struct GemmParams {
   int b_batch_mode; // 0 -> 0 (weights), 1 -> b, 2 -> z
   int epi;
   float alpha;
+  float act_slope;  // EPI_STORE_OT: out = (v > 0 ? v : act_slope * v) after the bias (1 = identity, 0.2 = LeakyReLU, 0 = ReLU)
   const float* bias;
   const uint8_t* rowmask;  // may be null
   int mask_bstride;        // bytes per batch entry

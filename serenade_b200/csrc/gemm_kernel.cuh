@@ -61,6 +61,10 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     stager_put<float, 32>(st, lane, v);
     stager_flush<float>(st, lane, p, nc + h * p.d_hcol, row0, batch);
   } else if constexpr (EPI == EPI_STORE_OT) {
+    if (p.act_slope != 1.0f) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.act_slope;
+    }
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] *= mk;
     round_op(v);

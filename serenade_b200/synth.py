@@ -210,3 +210,92 @@ def estimator_flops(L: int) -> float:
     """Algorithmic FLOPs of one estimator call on one utterance of L valid frames."""
     L2 = (L + 1) // 2
     return 2.0 * (20_983_808 * L + 39_321_600 * L2) + 8192.0 * (2 * L * L + 4 * L2 * L2) + 25.1e6
+
+
+# ------------------------------------------------------------------------------------------------------------
+# Conditioning front half (SURVEY.md 8f-1): content encoder + GST style encoder of `Serenade` (serenade.py:59-73)
+
+def frontend_param_shapes(input_dim: int = 768, hidden: int = 512, out_dim: int = 80,
+                          gst_chans: Sequence[int] = (128, 128, 256, 256, 512, 512), gst_tokens: int = 50,
+                          gst_dim: int = 256, gru_units: int = 128, heads: int = 4) -> "OrderedDict[str, Tuple[int, ...]]":
+    """Keys / shapes of `encoder.*` and `gst.*` in the reference `Serenade` state dict (old-style weight_norm:
+    weight_g (O,1,1) + weight_v (O,I,k))."""
+    out: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
+
+    def wn(name, o, i, k):
+        out[name + ".bias"] = (o,)
+        out[name + ".weight_g"] = (o, 1, 1)
+        out[name + ".weight_v"] = (o, i, k)
+
+    wn("encoder.model.1", hidden, input_dim, 7)
+    for idx in (2, 3):
+        wn(f"encoder.model.{idx}.block.2", hidden, hidden, 3)
+        wn(f"encoder.model.{idx}.block.4", hidden, hidden, 1)
+        wn(f"encoder.model.{idx}.shortcut", hidden, hidden, 1)
+    wn("encoder.model.6", out_dim, hidden, 7)
+    cin, f = 1, 80
+    for i, c in enumerate(gst_chans):
+        out[f"gst.ref_enc.convs.{3 * i}.weight"] = (c, cin, 3, 3)
+        for nm in ("weight", "bias", "running_mean", "running_var"):
+            out[f"gst.ref_enc.convs.{3 * i + 1}.{nm}"] = (c,)
+        out[f"gst.ref_enc.convs.{3 * i + 1}.num_batches_tracked"] = ()
+        cin, f = c, (f - 1) // 2 + 1
+    gin = f * gst_chans[-1]
+    out["gst.ref_enc.gru.weight_ih_l0"] = (3 * gru_units, gin)
+    out["gst.ref_enc.gru.weight_hh_l0"] = (3 * gru_units, gru_units)
+    out["gst.ref_enc.gru.bias_ih_l0"] = (3 * gru_units,)
+    out["gst.ref_enc.gru.bias_hh_l0"] = (3 * gru_units,)
+    dk = gst_dim // heads
+    out["gst.stl.gst_embs"] = (gst_tokens, dk)
+    for nm, i in (("linear_q", gru_units), ("linear_k", dk), ("linear_v", dk), ("linear_out", gst_dim)):
+        out[f"gst.stl.mha.{nm}.weight"] = (gst_dim, i)
+        out[f"gst.stl.mha.{nm}.bias"] = (gst_dim,)
+    return out
+
+
+def make_frontend_state_dict(seed: int = 0) -> "OrderedDict[str, torch.Tensor]":
+    """Random `encoder.*` / `gst.*` parameters in torch's default-init ranges (uniform +-1/sqrt(fan_in); weight_g
+    jittered around ||v||; BatchNorm running statistics away from (0, 1) so that eval-mode folding is exercised)."""
+    rng = np.random.Generator(np.random.PCG64(seed + 7919))
+    sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+    shapes = frontend_param_shapes()
+    for key, shape in shapes.items():
+        if key.endswith("num_batches_tracked"):
+            sd[key] = torch.tensor(100, dtype=torch.long)
+        elif key.endswith("weight_g"):
+            continue            # filled after its weight_v
+        elif key.endswith("weight_v"):
+            fan_in = shape[1] * shape[2]
+            v = _uniform(rng, shape, 1.0 / math.sqrt(fan_in))
+            sd[key] = v
+            g = v.flatten(1).norm(dim=1).view(-1, 1, 1)
+            sd[key[:-1] + "g"] = g * torch.from_numpy(rng.uniform(0.8, 1.25, size=(shape[0], 1, 1)).astype(np.float32))
+        elif key.endswith("running_var"):
+            sd[key] = torch.from_numpy(rng.uniform(0.5, 1.5, size=shape).astype(np.float32))
+        elif key.endswith("running_mean"):
+            sd[key] = 0.1 * torch.from_numpy(rng.standard_normal(shape, dtype=np.float32))
+        elif ".convs." in key and key.endswith(".weight") and len(shape) == 1:
+            sd[key] = torch.from_numpy(rng.uniform(0.8, 1.2, size=shape).astype(np.float32))
+        elif key == "gst.stl.gst_embs":
+            sd[key] = torch.from_numpy(rng.standard_normal(shape, dtype=np.float32))
+        elif len(shape) >= 2:
+            fan_in = int(np.prod(shape[1:]))
+            if ".convs." in key:
+                sd[key] = _kaiming(rng, shape, fan_in)          # keeps ReLU activations O(1) through six layers
+            else:
+                sd[key] = _uniform(rng, shape, 1.0 / math.sqrt(fan_in))
+        else:
+            sd[key] = 0.1 * torch.from_numpy(rng.standard_normal(shape, dtype=np.float32))
+    return OrderedDict((k, sd[k]) for k in shapes)
+
+
+def make_frontend_inputs(src_len: int, ref_len: int, seed: int = 99, batch: int = 1, input_dim: int = 768):
+    """Synthetic `Serenade.inference` inputs: cvec-like content features, MIDI score and loudness in [0, 1]
+    (audio_mel_dataset.py:104-110), reference log-mel ~ N(0, 1) (normalised features)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    n = lambda *s: torch.from_numpy(rng.standard_normal(s, dtype=np.float32))
+    u = lambda *s: torch.from_numpy(rng.uniform(0.0, 1.0, size=s).astype(np.float32))
+    return dict(x=n(batch, src_len, input_dim), lengths=torch.full((batch,), src_len, dtype=torch.long),
+                midi=u(batch, src_len, 1), lft=u(batch, src_len, 1),
+                ref_x=n(batch, ref_len, input_dim), ref_lengths=torch.full((batch,), ref_len, dtype=torch.long),
+                ref_logmel=n(batch, ref_len, 80), ref_midi=u(batch, ref_len, 1), ref_lft=u(batch, ref_len, 1))
