@@ -126,8 +126,9 @@ class Decoder(nn.Module):
             _attach(self, key[len("estimator."):], nn.Parameter(torch.empty(shape), requires_grad=False))
         self.initialize_weights()
         self._engine: Optional[_Engine] = None
-        self._synced_version = None
+        self._dirty = True            # packed device copies are stale: set by load_state_dict / .to() / mark_weights_dirty()
         self._extra_state = None      # set by models.Serenade: callable -> {key: tensor} of encoder.* / gst.* weights
+        self.register_load_state_dict_post_hook(lambda module, _keys: module.mark_weights_dirty())
 
     def initialize_weights(self):
         """Same distributions as reference decoder.py:366-382 (+ torch defaults for the ConvTranspose1d)."""
@@ -146,11 +147,14 @@ class Decoder(nn.Module):
                     p.zero_()
 
     # ---------------------------------------------------------------- engine plumbing
-    def _weights_version(self):
-        ts = list(self.parameters())
-        if self._extra_state is not None:
-            ts += list(self._extra_state().values())
-        return tuple(p._version for p in ts) + tuple(p.data_ptr() for p in ts)
+    def mark_weights_dirty(self):
+        """The packed / bf16 device copies are derived buffers: they are rebuilt on the next call after
+        `load_state_dict` or `.to()` (both tracked here).  Call this after modifying a parameter in place by hand."""
+        self._dirty = True
+
+    def _apply(self, fn, *args, **kwargs):
+        self._dirty = True
+        return super()._apply(fn, *args, **kwargs)
 
     def engine(self, device: torch.device) -> _Engine:
         device = torch.device(device)
@@ -159,18 +163,17 @@ class Decoder(nn.Module):
                                f"Got tensors on '{device}'.")
         if device.index is None:
             device = torch.device("cuda", torch.cuda.current_device())
-        ver = self._weights_version()
         if self._engine is None or self._engine.device != device:
             if self._engine is not None:
                 self._engine.close()
             self._engine = _Engine(self.geom, self.precision, device)
-            self._synced_version = None
-        if self._synced_version != ver:
+            self._dirty = True
+        if self._dirty:
             sd = {"estimator." + k: v for k, v in self.state_dict().items()}
             if self._extra_state is not None:
                 sd.update(self._extra_state())
             self._engine.load_state_dict(sd)
-            self._synced_version = ver
+            self._dirty = False
         return self._engine
 
     def _check_inputs(self, x, mask, mu, spk):

@@ -66,15 +66,28 @@ class Serenade(nn.Module):
         self.cfm_decoder = CFM(in_channels=conditioning_dim + output_dim, out_channels=output_dim,
                                spk_embed_dim=gst_embed_dim, decoder_channels=(decoder_channels, decoder_channels),
                                decoder_attention_head_dim=decoder_attention_head_dim, precision=precision)
+        self._front_refs = None
         self.cfm_decoder.estimator._extra_state = self._frontend_state
+        self.register_load_state_dict_post_hook(lambda module, _keys: module.cfm_decoder.estimator.mark_weights_dirty())
 
     # ------------------------------------------------------------------ engine plumbing
     def _frontend_state(self) -> Dict[str, torch.Tensor]:
-        out = {}
-        for k, v in self.state_dict().items():
-            if (k.startswith("encoder.") or k.startswith("gst.")) and v.dim() > 0:
-                out[k] = v
-        return out
+        """encoder.* / gst.* tensors by reference key (0-d BatchNorm counters are not part of the C ABI).  Looked up
+        through (module, attribute) pairs cached once: `state_dict()` per call costs more than the kernels at B=1."""
+        if self._front_refs is None:
+            refs = []
+            for prefix in ("encoder", "gst"):
+                root = self._modules[prefix]
+                for mname, mod in root.named_modules():
+                    for kind in (mod._parameters, mod._buffers):
+                        for pname in kind:
+                            refs.append((".".join(x for x in (prefix, mname, pname) if x), kind, pname))
+            self._front_refs = refs
+        return {key: store[name] for key, store, name in self._front_refs if store[name].dim() > 0}
+
+    def _apply(self, fn, *args, **kwargs):
+        self.cfm_decoder.estimator.mark_weights_dirty()
+        return super()._apply(fn, *args, **kwargs)
 
     def _engine(self, device):
         return self.cfm_decoder.estimator.engine(device)

@@ -193,3 +193,17 @@ def test_bad_arguments_raise(cfm_jitter, dev):
         cfm_jitter.solve_euler(b.z.to(dev), b.t_span[:1].to(dev), b.mu.to(dev), b.mask.to(dev), b.spks.to(dev))
     with pytest.raises(RuntimeError):
         cfm_jitter.solve_euler(b.z, b.t_span, b.mu, b.mask, b.spks)      # CPU tensors: no fallback
+
+
+def test_reloading_weights_takes_effect(jitter_sd, stock_sd, dev):
+    """Packed device weights are derived buffers: rebuilt after load_state_dict (dirty tracking, no per-call scan)."""
+    import serenade_b200 as S
+    cfm = _make_cfm(jitter_sd)
+    b = S.make_batch([80], n_steps=2, seed=6)
+    args = (b.z.to(dev), b.t_span.to(dev), b.mu.to(dev), b.mask.to(dev), b.spks.to(dev))
+    x1 = cfm.solve_euler(*args)
+    cfm.load_state_dict(stock_sd, strict=True)
+    x2 = cfm.solve_euler(*args)
+    x3 = _make_cfm(stock_sd).solve_euler(*args)
+    assert not torch.equal(x1, x2)
+    assert torch.equal(x2, x3)
