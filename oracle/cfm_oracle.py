@@ -44,7 +44,7 @@ def _time_embedding(sd, t: torch.Tensor, in_channels: int) -> torch.Tensor:
         t = t.unsqueeze(0)
     half = in_channels // 2
     e = math.log(10000) / (half - 1)
-    freqs = torch.exp(torch.arange(half).float() * -e)
+    freqs = torch.exp(torch.arange(half, device=t.device).float() * -e)
     emb = 1000 * t.unsqueeze(1) * freqs.unsqueeze(0)
     emb = torch.cat((emb.sin(), emb.cos()), dim=-1)
     # decoder.py:145-157: linear_1 -> SiLU -> linear_2

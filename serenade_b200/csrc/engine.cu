@@ -10,9 +10,14 @@ namespace srn {
 
 template <typename OT, int BN, int EPI>
 static void configure_one() {
-  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 GemmCfg<BN>::kSmemBytes));
-  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
+  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
+#if SRN_MC
+  if (BN == 256)
+    SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, 256, EPI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  GemmCfg<256>::kSmemBytes));
+#endif
 }
 
 template <typename OT, int BN>

@@ -185,6 +185,7 @@ class Engine : public EngineBase {
   void prepass(Plan<OT>& pl, const std::vector<float>& ts, const std::vector<float>& dts, cudaStream_t st);
   void solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bool blend, cudaStream_t st);
   void capture_tap(const Plan<OT>& pl, const Tap& tap, cudaStream_t st);
+  void check_abort();
 };
 
 }  // namespace srn

@@ -38,7 +38,7 @@ GemmParams Engine<OT>::base_gemm(const Plan<OT>& pl, int level) const {
 namespace {
 template <typename OT>
 void set_A(GemmParams& gp, int idx, const OT* ptr, int cols, int rows, long long alloc_rows, int ld, int nbatch) {
-  gp.mapA[idx] = make_tmap_3d(ptr, sizeof(OT), cols, rows, nbatch, ld, (uint64_t)alloc_rows * ld, OpTraits<OT>::kBK, 128);
+  gp.mapA[idx] = make_tmap_3d(ptr, sizeof(OT), cols, rows, nbatch, ld, (uint64_t)alloc_rows * ld, OpTraits<OT>::kBK, SRN_MC ? 64 : 128);
   if (idx == 0) gp.mapA[1] = gp.mapA[0];
 }
 // Call after every add_seg of the op.  TF32 mode: the packed weight rows are [hi | lo] (engine_weights.inl: up_w),
@@ -245,7 +245,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     op.gp = base_gemm(pl, level);
     GemmParams& gp = op.gp;
     gp.HB = H;
-    gp.mapA[0] = make_tmap_3d(P, sizeof(OT), S, S, (uint64_t)B * H, Sp, (uint64_t)S * Sp, BK, 128);
+    gp.mapA[0] = make_tmap_3d(P, sizeof(OT), S, S, (uint64_t)B * H, Sp, (uint64_t)S * Sp, BK, SRN_MC ? 64 : 128);
     gp.mapA[1] = gp.mapA[0];
     gp.a_zbatch = 1;
     add_seg(gp, 0, 0, 0, cdiv(S, BK));

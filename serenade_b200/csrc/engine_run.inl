@@ -34,11 +34,8 @@ static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t
   gp.ntn = (int)grid.x;
   gp.ntm = (int)grid.y;
   gp.nz = (int)grid.z;
-  const long long tiles = (long long)grid.x * grid.y * grid.z;                 // 256 x BN tiles, one per CTA pair
-  const unsigned pairs = (unsigned)std::min<long long>(tiles, num_sms / 2);    // persistent: one pair per SM pair
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof cfg);
-  cfg.gridDim = dim3(2 * pairs);
   cfg.blockDim = dim3(GemmCfg<BN>::kThreads);
   cfg.dynamicSmemBytes = GemmCfg<BN>::kSmemBytes;
   cfg.stream = st;
@@ -51,7 +48,33 @@ static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
-  SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, BN, EPI>, gp));
+#if SRN_MC
+  if (BN == 256) {
+    // clusters of two CTA pairs on adjacent N tiles, A multicast between them (gemm_mainloop.cuh)
+    static const int max_clusters = [&] {
+      cudaLaunchConfig_t q = cfg;
+      q.gridDim = dim3(4 * 64);
+      cudaLaunchAttribute a4 = attr[0];
+      a4.val.clusterDim.x = 4;
+      q.attrs = &a4;
+      q.numAttrs = 1;
+      int n = 0;
+      SRN_CUDA(cudaOccupancyMaxActiveClusters(&n, gemm_kernel<OT, 256, EPI, true>, &q));
+      if (getenv("SRN_VERBOSE")) fprintf(stderr, "[srn] 4-CTA clusters resident: %d\n", n);
+      return n;
+    }();
+    const long long units = (long long)((grid.x + 1) / 2) * grid.y * grid.z;
+    const unsigned ncl = (unsigned)std::min<long long>(units, max_clusters);
+    attr[0].val.clusterDim.x = 4;
+    cfg.gridDim = dim3(4 * ncl);
+    SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, 256, EPI, true>, gp));
+    return;
+  }
+#endif
+  const long long tiles = (long long)grid.x * grid.y * grid.z;                 // 256 x BN tiles, one per CTA pair
+  const unsigned pairs = (unsigned)std::min<long long>(tiles, num_sms / 2);    // persistent: one pair per SM pair
+  cfg.gridDim = dim3(2 * pairs);
+  SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, BN, EPI, false>, gp));
 }
 
 template <typename OT, int BN>
@@ -172,6 +195,18 @@ void Engine<OT>::run_forward(Plan<OT>& pl, int step, float* v_out, bool update_x
   for (Op& op : pl.ops) launch_op(pl, op, step, v_out, update_x, st);
 }
 
+// Reads (and clears) the device-side soft-abort flag of ptx.cuh: mbar_wait.  Call only after a synchronisation.
+template <typename OT>
+void Engine<OT>::check_abort() {
+  int flag = 0;
+  SRN_CUDA(cudaMemcpyFromSymbol(&flag, g_srn_abort, sizeof flag));
+  if (flag != 0) {
+    const int zero = 0;
+    SRN_CUDA(cudaMemcpyToSymbol(g_srn_abort, &zero, sizeof zero));
+    fail("a GEMM pipeline barrier timed out on the device (soft abort %d): results of the last calls are invalid", flag);
+  }
+}
+
 template <typename OT>
 void Engine<OT>::stage_inputs(Plan<OT>& pl, const float* x, const float* mu, const uint8_t* mask, const float* spk,
                               cudaMemcpyKind kind, cudaStream_t st) {
@@ -275,6 +310,7 @@ void Engine<OT>::solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bo
   SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, ts.data(), (size_t)n_steps * 4, cudaMemcpyHostToDevice, st));
   SRN_CUDA(cudaMemcpyAsync(pl.dts.p, dts.data(), (size_t)n_steps * 4, cudaMemcpyHostToDevice, st));
   SRN_CUDA(cudaStreamSynchronize(st));   // ts / dts are host temporaries
+  check_abort();                         // (reports a timeout of an earlier asynchronous solve)
   blend_active_ = blend;
   if (use_graph && !debug) {
     if (pl.graph == nullptr || pl.graph_steps != n_steps || pl.graph_blend != blend) {
@@ -335,6 +371,7 @@ void Engine<OT>::solve_euler_host(const float* z, const float* mu, const uint8_t
   solve_staged(pl, t_span, n_steps, false, st);
   SRN_CUDA(cudaMemcpyAsync(mel_out, pl.x_state.p, (size_t)B * cfg_.out_channels * T * 4, cudaMemcpyDeviceToHost, st));
   SRN_CUDA(cudaStreamSynchronize(st));
+  check_abort();
 }
 
 }  // namespace srn

@@ -14,6 +14,12 @@
 
 #include "ptx.cuh"
 
+// Build-time experiment (python -m serenade_b200.build --variant mc -DSRN_MC=1): BN = 256 GEMMs run as clusters of two
+// CTA pairs with the A operand multicast between them (gemm_mainloop.cuh).
+#ifndef SRN_MC
+#define SRN_MC 0
+#endif
+
 namespace srn {
 
 enum EpiMode : int {

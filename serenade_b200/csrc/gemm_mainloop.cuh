@@ -3,7 +3,13 @@
 
 namespace srn {
 
-template <typename OT, int BN, int EPI>
+// MC = A-operand multicast: clusters of FOUR CTAs = two CTA pairs that work on the same 256 output rows and on
+// adjacent N tiles.  The CTAs with the same rank inside their pair need the same 128 rows of A: each loads 64 of them
+// and multicasts to both (cp.async.bulk.tensor ... .cta_group::2 ... .multicast::cluster; the bytes complete on the
+// full barrier of the destination's own pair leader), which removes a quarter of the operand traffic of every k-block
+// (the SM<->L2 fabric, not the tensor pipe, bounds this kernel: DESIGN.md 3.1).  A stage is free when BOTH pairs have
+// consumed it (empty barriers count two commits, multicast to all four CTAs).
+template <typename OT, int BN, int EPI, bool MC>
 __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
   using TR = OpTraits<OT>;
   using CFG = GemmCfg<BN>;
@@ -23,11 +29,16 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int tiles_mn = p.ntn * p.ntm;
-  const int total_tiles = tiles_mn * p.nz;
-  const uint32_t rank = cluster_ctarank();      // 0 = leader of the pair
-  const int pair0 = blockIdx.x >> 1;
-  const int npairs = gridDim.x >> 1;
+  constexpr int CL = MC ? 4 : 2;                 // CTAs per cluster
+  const int ntn_u = MC ? (p.ntn + 1) / 2 : p.ntn;   // work units along N: single tiles, or pairs of adjacent tiles
+  const int tiles_mn = ntn_u * p.ntm;
+  const int total_tiles = tiles_mn * p.nz;       // units of work per cluster
+  const uint32_t crank = cluster_ctarank();
+  const uint32_t rank = crank & 1u;              // rank inside the CTA pair, 0 = leader (issues the MMAs)
+  const uint32_t pj = MC ? (crank >> 1) : 0u;    // which pair of the cluster: N tile 2 u + pj
+  const uint32_t leader = crank & ~1u;           // cluster rank of this pair's leader
+  const int pair0 = blockIdx.x / CL;
+  const int npairs = gridDim.x / CL;
 
   pdl_launch_dependents();
   if (warp == 0 && elect_one()) {
@@ -39,7 +50,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   if (warp == 1 && elect_one()) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
+      mbar_init(&empty_bar[s], MC ? 2 : 1);
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
@@ -61,8 +72,8 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       for (int tile = pair0; tile < total_tiles; tile += npairs) {
         const int z = tile / tiles_mn;
         const int rem = tile - z * tiles_mn;
-        const int m0 = (rem / p.ntn) * 256 + (int)rank * 128;
-        const int n0 = (rem % p.ntn) * BN;
+        const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
+        const int n0 = ((rem % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN;     // may lie beyond N for the odd last unit (all zero)
         const int b = z / p.HB;
         const int h = z - b * p.HB;
         const int a_batch = p.a_zbatch ? z : b;
@@ -73,14 +84,25 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * CFG::kStageBytes;
           uint8_t* sb = sa + CFG::kABytes;
-          // both CTAs' bytes complete on the LEADER's full barrier; only the leader arms it (for both)
-          const uint32_t fb = map_to_cta(&full_bar[stage], 0);
+          // both CTAs' bytes complete on the pair LEADER's full barrier; only the leader arms it (for both)
+          const uint32_t fb = map_to_cta(&full_bar[stage], leader);
           const KSeg sg = p.seg[seg];
           if (p.dbg_mode & 1) {          // profiling experiment: no operand traffic (results are garbage)
             if (rank == 0) mbar_arrive(&full_bar[stage]);
           } else {
             if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * CFG::kStageBytes);
-            tma_load_3d_2sm(sa, &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol, m0 + sg.shift, a_batch);
+            if constexpr (MC) {
+              // my half (64 rows) of this pair-rank's 128 A rows, to me and to the same-rank CTA of the other pair
+              tma_load_3d_2sm_mc(sa + pj * (CFG::kABytes / 2), &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol,
+                                 m0 + (int)pj * 64 + sg.shift, a_batch, (uint16_t)((1u << rank) | (1u << (rank + 2))));
+            } else {
+              tma_load_3d_2sm(sa, &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol, m0 + sg.shift, a_batch);
+#if SRN_MC
+              // builds with the multicast kernels encode every A map with 64-row boxes
+              tma_load_3d_2sm(sa + CFG::kABytes / 2, &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol,
+                              m0 + 64 + sg.shift, a_batch);
+#endif
+            }
             tma_load_3d_2sm(sb, &p.mapB, fb, p.b_col0 + kb * BK + h * p.b_hcol, b_row, b_batch);
           }
           if (++j == sg.nblk) { j = 0; ++seg; }
@@ -110,10 +132,10 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
             for (int k = 0; k < 4; ++k)   // 4 x 32 bytes of K per 128-byte swizzled row
               umma_pair<TR::kTF32>(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
           }
-          tc_commit_pair(&empty_bar[stage]);     // frees the stage in both CTAs
+          tc_commit_mask(&empty_bar[stage], MC ? 0xF : 0x3);     // frees the stage in both CTAs (MC: one of the two arrivals, in all four)
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        tc_commit_pair(&tfull_bar[as]);          // both CTAs' epilogues may drain their half
+        tc_commit_mask(&tfull_bar[as], (uint16_t)(0x3u << leader));          // both CTAs' epilogues may drain their half
       }
     }
   } else {
@@ -127,14 +149,14 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     const bool has_bias = p.bias != nullptr;
     const bool has_alpha = p.alpha != 1.0f;
     float* bias_s = reinterpret_cast<float*>(smem + CFG::kBiasOff) + (warp - 2) * 128;   // this warp's bias slice
-    const uint32_t tepi_addr = map_to_cta(&tempty_bar[0], 0);
+    const uint32_t tepi_addr = map_to_cta(&tempty_bar[0], leader);
     uint32_t it = 0;
     for (int tile = pair0; tile < total_tiles; tile += npairs, ++it) {
       const int z = tile / tiles_mn;
       const int rem = tile - z * tiles_mn;
-      const int mt = (rem / p.ntn) * 2 + (int)rank;     // 128-row tile index inside the batch entry
+      const int mt = (rem / ntn_u) * 2 + (int)rank;     // 128-row tile index inside the batch entry
       const int m0 = mt * 128;
-      const int n0 = (rem % p.ntn) * BN;
+      const int n0 = ((rem % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN;
       const int b = z / p.HB;
       const int h = z - b * p.HB;
       const uint32_t as = it & 1;
@@ -287,7 +309,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
             const float s = red[(0 * NG + g) * 2 + w] + red[(1 * NG + g) * 2 + w] + red[(2 * NG + g) * 2 + w] +
                             red[(3 * NG + g) * 2 + w];
             const int group = (n0 >> 6) + g;
-            p.gn_part[(((long long)b * (2 * p.ntm) + mt) * 8 + group) * 2 + w] = s;
+            if (n0 < p.N) p.gn_part[(((long long)b * (2 * p.ntm) + mt) * 8 + group) * 2 + w] = s;
           }
         }
       }

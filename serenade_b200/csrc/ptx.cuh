@@ -56,11 +56,23 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded spin: a pipeline bug becomes a trapped kernel (an error the host sees) instead of a hung GPU.
+// Bounded spin with a SOFT abort: if a barrier does not flip within ~2 s (a pipeline / protocol bug), the waiter
+// records a code in g_srn_abort and carries on as if it had flipped.  Every role loop is bounded, so the kernel still
+// tears down cleanly (TMEM deallocated, cluster barrier reached) with garbage results instead of hanging the GPU or
+// trapping (a trap is an Xid on the box); once the flag is set later waits give up after a short spin.  The host
+// reads the flag at its next synchronisation point and fails the call (Engine::check_abort).
+static __device__ int g_srn_abort;
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 26)) __trap();
+    ++spins;
+    if ((spins & 4095u) == 0) {
+      if (*reinterpret_cast<volatile int*>(&g_srn_abort) != 0 && spins > (1u << 14)) return;
+      if (spins > (1u << 26)) {
+        atomicExch(&g_srn_abort, 1);
+        return;
+      }
+    }
   }
 }
 
@@ -201,6 +213,18 @@ __device__ __forceinline__ void tma_load_3d_2sm(void* smem_dst, const CUtensorMa
       ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+// The same, multicast to the CTAs of `cta_mask` (same smem offset in each); with .cta_group::2 every destination's
+// bytes complete on the barrier at `bar_cluster_addr`'s offset in the destination itself or in its pair peer, according
+// to whether `bar_cluster_addr` is the issuing CTA's own barrier or its peer's: here always the pair leader's.
+__device__ __forceinline__ void tma_load_3d_2sm_mc(void* smem_dst, const CUtensorMap* m, uint32_t bar_cluster_addr, int c0,
+                                                   int c1, int c2, uint16_t cta_mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%3, %4, %5}], [%2], %6;"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2),
+      "h"(cta_mask)
+      : "memory");
+}
 template <int kCols>
 __device__ __forceinline__ void tmem_alloc_2sm(uint32_t* smem_result) {
   asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_result)),
@@ -218,6 +242,13 @@ __device__ __forceinline__ void tc_commit_pair(uint64_t* bar) {
       "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
           smem_u32(bar)),
       "h"(static_cast<uint16_t>(3))
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit_mask(uint64_t* bar, uint16_t cta_mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"(cta_mask)
       : "memory");
 }
 template <bool kTF32>

@@ -184,6 +184,59 @@ def test_full_size_c2_properties(cfm_stock, dev):
     assert torch.equal(one[0], x[3])
 
 
+def test_gpu_fp32_oracle_agrees_with_cpu_oracle(jitter_sd, dev):
+    """The oracle's functions in strict fp32 on the GPU are the full-size checker below: pin them to the CPU oracle."""
+    import serenade_b200 as S
+    from oracle import cfm_oracle as O
+    import gpu_eager_reference as E
+    b = S.make_batch([300, 257, 190, 64], n_steps=4, seed=5)
+    with torch.inference_mode():
+        x_cpu = O.solve_euler(jitter_sd, b.z, b.t_span, b.mu, b.mask, b.spks)
+    x_gpu = E.eager_solve(E.to_dev(jitter_sd, dev), b, dev, "fp32").cpu()
+    assert rel_l2(x_gpu, x_cpu) < 1e-5
+
+
+@pytest.mark.parametrize("cfg", ["C1", "C2", "C2_ragged"])
+def test_full_size_parity_against_fp32_oracle_on_gpu(cfg, stock_sd, cfm_stock, cfm_tf32, dev):
+    """BASELINE configs 1 and 2 at their FULL sizes (and config 2 with ragged lengths): every Euler iterate of the
+    bf16 path within 1e-2 and every per-step velocity of the TF32-class path within 1e-3 of the oracle (strict fp32,
+    executed on the GPU because the CPU needs minutes at these sizes)."""
+    import serenade_b200 as S
+    import gpu_eager_reference as E
+    lengths = {"C1": [500], "C2": [1000] * 16,
+               "C2_ragged": [1000, 987, 901, 850, 777, 700, 655, 600, 512, 499, 431, 400, 333, 257, 129, 64]}[cfg]
+    seed = 1234 if cfg == "C1" else 1235
+    b = S.make_batch(lengths, n_steps=10, seed=seed, infill=(0.25, 0.75))
+    sd_dev = E.to_dev(stock_sd, dev)
+    sol = E.eager_solve(sd_dev, b, dev, "fp32", return_all=True)          # x_1 .. x_10
+    args = [b.z.to(dev), b.t_span.to(dev), b.mu.to(dev), b.mask.to(dev), b.spks.to(dev)]
+    x = cfm_stock.solve_euler(*args)
+    e_final = rel_l2(x.cpu(), sol[-1].cpu())
+    # per-step gate along the reference trajectory: v(x_k, t_k) for k = 0, 4, 9
+    tf = cfm_tf32[False]
+    t, dt = b.t_span[0], b.t_span[1] - b.t_span[0]
+    ts = [float(t)]
+    for k in range(1, 10):
+        t = t + dt
+        ts.append(float(t))
+        dt = b.t_span[k + 1] - t
+    errs = []
+    for k in (0, 4, 9):
+        xk = args[0] if k == 0 else sol[k - 1]
+        v_ref = E.eager_velocity(sd_dev, b, dev, xk, ts[k])
+        v = tf.estimator(xk, args[3], args[2], torch.tensor(ts[k]), args[4])
+        errs.append(rel_l2(v.cpu(), v_ref.cpu()))
+    x_tf = tf.solve_euler(*args)
+    e_final_tf = rel_l2(x_tf.cpu(), sol[-1].cpu())
+    _report(f"fullsize_{cfg}.txt", f"{cfg}: bf16 final mel rel_l2={e_final:.3e}; tf32 per-step rel_l2 at steps 0,4,9 = "
+            + ", ".join(f"{e:.3e}" for e in errs) + f"; tf32 final mel rel_l2={e_final_tf:.3e}")
+    assert e_final < BF16_FINAL_TOL
+    assert max(errs) < TF32_STEP_TOL
+    assert e_final_tf < TF32_STEP_TOL
+    pad = ~b.mask.expand_as(b.z)
+    assert torch.equal(x.cpu()[pad], b.z[pad])
+
+
 def test_bad_arguments_raise(cfm_jitter, dev):
     import serenade_b200 as S
     b = S.make_batch([64], n_steps=2, seed=1)
