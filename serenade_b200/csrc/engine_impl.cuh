@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_bf16.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <list>
@@ -120,6 +121,10 @@ class Engine : public EngineBase {
   void solve_euler_host(const float* z, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
                         int n_steps, int B, int T, float* mel_out, cudaStream_t st) override;
   std::string profile_ops(int B, int T, int reps) override;
+#if SRN_TRACE
+  void trace_op(Plan<OT>& pl, Op& op, cudaStream_t st);
+  void trace_row_op(Plan<OT>& pl, Op& op, cudaStream_t st);
+#endif
   void content_encode(const float* x, int B, int L, float* out, cudaStream_t st) override;
   void style_encode(const float* mel, int B, int L, float* out, cudaStream_t st) override;
 

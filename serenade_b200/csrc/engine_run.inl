@@ -97,6 +97,7 @@ static void launch_gemm_bn(const GemmParams& gp, dim3 grid, int num_sms, cudaStr
 template <typename OT>
 void Engine<OT>::launch_gemm(const GemmParams& gp, int bn, dim3 grid, cudaStream_t st) {
   if (gp.nkb < 1 || gp.nseg < 1) fail("gemm with empty K");
+  if (gp.epi == EPI_RESID_F32 && gp.resid != gp.out) fail("EPI_RESID_F32 updates its residual in place (TMA reduce-add)");
   if (bn == 256) launch_gemm_bn<OT, 256>(gp, grid, num_sms_, st);
   else launch_gemm_bn<OT, 128>(gp, grid, num_sms_, st);
   ++launches;
@@ -381,6 +382,108 @@ namespace srn {
 // Per-op timing of one estimator forward (CUDA events around `reps` back-to-back launches of each op).
 // Algorithmic work: GEMM flops = 2 * valid rows * N * K (K as issued, incl. zero padding of C_in 242 -> 256);
 // row-kernel bytes = the tensors they must read and write once.
+#if SRN_TRACE
+// One traced launch of a GEMM op: medians over CTAs of the phase lengths in SM clocks (stderr).
+// stamps: 0 kernel entry, 1 after griddepcontrol.wait, 2 first operand stage landed (leader), 3 last MMA committed
+// (leader), 4 first accumulator ready (epilogue warp 2), 5 last accumulator ready, 6 last chunk staged, 7 stores drained
+template <typename OT>
+void Engine<OT>::trace_op(Plan<OT>& pl, Op& op, cudaStream_t st) {
+  const int ncta = 160;
+  unsigned long long* d = nullptr;
+  SRN_CUDA(cudaMalloc(&d, ncta * 8 * sizeof(unsigned long long)));
+  SRN_CUDA(cudaMemset(d, 0, ncta * 8 * sizeof(unsigned long long)));
+  op.gp.trace = d;
+  launch_op(pl, op, 0, nullptr, true, st);
+  op.gp.trace = nullptr;
+  SRN_CUDA(cudaStreamSynchronize(st));
+  std::vector<unsigned long long> h(ncta * 8);
+  SRN_CUDA(cudaMemcpy(h.data(), d, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  SRN_CUDA(cudaFree(d));
+  auto med = [&](int a, int b, bool leader_only, double* mx) {
+    std::vector<double> v;
+    for (int c = 0; c < ncta; ++c) {
+      if (leader_only && (c & 1)) continue;
+      const unsigned long long ta = h[c * 8 + a], tb = h[c * 8 + b];
+      if (ta == 0 || tb == 0) continue;
+      v.push_back((double)tb - (double)ta);
+    }
+    if (v.empty()) { *mx = 0; return 0.0; }
+    std::sort(v.begin(), v.end());
+    *mx = v.back();
+    return v[v.size() / 2];
+  };
+  double m[8], x[8];
+  m[0] = med(0, 1, false, &x[0]);   // launch overlap: entry -> dependencies resolved
+  m[1] = med(1, 2, true, &x[1]);    // first stage latency
+  m[2] = med(2, 3, true, &x[2]);    // main loops (all tiles)
+  m[3] = med(1, 4, false, &x[3]);   // dependencies resolved -> first accumulator
+  m[4] = med(5, 6, false, &x[4]);   // last tile's epilogue (TMEM -> staged)
+  m[5] = med(6, 7, false, &x[5]);   // store drain
+  m[6] = med(1, 7, false, &x[6]);   // body
+  m[7] = med(0, 7, false, &x[7]);   // whole CTA
+  fprintf(stderr, "[trace] %-18s pdl_wait %6.0f | first stage %6.0f | mainloop %7.0f | ->first acc %7.0f | last epilogue %6.0f (max %6.0f) | "
+                  "drain %6.0f (max %6.0f) | body %7.0f (max %7.0f) | cta %7.0f clk\n",
+          op.name.c_str(), m[0], m[1], m[2], m[3], m[4], x[4], m[5], x[5], m[6], x[6], m[7]);
+}
+#endif
+
+#if SRN_TRACE
+template <typename OT>
+void Engine<OT>::trace_row_op(Plan<OT>& pl, Op& op, cudaStream_t st) {
+  const int nblk = 4096;
+  unsigned long long* d = nullptr;
+  SRN_CUDA(cudaMalloc(&d, (size_t)nblk * 16 * sizeof(unsigned long long)));
+  SRN_CUDA(cudaMemset(d, 0, (size_t)nblk * 16 * sizeof(unsigned long long)));
+  SRN_CUDA(cudaMemcpyToSymbol(g_row_trace, &d, sizeof d));
+  launch_op(pl, op, 0, nullptr, true, st);
+  SRN_CUDA(cudaStreamSynchronize(st));
+  unsigned long long* nul = nullptr;
+  SRN_CUDA(cudaMemcpyToSymbol(g_row_trace, &nul, sizeof nul));
+  std::vector<unsigned long long> h((size_t)nblk * 16);
+  SRN_CUDA(cudaMemcpy(h.data(), d, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  SRN_CUDA(cudaFree(d));
+  std::vector<double> stats_clk, row_clk, body_clk, dur_ns, ph[5];
+  unsigned long long g0 = ~0ull, g1 = 0;
+  int per_sm[256] = {0};
+  int n = 0;
+  for (int i = 0; i < nblk; ++i) {
+    const unsigned long long* t = &h[(size_t)i * 16];
+    if (t[0] == 0 || t[4] == 0) continue;
+    ++n;
+    stats_clk.push_back((double)(t[2] - t[1]));
+    if (t[3] != 0) row_clk.push_back((double)(t[3] - t[2]));
+    body_clk.push_back((double)(t[4] - t[1]));
+    if (t[8] && t[12]) {
+      ph[0].push_back((double)(t[8] - t[2]));
+      ph[1].push_back((double)(t[9] - t[8]));
+      ph[2].push_back((double)(t[10] - t[9]));
+      ph[3].push_back((double)(t[11] - t[10]));
+      ph[4].push_back((double)(t[12] - t[11]));
+    }
+    dur_ns.push_back((double)(t[7] - t[6]));
+    g0 = std::min(g0, t[6]);
+    g1 = std::max(g1, t[7]);
+    ++per_sm[t[5] & 255];
+  }
+  auto med = [](std::vector<double>& v) { if (v.empty()) return 0.0; std::sort(v.begin(), v.end()); return v[v.size() / 2]; };
+  double sum_ns = 0;
+  for (double x : dur_ns) sum_ns += x;
+  int late = 0;
+  for (int i = 0; i < nblk; ++i) {
+    const unsigned long long* t = &h[(size_t)i * 16];
+    if (t[0] != 0 && t[6] > g0 + 3000) ++late;
+  }
+  int mx = 0, used = 0;
+  for (int i = 0; i < 256; ++i) { mx = std::max(mx, per_sm[i]); used += per_sm[i] > 0; }
+  fprintf(stderr, "[trace] %-18s blocks %d on %d SMs (max %d per SM) | stats %5.0f clk | first row %6.0f clk | block body %7.0f clk | "
+                  "span %6.1f us, mean block %5.1f us, mean concurrency %5.1f blocks, %d blocks start > 3 us late\n",
+          op.name.c_str(), n, used, mx, med(stats_clk), med(row_clk), med(body_clk), (double)(g1 - g0) * 1e-3,
+          n ? sum_ns / n * 1e-3 : 0.0, (g1 > g0) ? sum_ns / (double)(g1 - g0) : 0.0, late);
+  fprintf(stderr, "[trace]   first row of warp 0: loads+mish half 0 %6.0f | half 1 %6.0f | speaker LN stats %6.0f | scale + hres store %6.0f | LN stats %6.0f clk\n",
+          med(ph[0]), med(ph[1]), med(ph[2]), med(ph[3]), med(ph[4]));
+}
+#endif
+
 template <typename OT>
 std::string Engine<OT>::profile_ops(int B, int T, int reps) {
   Plan<OT>& pl = get_plan(B, T);
@@ -412,6 +515,10 @@ std::string Engine<OT>::profile_ops(int B, int T, int reps) {
     SRN_CUDA(cudaEventSynchronize(e1));
     float ms = 0.f;
     SRN_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+#if SRN_TRACE
+    if (op.kind == OP_GEMM && getenv("SRN_TRACE") != nullptr) trace_op(pl, op, st);
+    if ((op.kind == OP_GN_RES_SPK_LN || op.kind == OP_GN_APPLY) && getenv("SRN_TRACE") != nullptr) trace_row_op(pl, op, st);
+#endif
     const Level& L = pl.lv[op.level];
     double flops = 0, bytes = 0;
     const char* kind = "";

@@ -19,6 +19,10 @@
 #ifndef SRN_MC
 #define SRN_MC 0
 #endif
+// -DSRN_TRACE=1: gemm_kernel stamps clock64 at its phase boundaries into GemmParams::trace (8 slots per CTA).
+#ifndef SRN_TRACE
+#define SRN_TRACE 0
+#endif
 
 namespace srn {
 
@@ -93,6 +97,7 @@ struct GemmParams {
   int T_cf;         // row length of the channels-first tensors
   int d_hcol;       // output column offset per h (elements), e.g. 512 for the per-head attention output
   int d_zbatch;     // output batch coordinate: 1 -> z, 0 -> b
+  unsigned long long* trace;   // -DSRN_TRACE=1 builds: per-CTA clock64 stamps of the kernel's phases (srn_profile_ops)
   int dbg_mode;     // profiling experiments only (SRN_DBG_MODE, srn_profile_ops): bit 0 = no TMA loads, bit 1 = no MMAs,
                     // bit 2 = no epilogue (results are garbage)
   // EPI_ROWMAX / EPI_EXP / EPI_PV: per-row softmax statistics, one entry per 64-key slice:

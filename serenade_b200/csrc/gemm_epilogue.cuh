@@ -60,7 +60,8 @@ __device__ __forceinline__ void stager_put(Stager& s, int lane, const float (&v)
 #define SRN_DIRECT_STORE 0
 #endif
 template <typename OutT>
-__device__ __forceinline__ void stager_flush(Stager& s, int lane, const GemmParams& p, int col, int row0, int batch) {
+__device__ __forceinline__ void stager_flush(Stager& s, int lane, const GemmParams& p, int col, int row0, int batch,
+                                             bool reduce_add = false) {
   if (s.fill < 128) return;
 #if SRN_DIRECT_STORE
   __syncwarp();
@@ -84,10 +85,19 @@ __device__ __forceinline__ void stager_flush(Stager& s, int lane, const GemmPara
   fence_proxy_async();
   __syncwarp();
   if (lane == 0) {
-    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
-                     reinterpret_cast<uint64_t>(&p.mapD)),
-                 "r"(s.box()), "r"(col), "r"(row0), "r"(batch)
-                 : "memory");
+    if (reduce_add) {
+      // out += box, the addition done by the L2 (f32, every element touched once: deterministic): the residual
+      // stream is updated in place without the SM ever reading it
+      asm volatile("cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                       reinterpret_cast<uint64_t>(&p.mapD)),
+                   "r"(s.box()), "r"(col), "r"(row0), "r"(batch)
+                   : "memory");
+    } else {
+      asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                       reinterpret_cast<uint64_t>(&p.mapD)),
+                   "r"(s.box()), "r"(col), "r"(row0), "r"(batch)
+                   : "memory");
+    }
     tma_store_commit();
   }
 #endif

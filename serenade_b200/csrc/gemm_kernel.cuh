@@ -71,11 +71,11 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     stager_acquire(st, lane);
     stager_put<OT, 32>(st, lane, v);
     stager_flush<OT>(st, lane, p, nc + 32 - kOtCols + h * p.d_hcol, row0, batch);
-  } else if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_RESID_OT) {     // residual already added by the caller
+  } else if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_RESID_OT) {     // RESID_OT: residual already added by the caller
     stager_acquire(st, lane);
-    if constexpr (EPI == EPI_RESID_F32) {
+    if constexpr (EPI == EPI_RESID_F32) {      // out and residual are the same f32 tensor: TMA reduce-add in place
       stager_put<float, 32>(st, lane, v);
-      stager_flush<float>(st, lane, p, nc, row0, batch);
+      stager_flush<float>(st, lane, p, nc, row0, batch, !SRN_DIRECT_STORE);
     } else {
 #pragma unroll
       for (int i = 0; i < 32; ++i) v[i] *= mk;

@@ -9,6 +9,12 @@ namespace srn {
 // full barrier of the destination's own pair leader), which removes a quarter of the operand traffic of every k-block
 // (the SM<->L2 fabric, not the tensor pipe, bounds this kernel: DESIGN.md 3.1).  A stage is free when BOTH pairs have
 // consumed it (empty barriers count two commits, multicast to all four CTAs).
+#if SRN_TRACE
+#define SRN_STAMP(k) do { if (p.trace != nullptr) p.trace[blockIdx.x * 8 + (k)] = (unsigned long long)clock64(); } while (0)
+#else
+#define SRN_STAMP(k) do { } while (0)
+#endif
+
 template <typename OT, int BN, int EPI, bool MC>
 __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
   using TR = OpTraits<OT>;
@@ -41,6 +47,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   const int npairs = gridDim.x / CL;
 
   pdl_launch_dependents();
+  if (threadIdx.x == 0) SRN_STAMP(0);
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&p.mapA[0]);
     tma_prefetch_desc(&p.mapA[1]);
@@ -64,6 +71,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();     // everything above overlapped with the previous kernel's tail
+  if (threadIdx.x == 0) SRN_STAMP(1);
 
   if (warp == 0) {
     if (elect_one()) {
@@ -124,6 +132,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         for (int kb = 0; kb < p.nkb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
+          if (it == 0 && kb == 0) SRN_STAMP(2);
           const uint32_t sa = smem_u32(smem + stage * CFG::kStageBytes);
           const uint64_t da = make_kmajor_sw128_desc(sa);
           const uint64_t db = make_kmajor_sw128_desc(sa + CFG::kABytes);
@@ -136,6 +145,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         tc_commit_mask(&tfull_bar[as], (uint16_t)(0x3u << leader));          // both CTAs' epilogues may drain their half
+        SRN_STAMP(3);
       }
     }
   } else {
@@ -209,7 +219,8 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         if (lane < NCH * 4) *reinterpret_cast<float4*>(bias_s + lane * 4) = bv;
         __syncwarp();
       }
-      constexpr bool kResid = EPI == EPI_RESID_F32 || EPI == EPI_RESID_OT;
+      // (EPI_RESID_F32 adds its residual in the L2 with a TMA reduce-add store: nothing to load)
+      constexpr bool kResid = EPI == EPI_RESID_OT || (EPI == EPI_RESID_F32 && SRN_DIRECT_STORE);
       float4 r4[kResid ? 8 : 1];
       const float4* rs = nullptr;
       if constexpr (kResid) {
@@ -222,6 +233,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       if (p.dbg_mode & 4) nvalid = 0;    // profiling experiment without the epilogue
       mbar_wait(&tfull_bar[as], (it >> 1) & 1);
       tc_fence_after();
+      if (threadIdx.x == 64) { if (it == 0) SRN_STAMP(4); SRN_STAMP(5); }
       uint32_t raw[32];
       if (nvalid > 0) tmem_ld_32x32b_x32(trow, raw);
       else {
@@ -314,7 +326,9 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         }
       }
     }
+    if (threadIdx.x == 64) SRN_STAMP(6);
     if (lane == 0) tma_store_wait_all();     // smem boxes must outlive their bulk stores
+    if (threadIdx.x == 64) SRN_STAMP(7);
   }
   __syncwarp();
   tc_fence_before();

@@ -6,6 +6,10 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#ifndef SRN_TRACE
+#define SRN_TRACE 0     // see gemm.cuh
+#endif
+
 namespace srn {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {

@@ -18,6 +18,35 @@ namespace srn {
 constexpr int kC = 512;         // hidden width of the ssc1 decoder
 constexpr int kGroups = 8;      // GroupNorm groups (decoder.py:67)
 
+#ifndef SRN_GNRES_MINBLOCKS
+#define SRN_GNRES_MINBLOCKS 2
+#endif
+#ifndef SRN_GNRES_PREFETCH
+#define SRN_GNRES_PREFETCH 1
+#endif
+#if SRN_TRACE
+// -DSRN_TRACE=1 builds: per-block stamps of gn_res_spk_ln (8 slots per block: 0-4 clock64 at the phase boundaries,
+// 5 SM id, 6/7 globaltimer at entry/exit); see Engine::trace_op
+static __device__ unsigned long long* g_row_trace;
+__device__ __forceinline__ void row_stamp(int k) {
+  if (g_row_trace == nullptr || threadIdx.x != 0) return;
+  unsigned long long* t = g_row_trace + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 16;
+  t[k] = (unsigned long long)clock64();
+  unsigned long long gt;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt));
+  if (k == 0) {
+    unsigned smid;
+    asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+    t[5] = smid;
+    t[6] = gt;
+  }
+  if (k == 4) t[7] = gt;
+}
+#define ROW_STAMP(k) row_stamp(k)
+#else
+#define ROW_STAMP(k) do { } while (0)
+#endif
+
 __device__ __forceinline__ float mish_f(float x) {
   // x * tanh(softplus(x)) with w = e^x: tanh(ln(1 + w)) = (w^2 + 2w) / (w^2 + 2w + 2)  -- one exp and one
   // division instead of expf + log1pf + tanhf (the row kernels were instruction-bound on those, not HBM-bound).
@@ -144,9 +173,12 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__
   __shared__ float stats[16];
   __shared__ double red[256];
   pdl_launch_dependents();
+  ROW_STAMP(0);
   pdl_wait();
+  ROW_STAMP(1);
   const int b = blockIdx.y;
   gn_reduce_stats(part, b, mtiles, T, stats, red);
+  ROW_STAMP(2);
   const int c = (threadIdx.x & 63) * 8;
   const int g = c >> 6;
   const float mean = stats[2 * g], rstd = stats[2 * g + 1];
@@ -172,6 +204,7 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__
     for (int i = 0; i < 8; ++i) v[i] = (mish_f(v[i] * ga[i] + be[i]) + tb[i]) * m;
     store8_op(out + off, v);
   }
+  ROW_STAMP(4);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -179,9 +212,13 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__
 //   u   = Mish(GN(y2)) * mask + r                                  (ResnetBlock1D, decoder.py:98-99)
 //   s   = (u - mean_c(u)) / sqrt(var_c(u) + 1e-5) * scale[b] + bias[b]   (SpeakerAdapter, decoder.py:34-45)
 //   hres = s (f32 residual stream);  ln = LayerNorm(s) * g1 + b1 (OT)    (transformer.py:286)
+// The kernel is latency-bound, not bandwidth-bound (clock64 trace: ~7800 clk per row and warp, 100 registers = 16
+// warps per SM): a row is four dependent warp reductions behind a global-load round trip.  So the loads of a warp's
+// NEXT row are issued as soon as the current row's values are consumed (and the first row's before the statistics
+// prologue), and the per-channel constants come from shared memory with the GroupNorm affine folded.
 // (forcing 3 or 4 resident blocks per SM through __launch_bounds__ was measured: no faster, 3 spills and is slower)
 template <typename OT>
-__global__ void __launch_bounds__(256) gn_res_spk_ln(const float* __restrict__ y, const float* __restrict__ part,
+__global__ void __launch_bounds__(256, SRN_GNRES_MINBLOCKS) gn_res_spk_ln(const float* __restrict__ y, const float* __restrict__ part,
                                                      int mtiles, int T, long long bstride,
                                                      const float* __restrict__ gamma, const float* __restrict__ beta,
                                                      const float* __restrict__ res, const uint8_t* __restrict__ mask,
@@ -192,30 +229,61 @@ __global__ void __launch_bounds__(256) gn_res_spk_ln(const float* __restrict__ y
                                                      OT* __restrict__ ln_out, int rows_per_block) {
   __shared__ float stats[16];
   __shared__ double red[256];
+  __shared__ __align__(16) float cst[6][kC];     // folded GN scale / shift, speaker scale / bias, LN gain / bias
   pdl_launch_dependents();
+  ROW_STAMP(0);
   pdl_wait();
+  ROW_STAMP(1);
   const int b = blockIdx.y;
-  gn_reduce_stats(part, b, mtiles, T, stats, red);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(r0 + rows_per_block, T);
-  for (int r = r0 + warp; r < r1; r += 8) {
-    const long long rowoff = b * bstride + (long long)r * kC;
-    const float m = mask[(long long)b * mask_bstride + (long long)r * mask_step] ? 1.f : 0.f;
+  const long long boff = b * bstride;
+  float v[16], rr[16];
+  float m = 0.f;
+  int r = r0 + warp;
+  auto fetch = [&](int row) {       // this warp's next row: in flight during the statistics / the previous row's tail
+    const long long o = boff + (long long)row * kC + lane * 8;
+    load8(y + o, *reinterpret_cast<float(*)[8]>(&v[0]));
+    load8(y + o + 256, *reinterpret_cast<float(*)[8]>(&v[8]));
+    load8(res + o, *reinterpret_cast<float(*)[8]>(&rr[0]));
+    load8(res + o + 256, *reinterpret_cast<float(*)[8]>(&rr[8]));
+    m = mask[(long long)b * mask_bstride + (long long)row * mask_step] ? 1.f : 0.f;
+  };
+#if SRN_GNRES_PREFETCH
+  if (r < r1) fetch(r);
+#endif
+  gn_reduce_stats(part, b, mtiles, T, stats, red);
+  for (int c = threadIdx.x; c < kC; c += 256) {
+    const float a = stats[2 * (c >> 6) + 1] * gamma[c];
+    cst[0][c] = a;
+    cst[1][c] = beta[c] - stats[2 * (c >> 6)] * a;
+    cst[2][c] = spk_scale[(long long)b * kC + c];
+    cst[3][c] = spk_bias[(long long)b * kC + c];
+    cst[4][c] = ln_g[c];
+    cst[5][c] = ln_b[c];
+  }
+  __syncthreads();
+  ROW_STAMP(2);
+  for (; r < r1; r += 8) {
+    if (r >= r0 + 8) ROW_STAMP(3);
+    const long long rowoff = boff + (long long)r * kC;
     float u[16];
+#if !SRN_GNRES_PREFETCH
+    fetch(r);
+#endif
 #pragma unroll
     for (int hlf = 0; hlf < 2; ++hlf) {
       const int c = hlf * 256 + lane * 8;
-      const int g = c >> 6;
-      const float mean = stats[2 * g], rstd = stats[2 * g + 1];
-      float v[8], rr[8], ga[8], be[8];
-      load8(y + rowoff + c, v);
-      load8(res + rowoff + c, rr);
-      load8(gamma + c, ga);
-      load8(beta + c, be);
+      float ga[8], be[8];
+      load8(&cst[0][c], ga);
+      load8(&cst[1][c], be);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) u[hlf * 8 + i] = mish_f((v[i] - mean) * rstd * ga[i] + be[i]) * m + rr[i];
+      for (int i = 0; i < 8; ++i) u[hlf * 8 + i] = mish_f(fmaf(v[hlf * 8 + i], ga[i], be[i])) * m + rr[hlf * 8 + i];
     }
+#if SRN_GNRES_PREFETCH
+    if (r + 8 < r1) fetch(r + 8);
+#endif
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < 16; ++i) s += u[i];
@@ -229,8 +297,8 @@ __global__ void __launch_bounds__(256) gn_res_spk_ln(const float* __restrict__ y
     for (int hlf = 0; hlf < 2; ++hlf) {
       const int c = hlf * 256 + lane * 8;
       float sc[8], sb[8], o[8];
-      load8(spk_scale + (long long)b * kC + c, sc);
-      load8(spk_bias + (long long)b * kC + c, sb);
+      load8(&cst[2][c], sc);
+      load8(&cst[3][c], sb);
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         o[i] = u[hlf * 8 + i] * inv * sc[i] + sb[i];
@@ -248,13 +316,14 @@ __global__ void __launch_bounds__(256) gn_res_spk_ln(const float* __restrict__ y
     for (int hlf = 0; hlf < 2; ++hlf) {
       const int c = hlf * 256 + lane * 8;
       float g1[8], b1[8], o[8];
-      load8(ln_g + c, g1);
-      load8(ln_b + c, b1);
+      load8(&cst[4][c], g1);
+      load8(&cst[5][c], b1);
 #pragma unroll
       for (int i = 0; i < 8; ++i) o[i] = u[hlf * 8 + i] * inv2 * g1[i] + b1[i];
       store8_op(ln_out + rowoff + c, o);
     }
   }
+  ROW_STAMP(4);
 }
 
 // ------------------------------------------------------------------------------------------------
