@@ -340,6 +340,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.mask_bstride = pl.Tp;
     gp.mask_step = L.mask_step;
     set_D<OT>(gp, out_hc, 512, S, gp.out_bstride, 512, B);
+    gp.mapR = make_tmap_3d(hres, sizeof(float), 512, S, B, 512, (uint64_t)gp.resid_bstride, 32, 32);   // residual boxes (kResidTma)
     op.grid = dim3(512 / op.bn, L.mtiles, B);
     op.tap = Tap{"tfm", out_hc, 1, S, 512, 512, gp.out_bstride, B, 0};
     push(op, "ff_out");

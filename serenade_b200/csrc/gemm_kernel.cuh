@@ -72,7 +72,15 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     stager_put<OT, 32>(st, lane, v);
     stager_flush<OT>(st, lane, p, nc + 32 - kOtCols + h * p.d_hcol, row0, batch);
   } else if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_RESID_OT) {     // RESID_OT: residual already added by the caller
-    stager_acquire(st, lane);
+    if constexpr (EPI == EPI_RESID_OT && sizeof(OT) == 2 && !SRN_DIRECT_STORE) {
+      // one output box only (the warp's other box receives the residual, gemm_mainloop.cuh: kResidTma)
+      if (st.fill == 0) {
+        if (lane == 0) tma_store_wait_read<0>();
+        __syncwarp();
+      }
+    } else {
+      stager_acquire(st, lane);
+    }
     if constexpr (EPI == EPI_RESID_F32) {      // out and residual are the same f32 tensor: TMA reduce-add in place
       stager_put<float, 32>(st, lane, v);
       stager_flush<float>(st, lane, p, nc, row0, batch, !SRN_DIRECT_STORE);
@@ -82,6 +90,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
       round_op(v);
       stager_put<OT, 32>(st, lane, v);
       stager_flush<OT>(st, lane, p, nc + 32 - kOtCols, row0, batch);
+      if constexpr (sizeof(OT) == 2 && !SRN_DIRECT_STORE) st.buf = 0;
     }
   } else if constexpr (EPI == EPI_GEGLU) {
     float o[16];

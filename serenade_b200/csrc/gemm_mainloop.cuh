@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   uint64_t* tfull_bar = empty_bar + STAGES;     // [2] accumulator stage ready for the epilogue
   uint64_t* tempty_bar = tfull_bar + 2;         // [2] accumulator stage drained by the epilogue
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* resid_bar = reinterpret_cast<uint64_t*>(smem + CFG::kBarOff + 128);   // [8] one per epilogue warp (kResidTma)
   float* gn_red = reinterpret_cast<float*>(smem + CFG::kRedOff);   // [2 buffers][4 quarters][NG][2]
 
   const int warp = threadIdx.x >> 5;
@@ -53,6 +54,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     tma_prefetch_desc(&p.mapA[1]);
     tma_prefetch_desc(&p.mapB);
     tma_prefetch_desc(&p.mapD);
+    if (EPI == EPI_RESID_OT && sizeof(OT) == 2) tma_prefetch_desc(&p.mapR);
   }
   if (warp == 1 && elect_one()) {
     for (int s = 0; s < STAGES; ++s) {
@@ -63,6 +65,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       mbar_init(&tfull_bar[s], 1);
       mbar_init(&tempty_bar[s], 16);    // one arrival per epilogue warp of both CTAs (leader's copy is used)
     }
+    for (int s = 0; s < 8; ++s) mbar_init(&resid_bar[s], 1);
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc_2sm<CFG::kTmemCols>(tmem_slot);
@@ -156,6 +159,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     st.base = smem_u32(smem + CFG::kStgOff + (warp - 2) * 8192);
     st.buf = 0;
     st.fill = 0;
+    uint32_t rphase = 0;      // parity of this warp's residual barrier (kResidTma)
     const bool has_bias = p.bias != nullptr;
     const bool has_alpha = p.alpha != 1.0f;
     float* bias_s = reinterpret_cast<float*>(smem + CFG::kBiasOff) + (warp - 2) * 128;   // this warp's bias slice
@@ -220,7 +224,12 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         __syncwarp();
       }
       // (EPI_RESID_F32 adds its residual in the L2 with a TMA reduce-add store: nothing to load)
-      constexpr bool kResid = EPI == EPI_RESID_OT || (EPI == EPI_RESID_F32 && SRN_DIRECT_STORE);
+      // EPI_RESID_OT with 2-byte outputs: lane = row makes per-lane loads of the f32 residual 32 cache lines per
+      // instruction (clock64 trace: 2750 clk per chunk, all L1 wavefronts).  Its two output boxes per tile need only
+      // ONE staging box in flight, so the warp's second box receives the residual chunk by chunk through TMA, one
+      // chunk ahead (kResidTma); the other precisions keep the register path.
+      constexpr bool kResidTma = EPI == EPI_RESID_OT && sizeof(OT) == 2 && !SRN_DIRECT_STORE;
+      constexpr bool kResid = (EPI == EPI_RESID_OT && !kResidTma) || (EPI == EPI_RESID_F32 && SRN_DIRECT_STORE);
       float4 r4[kResid ? 8 : 1];
       const float4* rs = nullptr;
       if constexpr (kResid) {
@@ -228,6 +237,14 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         if (row_ok && nvalid > 0) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) r4[i] = rs[i];
+        }
+      }
+      if constexpr (kResidTma) {
+        __syncwarp();      // the previous tile's reads of the residual box are done
+        if (lane == 0 && nvalid > 0) {
+          mbar_expect_tx(&resid_bar[warp - 2], 4096);
+          tma_load_3d(reinterpret_cast<void*>(smem + CFG::kStgOff + (warp - 2) * 8192 + 4096), &p.mapR, &resid_bar[warp - 2],
+                      n0 + c_first * 32, row0, b);
         }
       }
       if (p.dbg_mode & 4) nvalid = 0;    // profiling experiment without the epilogue
@@ -267,6 +284,25 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(tepi_addr + as * 8);
+        }
+        if constexpr (kResidTma) {
+          mbar_wait(&resid_bar[warp - 2], rphase);
+          rphase ^= 1;
+          const uint32_t rbox = st.base + 4096 + lane * 128;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            float4 rv;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(rv.x), "=f"(rv.y), "=f"(rv.z), "=f"(rv.w)
+                         : "r"(rbox + ((i ^ (lane & 7)) << 4)));
+            v[4 * i + 0] += rv.x; v[4 * i + 1] += rv.y; v[4 * i + 2] += rv.z; v[4 * i + 3] += rv.w;
+          }
+          __syncwarp();      // every lane has its row: the box may receive the next chunk
+          if (lane == 0 && cc + 1 < nvalid) {
+            mbar_expect_tx(&resid_bar[warp - 2], 4096);
+            tma_load_3d(reinterpret_cast<void*>(smem + CFG::kStgOff + (warp - 2) * 8192 + 4096), &p.mapR,
+                        &resid_bar[warp - 2], nc + 32, row0, b);
+          }
         }
         if constexpr (kResid) {
           if (row_ok) {
