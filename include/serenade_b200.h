@@ -81,6 +81,12 @@ int srn_style_encode(SrnHandle* h, const float* logmel, int32_t B, int32_t L, fl
 int64_t srn_launch_count(const SrnHandle* h);
 /* Use one CUDA graph per (B, T, n_steps) for srn_solve_euler (default 1). */
 int srn_set_use_graph(SrnHandle* h, int32_t enable);
+/* GroupNorm statistics of Block1D (decoder.py:75) over the unmasked frames of each utterance only (default 0).
+ * 0 = the reference's padded-batch behaviour: statistics span all T_max frames, so an utterance's result depends on
+ *     how far its batch was padded.
+ * 1 = every utterance of a padded batch gets exactly what the reference gives it when decoded alone, as its CLI does
+ *     (bin/ssc_decode.py:346-378, batch 1, T = its own length): what a length-bucketed batched decode needs. */
+int srn_set_gn_valid_only(SrnHandle* h, int32_t enable);
 
 /* Test hooks: when enabled, every named intermediate of the next forward is kept (as f32, channels-last
  * (B, rows, cols)) and can be fetched by name.  srn_debug_fetch returns the element count via *n_out

@@ -75,6 +75,9 @@ class _Engine:
     def set_use_graph(self, flag: bool) -> None:
         _lib.check(self.lib.srn_set_use_graph(self.h, int(flag)), "srn_set_use_graph")
 
+    def set_gn_valid_only(self, flag: bool) -> None:
+        _lib.check(self.lib.srn_set_gn_valid_only(self.h, int(flag)), "srn_set_gn_valid_only")
+
     def profile_ops(self, B: int, T: int, reps: int = 5):
         """[(op name, kernel, avg ms)] for one estimator forward at (B, T): CUDA-event timing per op."""
         import json
@@ -113,8 +116,13 @@ class Decoder(nn.Module):
 
     def __init__(self, in_channels, out_channels, spk_embed_dim, channels=(512, 512), dropout=0.05,
                  attention_head_dim=512, n_blocks=1, num_mid_blocks=2, num_heads=4, act_fn="snake",
-                 precision="bf16", **_unused):
+                 precision="bf16", gn_stats="padded", **_unused):
         super().__init__()
+        if gn_stats not in ("padded", "valid"):
+            raise ValueError("gn_stats must be 'padded' (the reference's padded-batch behaviour) or 'valid'")
+        # 'valid': GroupNorm statistics over each utterance's own frames only, so that a padded batch reproduces the
+        # reference's batch-1 decode of every utterance (srn_set_gn_valid_only); may be changed between calls
+        self.gn_stats = gn_stats
         if n_blocks != 1:
             raise ValueError("only n_blocks=1 (the reference's setting) is supported")
         self.geom = DecoderGeometry(in_channels=in_channels, out_channels=out_channels, spk_embed_dim=spk_embed_dim,
@@ -174,6 +182,10 @@ class Decoder(nn.Module):
                 sd.update(self._extra_state())
             self._engine.load_state_dict(sd)
             self._dirty = False
+        want = self.gn_stats == "valid"
+        if getattr(self._engine, "_gn_valid", False) != want:
+            self._engine.set_gn_valid_only(want)
+            self._engine._gn_valid = want
         return self._engine
 
     def _check_inputs(self, x, mask, mu, spk):
@@ -210,7 +222,7 @@ class CFM(nn.Module):
     """Reference flow_matching.py:9-93 (inference side).  `compute_loss` (training) is out of scope."""
 
     def __init__(self, in_channels=80, out_channels=80, solver="euler", sigma_min=1e-4, spk_embed_dim=256,
-                 decoder_channels=(512, 512), decoder_attention_head_dim=256, precision="bf16"):
+                 decoder_channels=(512, 512), decoder_attention_head_dim=256, precision="bf16", gn_stats="padded"):
         super().__init__()
         self.n_feats = in_channels
         self.spk_embed_dim = spk_embed_dim
@@ -220,7 +232,7 @@ class CFM(nn.Module):
         self.out_channels = out_channels
         self.estimator = Decoder(in_channels=in_channels, out_channels=out_channels, spk_embed_dim=spk_embed_dim,
                                  channels=decoder_channels, attention_head_dim=decoder_attention_head_dim,
-                                 precision=precision)
+                                 precision=precision, gn_stats=gn_stats)
 
     def forward(self, x1, mask, mu, spks, mask_l=None):
         return self.compute_loss(x1, mask, mu, spks, mask_l)

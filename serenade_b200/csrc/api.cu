@@ -170,6 +170,13 @@ SRN_EXPORT int srn_set_use_graph(SrnHandle* h, int32_t enable) {
   SRN_API_END
 }
 
+SRN_EXPORT int srn_set_gn_valid_only(SrnHandle* h, int32_t enable) {
+  SRN_API_BEGIN
+  check_handle(h);
+  h->eng->gn_valid_only = enable != 0;
+  SRN_API_END
+}
+
 SRN_EXPORT int srn_debug_enable(SrnHandle* h, int32_t enable) {
   SRN_API_BEGIN
   check_handle(h);

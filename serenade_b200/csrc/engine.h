@@ -37,6 +37,10 @@ class EngineBase {
   int64_t launches = 0;
   bool use_graph = true;
   bool debug = false;
+  // GroupNorm statistics over the unmasked frames of each utterance only (srn_set_gn_valid_only): a padded batch
+  // then gives every utterance exactly what the reference gives it when decoded alone (batch 1, T = its length).
+  // Off (default) = the reference's own padded-batch behaviour (statistics over all T_max frames, decoder.py:75).
+  bool gn_valid_only = false;
   std::map<std::string, DebugTensor> debug_tensors;
 };
 

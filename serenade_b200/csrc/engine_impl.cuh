@@ -93,6 +93,7 @@ struct Plan {
   DevBuf xin, y, r, gnpart, a1, hres, ln, qk, vt, smax, ssum, P, ao, gg, hid0, hid1, hc, cv;
   DevBuf x_state, mask, spk_in, mu_in, spk_scale, spk_bias, tsteps, dts, temb0, temb1, temb2, tb;
   DevBuf blend_mask, blend_src;
+  DevBuf nvalid;      // [2][B] unmasked frames per batch entry at full / half rate (valid-frame GroupNorm mode)
   int tb_steps = 0;
   std::vector<Op> ops;
   int euler_op = -1;
@@ -100,6 +101,7 @@ struct Plan {
   cudaGraphExec_t graph = nullptr;
   int graph_steps = 0;
   bool graph_blend = false;
+  bool graph_gn_valid = false;
   int64_t graph_nodes = 0;
   ~Plan() {
     if (graph) cudaGraphExecDestroy(graph);

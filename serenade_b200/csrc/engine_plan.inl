@@ -385,6 +385,7 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
   pl.spk_scale.alloc((size_t)nres * B * C * 4);
   pl.spk_bias.alloc((size_t)nres * B * C * 4);
   pl.blend_mask.alloc((size_t)B * T);
+  pl.nvalid.alloc((size_t)2 * B * sizeof(int));
   pl.blend_src.alloc((size_t)B * cfg_.out_channels * T * 4);
 
   OT* xin = pl.xin.template as<OT>();

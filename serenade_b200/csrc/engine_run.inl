@@ -134,6 +134,7 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
   const Level& L = pl.lv[op.level];
   const uint8_t* mask = pl.mask.template as<uint8_t>();
   const int B = pl.B;
+  const int* nvalid = gn_valid_only ? pl.nvalid.template as<int>() + (size_t)op.level * B : nullptr;
   switch (op.kind) {
     case OP_GEMM: {
       if (op.is_euler) {
@@ -145,6 +146,12 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
           gp.blend_mask = pl.blend_mask.template as<uint8_t>();
           gp.blend_src = pl.blend_src.template as<float>();
         }
+        launch_gemm(gp, op.bn, op.grid, st);
+      } else if (op.gp.gn_part != nullptr && gn_valid_only) {
+        GemmParams gp = op.gp;
+        gp.gn_mask = mask;
+        gp.mask_bstride = pl.Tp;
+        gp.mask_step = L.mask_step;
         launch_gemm(gp, op.bn, op.grid, st);
       } else {
         launch_gemm(op.gp, op.bn, op.grid, st);
@@ -162,7 +169,7 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
                                      : nullptr;
       dim3 grid(cdiv(L.T, rpb), B);
       launch_k(gn_apply_kernel<OT>, grid, dim3(256), st, op.y, op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma,
-               op.beta, tb, mask, pl.Tp, L.mask_step, static_cast<OT*>(op.out), rpb);
+               op.beta, tb, mask, pl.Tp, L.mask_step, static_cast<OT*>(op.out), rpb, nvalid);
       ++launches;
     } break;
     case OP_GN_RES_SPK_LN: {
@@ -171,7 +178,8 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
       const float* sc = pl.spk_scale.template as<float>() + (size_t)op.resnet_idx * B * 512;
       const float* sb = pl.spk_bias.template as<float>() + (size_t)op.resnet_idx * B * 512;
       launch_k(gn_res_spk_ln<OT>, grid, dim3(256), st, op.y, op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma,
-               op.beta, op.res, mask, pl.Tp, L.mask_step, sc, sb, op.ln_g, op.ln_b, op.hres, static_cast<OT*>(op.out), rpb);
+               op.beta, op.res, mask, pl.Tp, L.mask_step, sc, sb, op.ln_g, op.ln_b, op.hres, static_cast<OT*>(op.out), rpb,
+               nvalid);
       ++launches;
     } break;
     case OP_LAYERNORM: {
@@ -231,6 +239,10 @@ void Engine<OT>::prepass(Plan<OT>& pl, const std::vector<float>& ts, const std::
     dim3 grid(cdiv(pl.T, 32), cdiv(cmu_, 32), B);
     launch_k(pack_cf_to_cl<OT>, grid, dim3(32, 8), st, pl.mu_in.template as<float>(), cmu_, pl.T, mask, pl.Tp,
              pl.xin.template as<OT>(), (long long)pl.Tp * 256, 256, cfg_.out_channels);
+    ++launches;
+  }
+  if (gn_valid_only) {
+    launch_k(count_valid_kernel, dim3(B), dim3(256), st, mask, pl.T, pl.Tp, B, pl.nvalid.template as<int>());
     ++launches;
   }
   const int sd = cfg_.spk_embed_dim;
@@ -314,7 +326,7 @@ void Engine<OT>::solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bo
   check_abort();                         // (reports a timeout of an earlier asynchronous solve)
   blend_active_ = blend;
   if (use_graph && !debug) {
-    if (pl.graph == nullptr || pl.graph_steps != n_steps || pl.graph_blend != blend) {
+    if (pl.graph == nullptr || pl.graph_steps != n_steps || pl.graph_blend != blend || pl.graph_gn_valid != gn_valid_only) {
       if (pl.graph) {
         cudaGraphExecDestroy(pl.graph);
         pl.graph = nullptr;
@@ -340,6 +352,7 @@ void Engine<OT>::solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bo
       if (e != cudaSuccess) fail("cudaGraphInstantiate failed: %s", cudaGetErrorString(e));
       pl.graph_steps = n_steps;
       pl.graph_blend = blend;
+      pl.graph_gn_valid = gn_valid_only;
     }
     SRN_CUDA(cudaGraphLaunch(pl.graph, st));
     launches += pl.graph_nodes;

@@ -82,6 +82,7 @@ struct GemmParams {
   long long resid_bstride;
   int ldr;
   float* gn_part;   // [B][m_tiles][8][2] partial (sum, sum of squares) per 64-channel group, or null
+  const uint8_t* gn_mask;   // non-null: only rows with gn_mask[b * mask_bstride + row * mask_step] != 0 enter gn_part
   // EPI_QKV
   int split_n;
   void* out2;       // V^T [B][split rows][ld2]

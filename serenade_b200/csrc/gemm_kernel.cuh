@@ -38,7 +38,7 @@ struct GemmCfg {
 template <typename OT, int EPI>
 __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[32], Stager& st, int lane, int b, int h,
                                                int z, int row, int row0, int nc, bool row_ok, float mk, float& gs,
-                                               float& gss, float& racc, float rowc, uint32_t keybits) {
+                                               float& gss, float& racc, float rowc, uint32_t keybits, bool gn_ok) {
   const int batch = p.d_zbatch ? z : b;
   constexpr int kOtCols = 128 / (int)sizeof(OT);     // output columns per 128-byte staging row
   // fp32-stored operand tensors are consumed as TF32: round to nearest here (the tensor core truncates)
@@ -53,7 +53,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     }
   };
   if constexpr (EPI == EPI_STORE_F32) {
-    if (p.gn_part != nullptr && row_ok) {
+    if (p.gn_part != nullptr && gn_ok) {
 #pragma unroll
       for (int i = 0; i < 32; ++i) { gs += v[i]; gss = fmaf(v[i], v[i], gss); }
     }

@@ -180,6 +180,11 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       float mk = 1.0f;
       if (p.rowmask != nullptr && row_ok)
         mk = p.rowmask[(long long)b * p.mask_bstride + (long long)row * p.mask_step + p.mask_off] ? 1.0f : 0.0f;
+      bool gn_ok = row_ok;      // does this row enter the GroupNorm statistics (valid-frame mode: unmasked rows only)
+      if constexpr (EPI == EPI_STORE_F32) {
+        if (p.gn_mask != nullptr && row_ok)
+          gn_ok = p.gn_mask[(long long)b * p.mask_bstride + (long long)row * p.mask_step] != 0;
+      }
       float* red = gn_red + as * (4 * NG * 2);
       const int c_first = sub * (NCH / 2);
       int nvalid = (p.N - (n0 + c_first * 32) + 31) / 32;     // chunks of this warp that start inside N
@@ -327,7 +332,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
 #pragma unroll
           for (int j = 0; j < NCH / 2; ++j) kbits = j == cc ? keybits[j] : kbits;    // keeps keybits[] in registers
         }
-        epilogue_chunk<OT, EPI>(p, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss, racc, rowc, kbits);
+        epilogue_chunk<OT, EPI>(p, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss, racc, rowc, kbits, gn_ok);
         if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
           // one partial per 64-key slice, whatever the tile shape: the order in which the row sum is formed (here
           // and in the P~ V epilogue) is then independent of BN, i.e. of the batch size the plan was built for

@@ -132,9 +132,39 @@ __global__ void pack_cf_to_cl(const float* __restrict__ src, int C, int T, const
 }
 
 // ------------------------------------------------------------------------------------------------
+// Valid-frame GroupNorm mode: number of unmasked frames of every batch entry at full rate (out[b]) and at half
+// rate (out[B + b], frames 0, 2, 4, ...).  One block per batch entry.
+__global__ void __launch_bounds__(256) count_valid_kernel(const uint8_t* __restrict__ mask, int T, int mask_bstride,
+                                                          int B, int* __restrict__ out) {
+  __shared__ int red[2][8];
+  pdl_launch_dependents();
+  pdl_wait();
+  const int b = blockIdx.x;
+  int full = 0, half = 0;
+  for (int t = threadIdx.x; t < T; t += 256) {
+    const int m = mask[(long long)b * mask_bstride + t] != 0;
+    full += m;
+    half += m & ((t & 1) == 0);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    full += __shfl_xor_sync(0xffffffffu, full, o);
+    half += __shfl_xor_sync(0xffffffffu, half, o);
+  }
+  if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = full; red[1][threadIdx.x >> 5] = half; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int f = 0, h = 0;
+    for (int i = 0; i < 8; ++i) { f += red[0][i]; h += red[1][i]; }
+    out[b] = f;
+    out[B + b] = h;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Reduce the conv epilogue's per-tile partial sums to (mean, rstd) for the 8 groups of batch b.
 // part: [B][mtiles][8][2].  Result in smem stats[16] = {mean_g, rstd_g}.  Call with >= 256 threads.
 __device__ __forceinline__ void gn_reduce_stats(const float* __restrict__ part, int b, int mtiles, int T,
+                                                const int* __restrict__ nvalid /* per batch entry, or null: T */,
                                                 float* stats /*smem [16]*/, double* red /*smem [256]*/) {
   const int t = threadIdx.x;
   if (t < 256) {
@@ -151,7 +181,7 @@ __device__ __forceinline__ void gn_reduce_stats(const float* __restrict__ part, 
   }
   __syncthreads();
   if (t < 8) {
-    const double n = 64.0 * (double)T;
+    const double n = 64.0 * (double)(nvalid != nullptr ? max(nvalid[b], 1) : T);
     const double mean = red[2 * t] / n;
     double var = red[2 * t + 1] / n - mean * mean;
     if (var < 0.0) var = 0.0;
@@ -169,7 +199,7 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                                        const float* __restrict__ tbias, const uint8_t* __restrict__ mask,
                                                        int mask_bstride, int mask_step, OT* __restrict__ out,
-                                                       int rows_per_block) {
+                                                       int rows_per_block, const int* __restrict__ nvalid) {
   __shared__ float stats[16];
   __shared__ double red[256];
   pdl_launch_dependents();
@@ -177,7 +207,7 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__
   pdl_wait();
   ROW_STAMP(1);
   const int b = blockIdx.y;
-  gn_reduce_stats(part, b, mtiles, T, stats, red);
+  gn_reduce_stats(part, b, mtiles, T, nvalid, stats, red);
   ROW_STAMP(2);
   const int c = (threadIdx.x & 63) * 8;
   const int g = c >> 6;
@@ -226,7 +256,8 @@ __global__ void __launch_bounds__(256, SRN_GNRES_MINBLOCKS) gn_res_spk_ln(const 
                                                      const float* __restrict__ spk_scale /*[B][512]*/,
                                                      const float* __restrict__ spk_bias, const float* __restrict__ ln_g,
                                                      const float* __restrict__ ln_b, float* __restrict__ hres,
-                                                     OT* __restrict__ ln_out, int rows_per_block) {
+                                                     OT* __restrict__ ln_out, int rows_per_block,
+                                                     const int* __restrict__ nvalid) {
   __shared__ float stats[16];
   __shared__ double red[256];
   __shared__ __align__(16) float cst[6][kC];     // folded GN scale / shift, speaker scale / bias, LN gain / bias
@@ -253,7 +284,7 @@ __global__ void __launch_bounds__(256, SRN_GNRES_MINBLOCKS) gn_res_spk_ln(const 
 #if SRN_GNRES_PREFETCH
   if (r < r1) fetch(r);
 #endif
-  gn_reduce_stats(part, b, mtiles, T, stats, red);
+  gn_reduce_stats(part, b, mtiles, T, nvalid, stats, red);
   for (int c = threadIdx.x; c < kC; c += 256) {
     const float a = stats[2 * (c >> 6) + 1] * gamma[c];
     cst[0][c] = a;

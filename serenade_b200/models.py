@@ -15,7 +15,7 @@ PyTorch only concatenates the conditioning tensors (serenade.py:186-206).  Train
 from __future__ import annotations
 
 import ctypes as C
-from typing import Dict
+from typing import Dict, List, Optional, Sequence
 
 import torch
 import torch.nn as nn
@@ -144,3 +144,61 @@ class Serenade(nn.Module):
                                               temperature=temperature, spks=ref_speaker_features).permute(0, 2, 1)
         mel_pred = mel_pred[:, int(ref_lengths[0]):, :]
         return mel_pred.squeeze(0)
+
+    @torch.inference_mode()
+    def inference_batch(self, items: Sequence[Sequence[torch.Tensor]], n_timesteps=10, temperature=0.667,
+                        max_batch=16, max_padded_frames: Optional[int] = None) -> List[torch.Tensor]:
+        """Length-bucketed batched decode: `items[i]` holds the positional arguments of `inference`
+        for ONE utterance (batch dimension 1); returns `[self.inference(*it) for it in items]` without the reference's
+        batch-1 restriction (the FIXMEs at serenade.py:209-210, :218: its concat / cut assume one reference length).
+
+        The encoders run per utterance (their reflection padding and the GRU depend on the true lengths); the flow-
+        matching decode, which is all the time, runs on padded batches of similar length with GroupNorm statistics
+        over each utterance's own frames (`gn_stats="valid"`), so every mel equals the one `inference` returns for that
+        utterance alone.  Noise is drawn per utterance, in order, with the same generator calls as sequential
+        `inference` calls make (flow_matching.py:57)."""
+        from . import sharding
+        if len(items) == 0:
+            return []
+        dev = items[0][0].device
+        clips, ref_lens = [], []
+        for it in items:
+            x, lengths, midi, lft, ref_x, ref_lengths, ref_logmel, ref_midi, ref_lft = it
+            if x.shape[0] != 1:
+                raise ValueError("inference_batch takes one utterance per item (batch dimension 1)")
+            enc = self.encode_content(x, lengths)
+            spk = self.encode_style(ref_logmel)
+            cond = ref_logmel.to(torch.float32)
+            ref_enc = torch.cat([self.encode_content(ref_x, ref_lengths), ref_midi.float(), ref_lft.float(), cond], dim=-1)
+            zero_cond = torch.zeros(1, enc.shape[1], cond.shape[-1], device=dev)
+            mu = torch.cat([ref_enc, torch.cat([enc, midi.float(), lft.float(), zero_cond], dim=-1)], dim=1)
+            total = int(lengths[0]) + int(ref_lengths[0])
+            mu = mu[0, :total].transpose(0, 1).contiguous()                   # (162, T_i); frames past the lengths are padding
+            z = torch.randn((1, self.cfm_decoder.out_channels, mu.shape[1])).to(dev) * temperature
+            clips.append(dict(mu=mu, z=z[0], spk=spk[0]))
+            ref_lens.append(int(ref_lengths[0]))
+        lens = [int(c["mu"].shape[-1]) for c in clips]
+        t_span = torch.linspace(0, 1, n_timesteps + 1, device=dev)
+        est = self.cfm_decoder.estimator
+        saved = est.gn_stats
+        est.gn_stats = "valid"
+        out: List[Optional[torch.Tensor]] = [None] * len(clips)
+        try:
+            for batch in sharding.make_batches(range(len(clips)), lens, max_batch=max_batch,
+                                               max_padded_frames=max_padded_frames):
+                T = max(lens[i] for i in batch)
+                z = torch.zeros(len(batch), clips[batch[0]]["z"].shape[0], T, device=dev)
+                mu = torch.zeros(len(batch), clips[batch[0]]["mu"].shape[0], T, device=dev)
+                mask = torch.zeros(len(batch), 1, T, dtype=torch.bool, device=dev)
+                for b, i in enumerate(batch):
+                    z[b, :, :lens[i]] = clips[i]["z"]
+                    mu[b, :, :lens[i]] = clips[i]["mu"]
+                    mask[b, :, :lens[i]] = True
+                spk = torch.stack([clips[i]["spk"] for i in batch])
+                mel = self.cfm_decoder.solve_euler(z, t_span, mu, mask, spk)
+                for b, i in enumerate(batch):
+                    out[i] = mel[b, :, ref_lens[i]:lens[i]].transpose(0, 1).contiguous()
+        finally:
+            est.gn_stats = saved
+        return out  # type: ignore[return-value]
+

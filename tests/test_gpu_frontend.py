@@ -79,3 +79,31 @@ def test_batch_rows_are_independent(models):
     for i in range(3):
         assert torch.equal(m.encode_content(inp["x"][i:i + 1].to(dev))[0], enc[i])
         assert torch.equal(m.encode_style(inp["ref_logmel"][i:i + 1].to(dev))[0], sty[i])
+
+
+def test_inference_batch_equals_sequential_single_utterance_inference(models):
+    """the length-bucketed batched decode returns, for every utterance, the mel that `inference` (the
+    reference's batch-1 call, bin/ssc_decode.py:428) returns for it alone - same noise draws, GroupNorm statistics
+    over the utterance's own frames."""
+    import serenade_b200 as S
+    dev = torch.device("cuda", 0)
+    m = models["bf16"]
+    order = ["x", "lengths", "midi", "lft", "ref_x", "ref_lengths", "ref_logmel", "ref_midi", "ref_lft"]
+    shapes = [(96, 64), (131, 70), (60, 97), (200, 64), (75, 75)]
+    items = []
+    for k, (src, ref) in enumerate(shapes):
+        inp = S.make_frontend_inputs(src, ref, seed=20 + k)
+        items.append([inp[name].to(dev) for name in order])
+    torch.manual_seed(7)
+    solo = [m.inference(*it) for it in items]
+    torch.manual_seed(7)
+    batched = m.inference_batch(items, max_batch=3)
+    assert m.cfm_decoder.estimator.gn_stats == "padded"      # restored
+    worst = 0.0
+    for (src, ref), a, b in zip(shapes, solo, batched):
+        assert a.shape == b.shape == (src, 80)
+        worst = max(worst, rel_l2(b.cpu(), a.cpu()))
+    _report("frontend_parity.txt", f"inference_batch vs sequential inference: worst rel_l2 {worst:.3e} "
+            f"(bit exact: {all(torch.equal(a, b) for a, b in zip(solo, batched))})")
+    assert worst < 1e-5
+

@@ -237,6 +237,39 @@ def test_full_size_parity_against_fp32_oracle_on_gpu(cfg, stock_sd, cfm_stock, c
     assert torch.equal(x.cpu()[pad], b.z[pad])
 
 
+def test_valid_frame_groupnorm_reproduces_solo_decodes(jitter_sd, dev):
+    """srn_set_gn_valid_only: in a padded batch every utterance gets what it gets when decoded alone at its own
+    length (the reference CLI's batch-1 call), and that in turn matches the oracle run on the unpadded utterance.
+    The default mode keeps the reference's padded-batch behaviour (statistics over T_max) and differs."""
+    import serenade_b200 as S
+    from oracle import cfm_oracle as O
+    cfm = _make_cfm(jitter_sd)
+    lengths = [300, 257, 190, 64]
+    b = S.make_batch(lengths, n_steps=4, seed=5)
+    args = [b.z.to(dev), b.t_span.to(dev), b.mu.to(dev), b.mask.to(dev), b.spks.to(dev)]
+    padded_mode = cfm.solve_euler(*args)
+    cfm.estimator.gn_stats = "valid"
+    valid_mode = cfm.solve_euler(*args)
+    cfm.estimator.gn_stats = "padded"
+    again = cfm.solve_euler(*args)
+    assert torch.equal(again, padded_mode)                    # the switch is honoured both ways (graph re-captured)
+    worst, exact = 0.0, True
+    for i, L in enumerate(lengths):
+        solo = cfm.solve_euler(b.z[i:i + 1, :, :L].to(dev), b.t_span.to(dev), b.mu[i:i + 1, :, :L].to(dev),
+                               b.mask[i:i + 1, :, :L].to(dev), b.spks[i:i + 1].to(dev))
+        got = valid_mode[i:i + 1, :, :L]
+        worst = max(worst, rel_l2(got.cpu(), solo.cpu()))
+        exact = exact and torch.equal(got, solo)
+        if L < max(lengths):
+            assert not torch.equal(padded_mode[i:i + 1, :, :L], solo)     # padded statistics do depend on T_max
+        with torch.inference_mode():
+            ref = O.solve_euler(jitter_sd, b.z[i:i + 1, :, :L], b.t_span, b.mu[i:i + 1, :, :L], b.mask[i:i + 1, :, :L],
+                                b.spks[i:i + 1])
+        assert rel_l2(got.cpu(), ref) < BF16_FINAL_TOL
+    _report("gn_valid_only.txt", f"valid-frame GroupNorm, padded batch vs solo decodes: worst rel_l2 {worst:.3e}, bit exact {exact}")
+    assert worst < 1e-5
+
+
 def test_bad_arguments_raise(cfm_jitter, dev):
     import serenade_b200 as S
     b = S.make_batch([64], n_steps=2, seed=1)
