@@ -38,6 +38,8 @@ template <typename OT>
 static void configure_kernels() {
   configure_bn<OT, 128>();
   configure_bn<OT, 256>();
+  configure_one<Fp8, 128, EPI_ROWMAX>();
+  configure_one<Fp8, 256, EPI_ROWMAX>();
 }
 
 std::unique_ptr<EngineBase> make_engine(const SrnConfig& cfg) {

@@ -91,6 +91,7 @@ struct Plan {
   int B = 0, T = 0, Tp = 0;
   Level lv[2];
   DevBuf xin, y, r, gnpart, a1, hres, ln, qk, vt, smax, ssum, P, ao, gg, hid0, hid1, hc, cv;
+  DevBuf qk8;      // e4m3 copy of Q | K (row-max pass operands)
   DevBuf x_state, mask, spk_in, mu_in, spk_scale, spk_bias, tsteps, dts, temb0, temb1, temb2, tb;
   DevBuf blend_mask, blend_src;
   DevBuf nvalid;      // [2][B] unmasked frames per batch entry at full / half rate (valid-frame GroupNorm mode)

@@ -36,6 +36,14 @@ GemmParams Engine<OT>::base_gemm(const Plan<OT>& pl, int level) const {
 }
 
 namespace {
+// SRN_ROWMAX_FP8=0 keeps the row-max pass in operand precision (A/B switch; default on)
+inline bool rowmax_fp8() {
+  static const bool on = [] {
+    const char* e = getenv("SRN_ROWMAX_FP8");
+    return !(e != nullptr && e[0] == '0');
+  }();
+  return on;
+}
 template <typename OT>
 void set_A(GemmParams& gp, int idx, const OT* ptr, int cols, int rows, long long alloc_rows, int ld, int nbatch) {
   gp.mapA[idx] = make_tmap_3d(ptr, sizeof(OT), cols, rows, nbatch, ld, (uint64_t)alloc_rows * ld, OpTraits<OT>::kBK, SRN_MC ? 64 : 128);
@@ -164,6 +172,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
   const long long tiles = (long long)L.mtiles * B;
   OT* ln = pl.ln.template as<OT>();
   OT* qk = pl.qk.template as<OT>();
+  uint8_t* qk8 = rowmax_fp8() ? pl.qk8.template as<uint8_t>() : nullptr;
   OT* vt = pl.vt.template as<OT>();
   OT* P = pl.P.template as<OT>();
   OT* ao = pl.ao.template as<OT>();
@@ -193,6 +202,9 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.out2_bstride = (long long)2048 * Sp;
     gp.ld2 = Sp;
     set_D<OT>(gp, qk, 4096, S, gp.out_bstride, 4096, B);
+    gp.out8 = qk8;
+    gp.out8_bstride = (long long)L.R * 4096;
+    gp.ld8 = 4096;
     gp.mapD2 = make_tmap_3d(vt, sizeof(OT), S, 2048, B, Sp, (uint64_t)2048 * Sp, 32, 32, false);
     op.grid = dim3(6144 / op.bn, L.mtiles, B);
     op.tap = Tap{"qk", qk, 1, S, 4096, 4096, gp.out_bstride, B, 0};
@@ -216,6 +228,16 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.a_hcol = 512;
     add_seg(gp, 0, 0, 0, 512 / BK);
     gp.mapB = make_tmap_3d(qk, sizeof(OT), 4096, S, B, 4096, (uint64_t)L.R * 4096, BK, op.bn / 2);
+    if (pass == 0 && qk8 != nullptr) {
+      // the shift only has to be NEAR the row maximum: e4m3 copies of Q and K, half the operand bytes, twice the MMA rate
+      gp.ab_fp8 = 1;
+      gp.nseg = 0;
+      gp.nkb = 0;
+      gp.mapA[0] = make_tmap_3d(qk8, 1, 4096, S, B, 4096, (uint64_t)L.R * 4096, 128, SRN_MC ? 64 : 128);
+      gp.mapA[1] = gp.mapA[0];
+      add_seg(gp, 0, 0, 0, 512 / 128);
+      gp.mapB = make_tmap_3d(qk8, 1, 4096, S, B, 4096, (uint64_t)L.R * 4096, 128, op.bn / 2);
+    }
     gp.b_col0 = 2048;
     gp.b_hcol = 512;
     gp.b_batch_mode = 1;
@@ -364,6 +386,7 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
   pl.hres.alloc(rows * C * 4);
   pl.ln.alloc(rows * C * es);
   pl.qk.alloc(rows * 4096 * es);
+  if (rowmax_fp8()) pl.qk8.alloc(rows * 4096);
   pl.vt.alloc((size_t)B * 2048 * pl.lv[0].Sp * es);
   {  // softmax statistics: one (max, sum) partial per row per 128-column (or 64-column) slice of the score GEMM
     const size_t n128 = 2 * (size_t)cdiv(T, 128);

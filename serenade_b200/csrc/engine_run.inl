@@ -98,7 +98,11 @@ template <typename OT>
 void Engine<OT>::launch_gemm(const GemmParams& gp, int bn, dim3 grid, cudaStream_t st) {
   if (gp.nkb < 1 || gp.nseg < 1) fail("gemm with empty K");
   if (gp.epi == EPI_RESID_F32 && gp.resid != gp.out) fail("EPI_RESID_F32 updates its residual in place (TMA reduce-add)");
-  if (bn == 256) launch_gemm_bn<OT, 256>(gp, grid, num_sms_, st);
+  if (gp.ab_fp8) {
+    if (gp.epi != EPI_ROWMAX) fail("e4m3 operands are only used by the row-max pass");
+    if (bn == 256) launch_gemm_impl<Fp8, 256, EPI_ROWMAX>(gp, grid, num_sms_, st);
+    else launch_gemm_impl<Fp8, 128, EPI_ROWMAX>(gp, grid, num_sms_, st);
+  } else if (bn == 256) launch_gemm_bn<OT, 256>(gp, grid, num_sms_, st);
   else launch_gemm_bn<OT, 128>(gp, grid, num_sms_, st);
   ++launches;
 }
@@ -539,7 +543,7 @@ std::string Engine<OT>::profile_ops(int B, int T, int reps) {
     switch (op.kind) {
       case OP_GEMM:
         kind = op.bn == 256 ? "gemm_bn256" : "gemm_bn128";
-        flops = 2.0 * (double)op.gp.M * op.gp.N * ((double)op.gp.nkb * BK) * (double)(B * op.gp.HB);
+        flops = 2.0 * (double)op.gp.M * op.gp.N * ((double)op.gp.nkb * (op.gp.ab_fp8 ? 128 : BK)) * (double)(B * op.gp.HB);
         break;
       case OP_PACKX: kind = "pack_cf_to_cl"; bytes = (double)B * cfg_.out_channels * T * (4 + es); break;
       case OP_GN_APPLY: kind = "gn_apply"; bytes = rows * 512 * (4 + es); break;

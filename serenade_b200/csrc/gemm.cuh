@@ -82,6 +82,10 @@ struct GemmParams {
   long long resid_bstride;
   int ldr;
   float* gn_part;   // [B][m_tiles][8][2] partial (sum, sum of squares) per 64-channel group, or null
+  uint8_t* out8;            // EPI_QKV: e4m3 copy of the Q | K columns for the row-max pass [B][rows][ld8], or null
+  long long out8_bstride;
+  int ld8;
+  int ab_fp8;               // host side: launch the Fp8-operand instantiation (EPI_ROWMAX only)
   const uint8_t* gn_mask;   // non-null: only rows with gn_mask[b * mask_bstride + row * mask_step] != 0 enter gn_part
   // EPI_QKV
   int split_n;
@@ -118,14 +122,27 @@ struct OpTraits;
 template <>
 struct OpTraits<__nv_bfloat16> {
   static constexpr bool kTF32 = false;
+  static constexpr int kKind = 0;      // tcgen05.mma kind::f16
   static constexpr uint32_t kFmt = 1;
   static constexpr int kBK = 64;   // elements per 128-byte K block
 };
 template <>
 struct OpTraits<float> {
   static constexpr bool kTF32 = true;
+  static constexpr int kKind = 1;      // kind::tf32
   static constexpr uint32_t kFmt = 2;
   static constexpr int kBK = 32;
+};
+// FP8 (e4m3) operands: used for ONE thing, the row-max pass of the attention (EPI_ROWMAX).  softmax is invariant to
+// the per-row shift, so the shift only has to be close to the true maximum (no overflow of exp(s - shift), no
+// underflow of the whole row): an e4m3 copy of Q and K gives it at half the operand bytes and twice the MMA rate.
+struct Fp8 { uint8_t v; };
+template <>
+struct OpTraits<Fp8> {
+  static constexpr bool kTF32 = false;
+  static constexpr int kKind = 2;      // kind::f8f6f4, A and B e4m3
+  static constexpr uint32_t kFmt = 0;
+  static constexpr int kBK = 128;
 };
 
 __device__ __forceinline__ float warp_sum_f(float v) {

@@ -109,6 +109,21 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     stager_flush<OT>(st, lane, p, (nc >> 1) + 16 - kOtCols, row0, batch);
   } else if constexpr (EPI == EPI_QKV) {
     round_op(v);
+    if (nc < p.split_n && p.out8 != nullptr && row_ok) {
+      // e4m3 copy of Q | K for the row-max pass, 32 bytes per lane and chunk straight to global memory (staging it
+      // through a TMA box was measured and is slower: it needs the chunk loop unrolled and a third box)
+      uint32_t w[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        uint16_t lo, hi;
+        asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(lo) : "f"(v[4 * i + 1]), "f"(v[4 * i + 0]));
+        asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(hi) : "f"(v[4 * i + 3]), "f"(v[4 * i + 2]));
+        w[i] = (uint32_t)lo | ((uint32_t)hi << 16);
+      }
+      uint4* g8 = reinterpret_cast<uint4*>(p.out8 + (long long)batch * p.out8_bstride + (long long)row * p.ld8 + nc);
+      g8[0] = make_uint4(w[0], w[1], w[2], w[3]);
+      g8[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    }
     if (nc < p.split_n) {
       stager_acquire(st, lane);
       stager_put<OT, 32>(st, lane, v);

@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           if (!(p.dbg_mode & 2)) {       // (dbg_mode & 2: profiling experiment without MMAs)
 #pragma unroll
             for (int k = 0; k < 4; ++k)   // 4 x 32 bytes of K per 128-byte swizzled row
-              umma_pair<TR::kTF32>(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+              umma_pair<TR::kKind>(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
           }
           tc_commit_mask(&empty_bar[stage], MC ? 0xF : 0x3);     // frees the stage in both CTAs (MC: one of the two arrivals, in all four)
           if (++stage == STAGES) { stage = 0; phase ^= 1; }

@@ -255,13 +255,19 @@ __device__ __forceinline__ void tc_commit_mask(uint64_t* bar, uint16_t cta_mask)
       "h"(cta_mask)
       : "memory");
 }
-template <bool kTF32>
+template <int kKind>     // 0 = kind::f16, 1 = kind::tf32, 2 = kind::f8f6f4
 __device__ __forceinline__ void umma_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                           uint32_t accumulate) {
-  if constexpr (kTF32) {
+  if constexpr (kKind == 1) {
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else if constexpr (kKind == 2) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
         "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
   } else {
