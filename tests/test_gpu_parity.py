@@ -237,6 +237,46 @@ def test_full_size_parity_against_fp32_oracle_on_gpu(cfg, stock_sd, cfm_stock, c
     assert torch.equal(x.cpu()[pad], b.z[pad])
 
 
+@pytest.mark.parametrize("cfg", ["C3", "C5"])
+def test_largest_configs_against_fp32_oracle_on_gpu(cfg, stock_sd, cfm_stock, cfm_tf32, dev):
+    """BASELINE configs 3 (64 ragged clips of 3-20 s, padded and masked) and 5 (8 clips of 60 s: the attention and
+    sequence-length stress) at their full batch shapes, two Euler steps (the oracle in strict fp32 needs 0.4 s per
+    step there): same gates as the full-size C1 / C2 test."""
+    import serenade_b200 as S
+    import gpu_eager_reference as E
+    if cfg == "C3":
+        g = torch.Generator().manual_seed(1234 + 2)
+        lengths = sorted(torch.randint(300, 2001, (64,), generator=g).tolist(), reverse=True)
+        seed = 1236
+    else:
+        lengths, seed = [6000] * 8, 1238
+    b = S.make_batch(lengths, n_steps=2, seed=seed, infill=(0.25, 0.75))
+    sd_dev = E.to_dev(stock_sd, dev)
+    sol = E.eager_solve(sd_dev, b, dev, "fp32", return_all=True)
+    args = [b.z.to(dev), b.t_span.to(dev), b.mu.to(dev), b.mask.to(dev), b.spks.to(dev)]
+    x = cfm_stock.solve_euler(*args)
+    e_bf16 = rel_l2(x.cpu(), sol[-1].cpu())
+    tf = cfm_tf32[False]
+    v_ref = E.eager_velocity(sd_dev, b, dev, args[0], 0.0)
+    v = tf.estimator(args[0], args[3], args[2], torch.tensor(0.0), args[4])
+    e_step = rel_l2(v.cpu(), v_ref.cpu())
+    x_tf = tf.solve_euler(*args)
+    e_tf = rel_l2(x_tf.cpu(), sol[-1].cpu())
+    _report(f"fullsize_{cfg}.txt", f"{cfg} ({len(lengths)} clips, T_max {max(lengths)}, 2 steps): bf16 x_2 rel_l2={e_bf16:.3e}; "
+            f"tf32 per-step rel_l2={e_step:.3e}; tf32 x_2 rel_l2={e_tf:.3e}")
+    assert e_bf16 < BF16_FINAL_TOL
+    assert e_step < TF32_STEP_TOL
+    assert e_tf < TF32_STEP_TOL
+    pad = ~b.mask.expand_as(b.z)
+    assert torch.equal(x.cpu()[pad], b.z[pad])
+    assert float(v.cpu()[pad].abs().sum()) == 0.0
+    del sol, x, x_tf, v, v_ref
+    for c in (cfm_stock, tf):          # release the large plans
+        c.estimator._engine.close()
+        c.estimator._engine = None
+    torch.cuda.empty_cache()
+
+
 def test_valid_frame_groupnorm_reproduces_solo_decodes(jitter_sd, dev):
     """srn_set_gn_valid_only: in a padded batch every utterance gets what it gets when decoded alone at its own
     length (the reference CLI's batch-1 call), and that in turn matches the oracle run on the unpadded utterance.
