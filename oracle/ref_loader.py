@@ -171,3 +171,42 @@ def load_reference_serenade():
 def build_reference_serenade(**kw):
     """Serenade() with the ssc1 recipe's parameters (conf/serenade.yaml: all constructor defaults)."""
     return load_reference_serenade().Serenade(**kw).eval()
+
+
+def load_reference_hifigan():
+    """Returns the reference `serenade.vocoder.models.hifigan` module (HiFiGANGenerator) loaded by file path.
+    `serenade.utils.read_hdf5` (h5py, absent here) is only used by register_stats and is stubbed."""
+    if "hifigan" in _cache:
+        return _cache["hifigan"]
+    _install_shims()
+    def mod(name, **attrs):
+        if name not in sys.modules:
+            m = types.ModuleType(name)
+            m.__path__ = []
+            sys.modules[name] = m
+        for k, v in attrs.items():
+            if not hasattr(sys.modules[name], k):
+                setattr(sys.modules[name], k, v)
+        return sys.modules[name]
+    def _no_h5(*a, **k):
+        raise RuntimeError("h5py is not available in this container")
+    mod("serenade")
+    mod("serenade.utils", read_hdf5=_no_h5)
+    mod("serenade.vocoder")
+    layers = mod("serenade.vocoder.layers")
+    mod("serenade.vocoder.models")
+    out = None
+    for dotted, rel in (("serenade.vocoder.layers.causal_conv", "serenade/vocoder/layers/causal_conv.py"),
+                        ("serenade.vocoder.layers.residual_block", "serenade/vocoder/layers/residual_block.py"),
+                        ("serenade.vocoder.models.hifigan", "serenade/vocoder/models/hifigan.py")):
+        spec = importlib.util.spec_from_file_location(dotted, os.path.join(REFERENCE_ROOT, rel))
+        m = importlib.util.module_from_spec(spec)
+        sys.modules[dotted] = m
+        spec.loader.exec_module(m)
+        for k in dir(m):                      # the package __init__ does `from .x import *`
+            if not k.startswith("_") and not hasattr(layers, k) and "layers" in dotted:
+                setattr(layers, k, getattr(m, k))
+        out = m
+    _cache["hifigan"] = out
+    return out
+

@@ -299,3 +299,58 @@ def make_frontend_inputs(src_len: int, ref_len: int, seed: int = 99, batch: int 
                 midi=u(batch, src_len, 1), lft=u(batch, src_len, 1),
                 ref_x=n(batch, ref_len, input_dim), ref_lengths=torch.full((batch,), ref_len, dtype=torch.long),
                 ref_logmel=n(batch, ref_len, 80), ref_midi=u(batch, ref_len, 1), ref_lft=u(batch, ref_len, 1))
+
+
+# ----------------------------------------------------------------------------------------------------------
+# HiFi-GAN vocoder: parameter shapes of reference serenade/vocoder/models/hifigan.py:21-161 after
+# remove_weight_norm(), and a seeded synthetic state dict whose activations stay O(1) through all stages (the
+# reference's own reset_parameters draws N(0, 0.01), under which the signal decays to 1e-3: fine for parity, useless
+# as a numerical stress).
+def vocoder_param_shapes(in_channels: int = 80, out_channels: int = 1, channels: int = 512, kernel_size: int = 7,
+                         upsample_scales: Sequence[int] = (8, 8, 2, 2),
+                         upsample_kernel_sizes: Optional[Sequence[int]] = None,
+                         resblock_kernel_sizes: Sequence[int] = (3, 7, 11),
+                         n_dilations: int = 3) -> "OrderedDict[str, Tuple[int, ...]]":
+    if upsample_kernel_sizes is None:
+        upsample_kernel_sizes = [2 * s for s in upsample_scales]
+    sh: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
+    sh["input_conv.weight"] = (channels, in_channels, kernel_size)
+    sh["input_conv.bias"] = (channels,)
+    for i, (s, k) in enumerate(zip(upsample_scales, upsample_kernel_sizes)):
+        ci, co = channels // (2 ** i), channels // (2 ** (i + 1))
+        sh[f"upsamples.{i}.1.weight"] = (ci, co, k)          # ConvTranspose1d: (in, out, k)
+        sh[f"upsamples.{i}.1.bias"] = (co,)
+        for j, rk in enumerate(resblock_kernel_sizes):
+            b = i * len(resblock_kernel_sizes) + j
+            for d in range(n_dilations):
+                for cv in ("convs1", "convs2"):
+                    sh[f"blocks.{b}.{cv}.{d}.1.weight"] = (co, co, rk)
+                    sh[f"blocks.{b}.{cv}.{d}.1.bias"] = (co,)
+    cl = channels // (2 ** len(upsample_scales))
+    sh["output_conv.1.weight"] = (out_channels, cl, kernel_size)
+    sh["output_conv.1.bias"] = (out_channels,)
+    return sh
+
+
+def make_vocoder_state_dict(seed: int = 0, **geometry) -> "OrderedDict[str, torch.Tensor]":
+    rng = np.random.Generator(np.random.PCG64(1000 + seed))
+    sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+    for key, shape in vocoder_param_shapes(**geometry).items():
+        if key.endswith(".bias"):
+            a = rng.uniform(-0.05, 0.05, size=shape)
+        elif key.startswith("upsamples."):
+            stride = shape[2] // 2
+            a = rng.standard_normal(shape) * np.sqrt(1.5 * stride / (shape[0] * shape[2]))    # taps per output = k / stride
+        elif ".convs2." in key:
+            a = rng.standard_normal(shape) * (0.5 / np.sqrt(shape[1] * shape[2]))             # residual branch: small
+        else:
+            a = rng.standard_normal(shape) * np.sqrt(1.5 / (shape[1] * shape[2]))
+        sd[key] = torch.from_numpy(a.astype(np.float32))
+    return sd
+
+
+def make_vocoder_input(frames: int, batch: int = 1, seed: int = 0, in_channels: int = 80) -> torch.Tensor:
+    """(B, T, 80) normalised mel, the layout `Vocoder.decode_batch` receives (vocoder.py:64)."""
+    rng = np.random.Generator(np.random.PCG64(2000 + seed))
+    return torch.from_numpy(rng.standard_normal((batch, frames, in_channels), dtype=np.float32))
+
