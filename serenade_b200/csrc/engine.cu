@@ -5,6 +5,7 @@
 #include "engine_plan.inl"
 #include "engine_run.inl"
 #include "engine_frontend.inl"
+#include "engine_vocoder.inl"
 
 namespace srn {
 

@@ -34,6 +34,10 @@ class EngineBase {
   virtual std::string profile_ops(int B, int T, int reps) = 0;
   virtual void content_encode(const float* x, int B, int L, float* out, cudaStream_t st) = 0;
   virtual void style_encode(const float* mel, int B, int L, float* out, cudaStream_t st) = 0;
+  virtual void vocoder_decode(const float* mel, const float* scale, const float* shift, int B, int T, float* wave,
+                              cudaStream_t st) = 0;
+  virtual int vocoder_hop() const = 0;
+  std::vector<int> voc_dilations = {1, 3, 5};     // HiFiGANResidualBlock dilations (not recoverable from the weights)
   int64_t launches = 0;
   bool use_graph = true;
   bool debug = false;

@@ -10,6 +10,7 @@
 #include "engine.h"
 #include "rowops.cuh"
 #include "frontops.cuh"
+#include "vocops.cuh"
 
 namespace srn {
 
@@ -130,6 +131,9 @@ class Engine : public EngineBase {
 #endif
   void content_encode(const float* x, int B, int L, float* out, cudaStream_t st) override;
   void style_encode(const float* mel, int B, int L, float* out, cudaStream_t st) override;
+  void vocoder_decode(const float* mel, const float* scale, const float* shift, int B, int T, float* wave,
+                      cudaStream_t st) override;
+  int vocoder_hop() const override { return voc_.present ? voc_.hop : 0; }
 
  private:
   static constexpr int BK = OpTraits<OT>::kBK;
@@ -160,7 +164,32 @@ class Engine : public EngineBase {
     float *wq = nullptr, *bq = nullptr, *kmat = nullptr, *vmat = nullptr, *wo = nullptr, *bo = nullptr;
   } front_;
   DevBuf fb_xpad_, fb_h_, fb_h2_, fb_apad_, fb_e_, fb_col_, fb_act0_, fb_act1_;
+  // HiFi-GAN vocoder (engine_vocoder.inl); optional: present only if vocoder.* weights were loaded
+  struct VocBlock {
+    int k = 0;
+    std::vector<OT*> w1, w2;          // per dilation: [Cp][k * Cp], [C][k * Cp]
+    std::vector<float*> b1, b2;
+  };
+  struct VocStage {
+    int s = 0, c = 0, cp = 0;         // stride, channels, channels padded to a K block
+    OT* w_up = nullptr;               // [s * C][3 * Cp_in]
+    float* b_up = nullptr;
+    std::vector<VocBlock> blocks;
+  };
+  struct VocW {
+    bool present = false;
+    int in_ch = 0, in_pad = 0, c0 = 0, k_in = 0, k_out = 0, n_blk = 0, n_dil = 0, hop = 1;
+    OT *w_in = nullptr, *w_out = nullptr;
+    float *b_in = nullptr, *b_out = nullptr;
+    std::vector<VocStage> stages;
+  } voc_;
+  DevBuf vb_ua_[2], vb_c_, vb_x_[4], vb_xa_, vb_ta_, vb_y4_;
+  bool decoder_present_ = false;
+  void pack_vocoder();
+  void voc_gemm(GemmParams& gp, const OT* W, int N, int K, const float* bias, int M, int nbatch, int mode, void* out,
+                long long out_bstride, int ldo, float slope, cudaStream_t st);
   void pack_frontend();
+  void pack_decoder(size_t n_est);
   void front_gemm(GemmParams& gp, const OT* W, int N, int K, const float* bias, int M, int nbatch, bool f32_out,
                   void* out, long long out_bstride, int ldo, float slope, cudaStream_t st);
   std::list<Plan<OT>> plans_;

@@ -59,7 +59,7 @@ void set_B_weight(GemmParams& gp, const OT* W, int N, int K, int bn) {
   gp.b_batch_mode = 0;
   if (OpTraits<OT>::kTF32) {
     const int n = gp.nseg;
-    if (2 * n > 16) fail("too many K segments");
+    if (2 * n > 24) fail("too many K segments");
     for (int i = 0; i < n; ++i) gp.seg[n + i] = gp.seg[i];
     gp.nseg = 2 * n;
     gp.nkb *= 2;
@@ -72,7 +72,7 @@ void set_D(GemmParams& gp, const T* ptr, int cols, int rows, long long bstride, 
   gp.out_cols = cols;
 }
 inline void add_seg(GemmParams& gp, int src, int col0, int shift, int nblk) {
-  if (gp.nseg >= 16) fail("too many K segments");
+  if (gp.nseg >= 24) fail("too many K segments");
   gp.seg[gp.nseg++] = KSeg{src, col0, shift, nblk};
   gp.nkb += nblk;
 }

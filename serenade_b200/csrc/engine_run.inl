@@ -492,7 +492,7 @@ void Engine<OT>::trace_row_op(Plan<OT>& pl, Op& op, cudaStream_t st) {
   }
   int mx = 0, used = 0;
   for (int i = 0; i < 256; ++i) { mx = std::max(mx, per_sm[i]); used += per_sm[i] > 0; }
-  fprintf(stderr, "[trace] %-18s blocks %d on %d SMs (max %d per SM) | stats %5.0f clk | first row %6.0f clk | block body %7.0f clk | "
+  fprintf(stderr, "[trace] %-18s blocks %d on %d SMs (max %d per SM) | stats+staging %5.0f clk | all rows but the last %6.0f clk | block body %7.0f clk | "
                   "span %6.1f us, mean block %5.1f us, mean concurrency %5.1f blocks, %d blocks start > 3 us late\n",
           op.name.c_str(), n, used, mx, med(stats_clk), med(row_clk), med(body_clk), (double)(g1 - g0) * 1e-3,
           n ? sum_ns / n * 1e-3 : 0.0, (g1 > g0) ? sum_ns / (double)(g1 - g0) : 0.0, late);

@@ -186,11 +186,25 @@ TfmW<OT> Engine<OT>::pack_tfm(const std::string& p) {
 
 template <typename OT>
 void Engine<OT>::finalize_weights() {
-  const int C = 512, te = 2048;
   arena_.clear();
   plans_.clear();
   resnets_.clear();
   tfms_.clear();
+  size_t n_est = 0;
+  for (const auto& kv : host_w_) n_est += kv.first.compare(0, 10, "estimator.") == 0;
+  decoder_present_ = n_est > 0;
+  if (decoder_present_) pack_decoder(n_est);
+  pack_frontend();      // optional encoder.* / gst.* weights of the conditioning front half
+  pack_vocoder();       // optional vocoder.* weights
+  if (!decoder_present_ && !front_.present && !voc_.present) fail("no weights were loaded");
+  host_w_.clear();
+  SRN_CUDA(cudaDeviceSynchronize());
+  finalized_ = true;
+}
+
+template <typename OT>
+void Engine<OT>::pack_decoder(size_t n_est) {
+  const int C = 512, te = 2048;
   time_w1_ = up_f32(hw("time_mlp.linear_1.weight", {te, cfg_.in_channels}).data);
   time_b1_ = up_f32(hw("time_mlp.linear_1.bias", {te}).data);
   time_w2_ = up_f32(hw("time_mlp.linear_2.weight", {te, te}).data);
@@ -244,14 +258,8 @@ void Engine<OT>::finalize_weights() {
     proj_b_ = up_f32(pb);
   }
   const size_t expected = 4 + resnets_.size() * 16 + tfms_.size() * 13 + 4 * 2 + 4 + 2;
-  size_t n_est = 0;
-  for (const auto& kv : host_w_) n_est += kv.first.compare(0, 10, "estimator.") == 0;
   if (n_est != expected)
     fail("state dict has %zu estimator tensors, the decoder expects %zu (unexpected extra keys?)", n_est, expected);
-  pack_frontend();      // optional encoder.* / gst.* weights of the conditioning front half
-  host_w_.clear();
-  SRN_CUDA(cudaDeviceSynchronize());
-  finalized_ = true;
 }
 
 }  // namespace srn

@@ -53,7 +53,7 @@ struct GemmParams {
   CUtensorMap mapD;    // output tile store: box = 32 rows x 128 bytes, SWIZZLE_128B (all epilogues but EULER)
   CUtensorMap mapD2;   // EPI_QKV: V^T store, box = 32 (d rows) x 32 (s, contiguous), no swizzle
   CUtensorMap mapR;      // EPI_RESID_OT (2-byte operands): the f32 residual as 32 x 32 boxes, like an f32 mapD
-  KSeg seg[16];
+  KSeg seg[24];
   int nseg;
   int nkb;          // total K blocks
   int ntn, ntm, nz; // tile grid: N tiles, M tiles, batch entries (persistent CTAs loop over ntn*ntm*nz tiles)
