@@ -77,6 +77,22 @@ int srn_solve_euler_host(SrnHandle* h, const float* z_host, const float* mu_host
 int srn_content_encode(SrnHandle* h, const float* x, int32_t B, int32_t L, float* enc_out, void* stream);
 int srn_style_encode(SrnHandle* h, const float* logmel, int32_t B, int32_t L, float* style_out, void* stream);
 
+/* HiFi-GAN vocoder, the stage after the CFM decoder in serenade-decode.  A handle may hold the
+ * vocoder alone: load the generator's state dict with keys "vocoder." + the reference's
+ * (serenade/vocoder/models/hifigan.py:21-161 after remove_weight_norm(): input_conv, upsamples.i.1, blocks.n.convs{1,2}.d.1,
+ * output_conv.1), then srn_finalize_weights.  Structure (stages, strides = kernel / 2, residual blocks, kernel sizes) is
+ * read off the weights; the residual blocks' dilations are not recoverable from them:
+ *   srn_vocoder_set_dilations  before srn_finalize_weights; default {1, 3, 5} (hifigan.py:32)
+ *   srn_vocoder_hop            samples per mel frame = product of the upsampling strides
+ *   srn_vocoder_decode         = Vocoder.decode_batch (vocoder/vocoder.py:64-75): mel (B, T, in_channels) f32 DEVICE, as the
+ *                              acoustic model returns it; scale / shift (DEVICE [in_channels], both or neither) fold
+ *                              the de-normalisation with the target statistics and the normalisation with the
+ *                              vocoder's (c * scale + shift); wave_out (B, T * hop) f32 DEVICE. */
+int srn_vocoder_set_dilations(SrnHandle* h, const int32_t* dilations, int32_t n);
+int srn_vocoder_hop(SrnHandle* h, int32_t* hop_out);
+int srn_vocoder_decode(SrnHandle* h, const float* mel, const float* scale, const float* shift, int32_t B, int32_t T,
+                       float* wave_out, void* stream);
+
 /* Number of kernels of this library launched since the handle was created. */
 int64_t srn_launch_count(const SrnHandle* h);
 /* Use one CUDA graph per (B, T, n_steps) for srn_solve_euler (default 1). */

@@ -163,6 +163,34 @@ SRN_EXPORT int srn_style_encode(SrnHandle* h, const float* logmel, int32_t B, in
   SRN_API_END
 }
 
+SRN_EXPORT int srn_vocoder_set_dilations(SrnHandle* h, const int32_t* dilations, int32_t n) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (dilations == nullptr || n < 1 || n > 8) srn::fail("srn_vocoder_set_dilations: 1..8 dilations expected");
+  h->eng->voc_dilations.assign(dilations, dilations + n);
+  for (int d : h->eng->voc_dilations)
+    if (d < 1) srn::fail("srn_vocoder_set_dilations: dilations must be >= 1");
+  SRN_API_END
+}
+
+SRN_EXPORT int srn_vocoder_hop(SrnHandle* h, int32_t* hop_out) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (hop_out == nullptr) srn::fail("srn_vocoder_hop: null pointer");
+  *hop_out = h->eng->vocoder_hop();
+  if (*hop_out == 0) srn::fail("vocoder weights (vocoder.*) were not loaded");
+  SRN_API_END
+}
+
+SRN_EXPORT int srn_vocoder_decode(SrnHandle* h, const float* mel, const float* scale, const float* shift, int32_t B,
+                                  int32_t T, float* wave_out, void* stream) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (mel == nullptr || wave_out == nullptr) srn::fail("srn_vocoder_decode: null pointer");
+  h->eng->vocoder_decode(mel, scale, shift, B, T, wave_out, static_cast<cudaStream_t>(stream));
+  SRN_API_END
+}
+
 SRN_EXPORT int64_t srn_launch_count(const SrnHandle* h) { return (h && h->eng) ? h->eng->launches : -1; }
 
 SRN_EXPORT int srn_set_use_graph(SrnHandle* h, int32_t enable) {
