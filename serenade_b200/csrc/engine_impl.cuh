@@ -167,11 +167,15 @@ class Engine : public EngineBase {
   // HiFi-GAN vocoder (engine_vocoder.inl); optional: present only if vocoder.* weights were loaded
   struct VocBlock {
     int k = 0;
-    std::vector<OT*> w1, w2;          // per dilation: [Cp][k * Cp], [C][k * Cp]
+    std::vector<OT*> w1, w2;          // per dilation: [n1][nseg * kc], [n2][nseg * kc]
     std::vector<float*> b1, b2;
+    std::vector<std::vector<int>> sh1, sh2;     // per dilation: row shift of every K segment
   };
   struct VocStage {
     int s = 0, c = 0, cp = 0;         // stride, channels, channels padded to a K block
+    // Channel counts below one K block (C = 32 in bf16): g = BK / C consecutive time steps form one GEMM row
+    // ([T][C] read as [T / g][g C], no padding); kc = K columns per segment, n1 / n2 = N of convs1 / convs2
+    int g = 1, kc = 0, n1 = 0, n2 = 0;
     OT* w_up = nullptr;               // [s * C][3 * Cp_in]
     float* b_up = nullptr;
     std::vector<VocBlock> blocks;
@@ -181,6 +185,8 @@ class Engine : public EngineBase {
     int in_ch = 0, in_pad = 0, c0 = 0, k_in = 0, k_out = 0, n_blk = 0, n_dil = 0, hop = 1;
     OT *w_in = nullptr, *w_out = nullptr;
     float *b_in = nullptr, *b_out = nullptr;
+    std::vector<int> sh_out;          // K segment shifts of the output conv
+    int g_out = 1, kc_out = 0;
     std::vector<VocStage> stages;
   } voc_;
   DevBuf vb_ua_[2], vb_c_, vb_x_[4], vb_xa_, vb_ta_, vb_y4_;

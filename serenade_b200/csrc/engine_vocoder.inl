@@ -41,6 +41,34 @@ void Engine<OT>::pack_vocoder() {
         for (int t = 0; t < k; ++t) pk[((size_t)o * k + t) * Ip + i] = w.data[((size_t)o * I + i) * k + t];
     return pk;
   };
+  // The same conv (dilation d, 'same' zero padding) on the grouped view: GEMM row q = time steps g q .. g q + g - 1.
+  // Output sub-step p, tap j reads time g q + p + (j - c) d = row q + shift, sub-step h; all (p, j) with one shift
+  // share a K segment.  Returns [Np][nseg * g I] and the segment shifts.  g = 1 with I padded is the plain form.
+  auto conv_pack_grouped = [&](const HostTensor& w, int g, int d, int Np, int kc, std::vector<int>& shifts) {
+    const int O = (int)w.dims[0], I = (int)w.dims[1], k = (int)w.dims[2], c = (k - 1) / 2;
+    auto fdiv = [](int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); };
+    shifts.clear();
+    for (int p = 0; p < g; ++p)
+      for (int j = 0; j < k; ++j) shifts.push_back(fdiv(p + (j - c) * d, g));
+    std::sort(shifts.begin(), shifts.end());
+    shifts.erase(std::unique(shifts.begin(), shifts.end()), shifts.end());
+    const int nseg = (int)shifts.size();
+    std::vector<float> pk((size_t)Np * nseg * kc, 0.f);
+    for (int p = 0; p < g; ++p)
+      for (int j = 0; j < k; ++j) {
+        const int tpos = p + (j - c) * d, sh = fdiv(tpos, g), h = tpos - sh * g;
+        const int seg = (int)(std::lower_bound(shifts.begin(), shifts.end(), sh) - shifts.begin());
+        for (int o = 0; o < O; ++o)
+          for (int i = 0; i < I; ++i)
+            pk[((size_t)(p * O + o) * nseg + seg) * kc + h * I + i] = w.data[((size_t)o * I + i) * k + j];
+      }
+    return pk;
+  };
+  auto tile_bias = [&](const std::vector<float>& b, int g) {
+    std::vector<float> o((size_t)round_up((int)b.size() * g, 128), 0.f);
+    for (int p = 0; p < g; ++p) std::copy(b.begin(), b.end(), o.begin() + (size_t)p * b.size());
+    return o;
+  };
   const HostTensor& win = any("input_conv.weight");
   if (win.dims.size() != 3 || win.dims[2] % 2 != 1) fail("vocoder.input_conv.weight must be (C, in, odd k)");
   VocW& v = voc_;
@@ -91,20 +119,45 @@ void Engine<OT>::pack_vocoder() {
     for (int phi = 0; phi < s; ++phi)
       for (int o = 0; o < co; ++o) bu[(size_t)phi * co + o] = b[o];
     sg.b_up = up_f32(bu);
+    // grouped rows when the channels do not fill a K block (every stage length is a multiple of its stride)
+    // (last stage only: an upsampling stage after it would want its operand padded to a K block)
+    sg.g = (i == n_up - 1 && co < BK && BK % co == 0 && s % (BK / co) == 0 && BK / co <= 4) ? BK / co : 1;
+    if (sg.g > 1) {      // every conv of the stage must fit the GEMM's K segments in the grouped form, else pad
+      auto fdiv = [](int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); };
+      for (int jb = 0; jb < v.n_blk && sg.g > 1; ++jb) {
+        const int k = (int)any("blocks." + std::to_string(i * v.n_blk + jb) + ".convs1.0.1.weight").dims[2];
+        for (int d : voc_dilations) {
+          std::vector<int> sh;
+          for (int p = 0; p < sg.g; ++p)
+            for (int j = 0; j < k; ++j) sh.push_back(fdiv(p + (j - (k - 1) / 2) * d, sg.g));
+          std::sort(sh.begin(), sh.end());
+          sh.erase(std::unique(sh.begin(), sh.end()), sh.end());
+          if ((int)sh.size() * (OpTraits<OT>::kTF32 ? 2 : 1) > 24) sg.g = 1;
+        }
+      }
+    }
+    sg.kc = sg.g > 1 ? sg.g * co : sg.cp;
+    sg.n1 = sg.g > 1 ? sg.g * co : sg.cp;
+    sg.n2 = sg.g * co;
     for (int jb = 0; jb < v.n_blk; ++jb) {
       VocBlock blk;
       const std::string p = "blocks." + std::to_string(i * v.n_blk + jb);
+      blk.sh1.resize(n_dil);
+      blk.sh2.resize(n_dil);
       for (int d = 0; d < n_dil; ++d) {
         const HostTensor& w1 = any(p + ".convs1." + std::to_string(d) + ".1.weight");
         const HostTensor& w2 = any(p + ".convs2." + std::to_string(d) + ".1.weight");
         if ((int)w1.dims[0] != co || (int)w1.dims[1] != co || w1.dims[2] % 2 != 1 || w2.dims != w1.dims)
           fail("vocoder.%s: unexpected conv shapes", p.c_str());
         blk.k = (int)w1.dims[2];
-        if (blk.k * (OpTraits<OT>::kTF32 ? 2 : 1) > 24) fail("vocoder: conv kernel size %d needs more K segments than the GEMM has", blk.k);
-        blk.w1.push_back(up_w(conv_pack(w1, sg.cp, sg.cp), sg.cp, blk.k * sg.cp));
-        blk.b1.push_back(up_f32(pad_to(any(p + ".convs1." + std::to_string(d) + ".1.bias").data, round_up(sg.cp, 128))));
-        blk.w2.push_back(up_w(conv_pack(w2, co, sg.cp), co, blk.k * sg.cp));
-        blk.b2.push_back(up_f32(pad_to(any(p + ".convs2." + std::to_string(d) + ".1.bias").data, round_up(co, 128))));
+        const std::vector<float> p1 = conv_pack_grouped(w1, sg.g, voc_dilations[d], sg.n1, sg.kc, blk.sh1[d]);
+        const std::vector<float> p2 = conv_pack_grouped(w2, sg.g, 1, sg.n2, sg.kc, blk.sh2[d]);
+        if ((int)std::max(blk.sh1[d].size(), blk.sh2[d].size()) * (OpTraits<OT>::kTF32 ? 2 : 1) > 24)
+          fail("vocoder: conv kernel size %d needs more K segments than the GEMM has", blk.k);
+        blk.w1.push_back(up_w(p1, sg.n1, (int)blk.sh1[d].size() * sg.kc));
+        blk.b1.push_back(up_f32(tile_bias(any(p + ".convs1." + std::to_string(d) + ".1.bias").data, sg.g)));
+        blk.w2.push_back(up_w(p2, sg.n2, (int)blk.sh2[d].size() * sg.kc));
+        blk.b2.push_back(up_f32(tile_bias(any(p + ".convs2." + std::to_string(d) + ".1.bias").data, sg.g)));
       }
       sg.blocks.push_back(std::move(blk));
     }
@@ -115,8 +168,15 @@ void Engine<OT>::pack_vocoder() {
   const HostTensor& wo = any("output_conv.1.weight");
   if ((int)wo.dims[0] != 1 || (int)wo.dims[1] != cin || wo.dims[2] % 2 != 1) fail("vocoder.output_conv.1.weight must be (1, C_last, odd k)");
   v.k_out = (int)wo.dims[2];
-  v.w_out = up_w(conv_pack(wo, 4, round_up(cin, BK)), 4, v.k_out * round_up(cin, BK));     // N padded to 4: 16-byte f32 rows
-  v.b_out = up_f32(pad_to(any("output_conv.1.bias").data, 128));
+  {   // output conv on the last stage's (possibly grouped) rows; N = g outputs per row, padded to 4 (16-byte f32 rows)
+    const VocStage& last = v.stages.back();
+    v.g_out = last.g;
+    v.kc_out = last.kc;
+    if (v.g_out > 4) fail("vocoder: unsupported channel count in the last stage");
+    const std::vector<float> po = conv_pack_grouped(wo, v.g_out, 1, 4, v.kc_out, v.sh_out);
+    v.w_out = up_w(po, 4, (int)v.sh_out.size() * v.kc_out);
+    v.b_out = up_f32(tile_bias(any("output_conv.1.bias").data, v.g_out));
+  }
   v.present = true;
 }
 
@@ -190,6 +250,10 @@ void Engine<OT>::vocoder_decode(const float* mel, const float* scale, const floa
     set_A<OT>(gp, 0, a, cp, t, t, cp, B);
     for (int j = 0; j < k; ++j) add_seg(gp, 0, 0, (j - (k - 1) / 2) * d, cp / BK);
   };
+  auto shift_segs = [&](GemmParams& gp, const OT* a, int kc, long long rows_per_clip, const std::vector<int>& shifts) {
+    set_A<OT>(gp, 0, a, kc, (int)rows_per_clip, rows_per_clip, kc, B);
+    for (int sh : shifts) add_seg(gp, 0, 0, sh, kc / BK);
+  };
   OT* ua = vb_ua_[0].template as<OT>();
   OT* ub = vb_ua_[1].template as<OT>();
   // normalised mel -> operand; input conv (hifigan.py:177), LeakyReLU of the first upsampling stage fused
@@ -221,8 +285,12 @@ void Engine<OT>::vocoder_decode(const float* mel, const float* scale, const floa
     }
     float* x[4] = {nullptr, nullptr, nullptr, nullptr};
     for (int j = 0; j < v.n_blk; ++j) x[j] = vb_x_[j].template as<float>();
+    // operand tensors of this stage: [T][cw] with cw = C (grouped rows, no padding) or C padded to a K block
+    const int cw = sg.g > 1 ? sg.c : sg.cp;
+    const long long tg = tn / sg.g;                  // GEMM rows per clip
+    if (tn % sg.g != 0) fail("vocoder: stage length not a multiple of the row group");
     // operand of every block's first conv + the blocks' own copies of the residual stream
-    launch_k(voc_lrelu_cast<OT>, blocks_for(rows * (sg.cp / 8)), dim3(256), st, (const float*)c, rows, sg.c, sg.cp, 0.1f, xa,
+    launch_k(voc_lrelu_cast<OT>, blocks_for(rows * (cw / 8)), dim3(256), st, (const float*)c, rows, sg.c, cw, 0.1f, xa,
              x[0], v.n_blk > 1 ? x[1] : (float*)nullptr, v.n_blk > 2 ? x[2] : (float*)nullptr);
     ++launches;
     if (v.n_blk > 3) SRN_CUDA(cudaMemcpyAsync(x[3], c, (size_t)rows * sg.c * sizeof(float), cudaMemcpyDeviceToDevice, st));
@@ -233,38 +301,42 @@ void Engine<OT>::vocoder_decode(const float* mel, const float* scale, const floa
         OT* a_in = xa;
         if (d > 0) {
           a_in = ub;      // (free here: ua holds this stage's input only until the transposed conv above has run)
-          launch_k(voc_lrelu_cast<OT>, blocks_for(rows * (sg.cp / 8)), dim3(256), st, (const float*)x[j], rows, sg.c, sg.cp,
+          launch_k(voc_lrelu_cast<OT>, blocks_for(rows * (cw / 8)), dim3(256), st, (const float*)x[j], rows, sg.c, cw,
                    0.1f, a_in, (float*)nullptr, (float*)nullptr, (float*)nullptr);
           ++launches;
         }
         {   // xt = convs1[d](x): LeakyReLU + dilated conv (residual_block.py:253); the LeakyReLU of convs2 is fused
           GemmParams gp = base();
-          conv_segs(gp, a_in, sg.cp, (int)tn, blk.k, voc_dilations[d]);
-          voc_gemm(gp, blk.w1[d], sg.cp, blk.k * sg.cp, blk.b1[d], (int)tn, B, VOC_OT, ta, tn * sg.cp, sg.cp, 0.1f, st);
+          shift_segs(gp, a_in, sg.kc, tg, blk.sh1[d]);
+          voc_gemm(gp, blk.w1[d], sg.n1, (int)blk.sh1[d].size() * sg.kc, blk.b1[d], (int)tg, B, VOC_OT, ta, tg * sg.n1, sg.n1,
+                   0.1f, st);
         }
         {   // x = convs2[d](xt) + x (residual_block.py:255-256)
           GemmParams gp = base();
-          conv_segs(gp, ta, sg.cp, (int)tn, blk.k, 1);
-          voc_gemm(gp, blk.w2[d], sg.c, blk.k * sg.cp, blk.b2[d], (int)tn, B, VOC_RESID, x[j], tn * sg.c, sg.c, 1.0f, st);
+          shift_segs(gp, ta, sg.kc, tg, blk.sh2[d]);
+          voc_gemm(gp, blk.w2[d], sg.n2, (int)blk.sh2[d].size() * sg.kc, blk.b2[d], (int)tg, B, VOC_RESID, x[j], tg * sg.n2,
+                   sg.n2, 1.0f, st);
         }
       }
     }
     // c = mean of the blocks (hifigan.py:180-183); next consumer's LeakyReLU fused: 0.1 before an upsampling stage,
     // torch's default 0.01 before the output conv (hifigan.py:137-140)
     const bool last = i + 1 == v.stages.size();
-    launch_k(voc_mean_lrelu<OT>, blocks_for(rows * (sg.cp / 8)), dim3(256), st, (const float*)x[0], (const float*)x[1],
-             (const float*)x[2], (const float*)x[3], v.n_blk, rows, sg.c, sg.cp, last ? 0.01f : 0.1f, ua);
+    launch_k(voc_mean_lrelu<OT>, blocks_for(rows * (cw / 8)), dim3(256), st, (const float*)x[0], (const float*)x[1],
+             (const float*)x[2], (const float*)x[3], v.n_blk, rows, sg.c, cw, last ? 0.01f : 0.1f, ua);
     ++launches;
     t = tn;
-    cin_p = sg.cp;
+    cin_p = cw;
   }
-  {   // output conv k7 -> 1 channel (N padded to 4), then tanh
+  {   // output conv k7 -> 1 channel (g per grouped row, N padded to 4), then tanh
     GemmParams gp = base();
-    conv_segs(gp, ua, cin_p, (int)t, v.k_out, 1);
-    voc_gemm(gp, v.w_out, 4, v.k_out * cin_p, v.b_out, (int)t, B, VOC_F32, vb_y4_.template as<float>(), t * 4, 4, 1.0f, st);
+    const long long tg = t / v.g_out;
+    shift_segs(gp, ua, v.kc_out, tg, v.sh_out);
+    voc_gemm(gp, v.w_out, 4, (int)v.sh_out.size() * v.kc_out, v.b_out, (int)tg, B, VOC_F32, vb_y4_.template as<float>(), tg * 4,
+             4, 1.0f, st);
   }
   launch_k(voc_tanh_out, blocks_for((long long)B * t), dim3(256), st, (const float*)vb_y4_.template as<float>(),
-           (long long)B * t, 4, wave);
+           (long long)B * t, v.g_out, 4, wave);
   ++launches;
   SRN_CUDA(cudaGetLastError());
 }

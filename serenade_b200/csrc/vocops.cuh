@@ -96,12 +96,13 @@ __global__ void __launch_bounds__(256) voc_mean_lrelu(const float* __restrict__ 
   store8_op(dst + r * Cp + c, v);
 }
 
-__global__ void __launch_bounds__(256) voc_tanh_out(const float* __restrict__ y4, long long rows, int ld,
+// y: [rows / g][ld] f32, sample r = column r % g of row r / g
+__global__ void __launch_bounds__(256) voc_tanh_out(const float* __restrict__ y, long long rows, int g, int ld,
                                                     float* __restrict__ wave) {
   pdl_launch_dependents();
   pdl_wait();
   const long long r = (long long)blockIdx.x * 256 + threadIdx.x;
-  if (r < rows) wave[r] = tanhf(y4[r * ld]);
+  if (r < rows) wave[r] = tanhf(y[(r / g) * ld + (r % g)]);
 }
 
 }  // namespace srn
