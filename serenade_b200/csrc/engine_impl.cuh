@@ -189,7 +189,15 @@ class Engine : public EngineBase {
     int g_out = 1, kc_out = 0;
     std::vector<VocStage> stages;
   } voc_;
-  DevBuf vb_ua_[2], vb_c_, vb_x_[4], vb_xa_, vb_ta_, vb_y4_;
+  DevBuf vb_ua_[2], vb_c_, vb_x_[4], vb_xa_, vb_ta_, vb_y4_, vb_mel_, vb_wave_, vb_aff_;
+  struct VocGraph {
+    int B = 0, T = 0;
+    bool affine = false;
+    cudaGraphExec_t exec = nullptr;
+    int64_t nodes = 0;
+  };
+  std::list<VocGraph> voc_graphs_;
+  void voc_body(const float* mel, const float* scale, const float* shift, int B, int T, float* wave, cudaStream_t st);
   bool decoder_present_ = false;
   void pack_vocoder();
   void voc_gemm(GemmParams& gp, const OT* W, int N, int K, const float* bias, int M, int nbatch, int mode, void* out,

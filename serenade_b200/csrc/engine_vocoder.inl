@@ -209,6 +209,9 @@ void Engine<OT>::voc_gemm(GemmParams& gp, const OT* W, int N, int K, const float
   launch_gemm(gp, bn, dim3(cdiv(N, bn), mtiles, nbatch), st);
 }
 
+// Public entry: one CUDA graph per (B, T).  Inputs are staged into engine-owned buffers (a graph bakes its pointers),
+// the ~120 launches of the generator replay as one graph launch, the waveform is copied out.  For a single 5 s clip
+// the per-launch host work (a tensor-map encode per operand) is otherwise longer than the kernels.
 template <typename OT>
 void Engine<OT>::vocoder_decode(const float* mel, const float* scale, const float* shift, int B, int T, float* wave,
                                 cudaStream_t st) {
@@ -229,13 +232,85 @@ void Engine<OT>::vocoder_decode(const float* mel, const float* scale, const floa
     }
   }
   ua_max = std::max(ua_max, op_max);
-  grow(vb_ua_[0], (size_t)ua_max * sizeof(OT));
-  grow(vb_ua_[1], (size_t)ua_max * sizeof(OT));
-  grow(vb_c_, (size_t)f32_max * sizeof(float));
-  for (int j = 0; j < v.n_blk; ++j) grow(vb_x_[j], (size_t)f32_max * sizeof(float));
-  grow(vb_xa_, (size_t)op_max * sizeof(OT));
-  grow(vb_ta_, (size_t)op_max * sizeof(OT));
-  grow(vb_y4_, (size_t)rows_max * 4 * sizeof(float));
+  bool moved = false;      // a scratch buffer was reallocated: graphs that baked its address are stale
+  auto grow_t = [&](DevBuf& b, size_t bytes) {
+    if (b.bytes < bytes) {
+      b.alloc(bytes);
+      moved = true;
+    }
+  };
+  grow_t(vb_ua_[0], (size_t)ua_max * sizeof(OT));
+  grow_t(vb_ua_[1], (size_t)ua_max * sizeof(OT));
+  grow_t(vb_c_, (size_t)f32_max * sizeof(float));
+  for (int j = 0; j < v.n_blk; ++j) grow_t(vb_x_[j], (size_t)f32_max * sizeof(float));
+  grow_t(vb_xa_, (size_t)op_max * sizeof(OT));
+  grow_t(vb_ta_, (size_t)op_max * sizeof(OT));
+  grow_t(vb_y4_, (size_t)rows_max * 4 * sizeof(float));
+  grow_t(vb_mel_, (size_t)B * T * v.in_ch * sizeof(float));
+  grow_t(vb_wave_, (size_t)rows_max * sizeof(float));
+  grow_t(vb_aff_, (size_t)2 * v.in_ch * sizeof(float));
+  if (moved) {
+    for (auto& g : voc_graphs_)
+      if (g.exec) cudaGraphExecDestroy(g.exec);
+    voc_graphs_.clear();
+  }
+  const bool affine = scale != nullptr;
+  const size_t mel_bytes = (size_t)B * T * v.in_ch * sizeof(float);
+  const size_t wave_bytes = (size_t)B * T * v.hop * sizeof(float);
+  float* aff = vb_aff_.template as<float>();
+  if (!use_graph || debug) {
+    voc_body(mel, scale, shift, B, T, wave, st);
+    return;
+  }
+  SRN_CUDA(cudaMemcpyAsync(vb_mel_.p, mel, mel_bytes, cudaMemcpyDeviceToDevice, st));
+  if (affine) {
+    SRN_CUDA(cudaMemcpyAsync(aff, scale, (size_t)v.in_ch * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    SRN_CUDA(cudaMemcpyAsync(aff + v.in_ch, shift, (size_t)v.in_ch * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  }
+  VocGraph* vg = nullptr;
+  for (auto& g : voc_graphs_)
+    if (g.B == B && g.T == T && g.affine == affine) vg = &g;
+  if (vg == nullptr) {
+    if (voc_graphs_.size() >= 8) {
+      if (voc_graphs_.front().exec) cudaGraphExecDestroy(voc_graphs_.front().exec);
+      voc_graphs_.pop_front();
+    }
+    if (capture_stream_ == nullptr) SRN_CUDA(cudaStreamCreateWithFlags(&capture_stream_, cudaStreamNonBlocking));
+    const int64_t before = launches;
+    cudaGraph_t g = nullptr;
+    SRN_CUDA(cudaStreamBeginCapture(capture_stream_, cudaStreamCaptureModeThreadLocal));
+    try {
+      voc_body(vb_mel_.template as<float>(), affine ? aff : nullptr, affine ? aff + v.in_ch : nullptr, B, T,
+               vb_wave_.template as<float>(), capture_stream_);
+    } catch (...) {
+      cudaStreamEndCapture(capture_stream_, &g);
+      if (g) cudaGraphDestroy(g);
+      launches = before;
+      throw;
+    }
+    SRN_CUDA(cudaStreamEndCapture(capture_stream_, &g));
+    VocGraph ng;
+    ng.B = B;
+    ng.T = T;
+    ng.affine = affine;
+    ng.nodes = launches - before;
+    launches = before;
+    const cudaError_t e = cudaGraphInstantiate(&ng.exec, g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) fail("cudaGraphInstantiate (vocoder) failed: %s", cudaGetErrorString(e));
+    voc_graphs_.push_back(ng);
+    vg = &voc_graphs_.back();
+  }
+  SRN_CUDA(cudaGraphLaunch(vg->exec, st));
+  launches += vg->nodes;
+  SRN_CUDA(cudaMemcpyAsync(wave, vb_wave_.p, wave_bytes, cudaMemcpyDeviceToDevice, st));
+}
+
+// The generator itself (launches only; every scratch buffer is already large enough).
+template <typename OT>
+void Engine<OT>::voc_body(const float* mel, const float* scale, const float* shift, int B, int T, float* wave,
+                          cudaStream_t st) {
+  const VocW& v = voc_;
   auto base = [&]() {
     GemmParams gp;
     memset(&gp, 0, sizeof gp);

@@ -32,6 +32,9 @@ Engine<OT>::Engine(const SrnConfig& cfg) : cfg_(cfg) {
 
 template <typename OT>
 Engine<OT>::~Engine() {
+  for (auto& g : voc_graphs_)
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+  voc_graphs_.clear();
   plans_.clear();
   arena_.clear();
 }
@@ -186,6 +189,9 @@ TfmW<OT> Engine<OT>::pack_tfm(const std::string& p) {
 
 template <typename OT>
 void Engine<OT>::finalize_weights() {
+  for (auto& g : voc_graphs_)
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+  voc_graphs_.clear();
   arena_.clear();
   plans_.clear();
   resnets_.clear();
