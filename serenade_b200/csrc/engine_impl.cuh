@@ -170,12 +170,14 @@ class Engine : public EngineBase {
     std::vector<OT*> w1, w2;          // per dilation: [n1][nseg * kc], [n2][nseg * kc]
     std::vector<float*> b1, b2;
     std::vector<std::vector<int>> sh1, sh2;     // per dilation: row shift of every K segment
+    std::vector<int> g1, g2;                    // per dilation: time steps per GEMM row of convs1 / convs2
   };
   struct VocStage {
     int s = 0, c = 0, cp = 0;         // stride, channels, channels padded to a K block
     // Channel counts below one K block (C = 32 in bf16): g = BK / C consecutive time steps form one GEMM row
     // ([T][C] read as [T / g][g C], no padding); kc = K columns per segment, n1 / n2 = N of convs1 / convs2
-    int g = 1, kc = 0, n1 = 0, n2 = 0;
+    int g = 1;      // 1 = operand rows padded to cp (or C >= BK); > 1 = unpadded, every conv picks its own grouping
+    bool padded = false;
     OT* w_up = nullptr;               // [s * C][3 * Cp_in]
     float* b_up = nullptr;
     std::vector<VocBlock> blocks;

@@ -119,26 +119,40 @@ void Engine<OT>::pack_vocoder() {
     for (int phi = 0; phi < s; ++phi)
       for (int o = 0; o < co; ++o) bu[(size_t)phi * co + o] = b[o];
     sg.b_up = up_f32(bu);
-    // grouped rows when the channels do not fill a K block (every stage length is a multiple of its stride)
-    // (last stage only: an upsampling stage after it would want its operand padded to a K block)
-    sg.g = (i == n_up - 1 && co < BK && BK % co == 0 && s % (BK / co) == 0 && BK / co <= 4) ? BK / co : 1;
-    if (sg.g > 1) {      // every conv of the stage must fit the GEMM's K segments in the grouped form, else pad
+    // Row grouping.  The activations of a stage are flat [T][C] arrays, so a convolution may read and write them as
+    // [T / g][g C] for any g that divides the stage length: g C must be whole K blocks (no padding), at most one
+    // 128-column tile, and the conv's distinct row shifts must fit the GEMM's K segments.  Per conv the g with the
+    // fewest K blocks per time step wins (ties: the larger g - fuller tiles, all epilogue warps busy).
+    int hop_here = v.hop * s;
+    const int seg_limit = OpTraits<OT>::kTF32 ? 12 : 24;
+    auto n_shifts = [&](int g, int k, int d) {
       auto fdiv = [](int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); };
-      for (int jb = 0; jb < v.n_blk && sg.g > 1; ++jb) {
-        const int k = (int)any("blocks." + std::to_string(i * v.n_blk + jb) + ".convs1.0.1.weight").dims[2];
-        for (int d : voc_dilations) {
-          std::vector<int> sh;
-          for (int p = 0; p < sg.g; ++p)
-            for (int j = 0; j < k; ++j) sh.push_back(fdiv(p + (j - (k - 1) / 2) * d, sg.g));
-          std::sort(sh.begin(), sh.end());
-          sh.erase(std::unique(sh.begin(), sh.end()), sh.end());
-          if ((int)sh.size() * (OpTraits<OT>::kTF32 ? 2 : 1) > 24) sg.g = 1;
-        }
+      std::vector<int> sh;
+      for (int p = 0; p < g; ++p)
+        for (int jj = 0; jj < k; ++jj) sh.push_back(fdiv(p + (jj - (k - 1) / 2) * d, g));
+      std::sort(sh.begin(), sh.end());
+      sh.erase(std::unique(sh.begin(), sh.end()), sh.end());
+      return (int)sh.size();
+    };
+    auto pick_g = [&](int k, int d) {        // 0 = no unpadded grouping possible
+      int best = 0;
+      double best_cost = 1e30;
+      for (int g : {1, 2, 4}) {
+        if ((g * co) % BK != 0 || g * co > 128 || hop_here % g != 0) continue;
+        const int ns = n_shifts(g, k, d);
+        if (ns > seg_limit) continue;
+        const double cost = (double)ns * (g * co / BK) / g;
+        if (cost <= best_cost) { best_cost = cost; best = g; }
       }
+      return best;
+    };
+    sg.padded = false;
+    for (int jb = 0; jb < v.n_blk; ++jb) {
+      const int k = (int)any("blocks." + std::to_string(i * v.n_blk + jb) + ".convs1.0.1.weight").dims[2];
+      for (int d : voc_dilations)
+        if (pick_g(k, d) == 0 || pick_g(k, 1) == 0) sg.padded = true;
     }
-    sg.kc = sg.g > 1 ? sg.g * co : sg.cp;
-    sg.n1 = sg.g > 1 ? sg.g * co : sg.cp;
-    sg.n2 = sg.g * co;
+    if (i < n_up - 1 && co % BK != 0) sg.padded = true;      // the next transposed conv reads rows padded to a K block
     for (int jb = 0; jb < v.n_blk; ++jb) {
       VocBlock blk;
       const std::string p = "blocks." + std::to_string(i * v.n_blk + jb);
@@ -150,14 +164,19 @@ void Engine<OT>::pack_vocoder() {
         if ((int)w1.dims[0] != co || (int)w1.dims[1] != co || w1.dims[2] % 2 != 1 || w2.dims != w1.dims)
           fail("vocoder.%s: unexpected conv shapes", p.c_str());
         blk.k = (int)w1.dims[2];
-        const std::vector<float> p1 = conv_pack_grouped(w1, sg.g, voc_dilations[d], sg.n1, sg.kc, blk.sh1[d]);
-        const std::vector<float> p2 = conv_pack_grouped(w2, sg.g, 1, sg.n2, sg.kc, blk.sh2[d]);
-        if ((int)std::max(blk.sh1[d].size(), blk.sh2[d].size()) * (OpTraits<OT>::kTF32 ? 2 : 1) > 24)
+        const int ga = sg.padded ? 1 : pick_g(blk.k, voc_dilations[d]), gb = sg.padded ? 1 : pick_g(blk.k, 1);
+        const int kc1 = sg.padded ? sg.cp : ga * co, kc2 = sg.padded ? sg.cp : gb * co;
+        const int n1 = sg.padded ? sg.cp : ga * co, n2 = gb * co;
+        blk.g1.push_back(ga);
+        blk.g2.push_back(gb);
+        const std::vector<float> p1 = conv_pack_grouped(w1, ga, voc_dilations[d], n1, kc1, blk.sh1[d]);
+        const std::vector<float> p2 = conv_pack_grouped(w2, gb, 1, n2, kc2, blk.sh2[d]);
+        if ((int)std::max(blk.sh1[d].size(), blk.sh2[d].size()) > seg_limit)
           fail("vocoder: conv kernel size %d needs more K segments than the GEMM has", blk.k);
-        blk.w1.push_back(up_w(p1, sg.n1, (int)blk.sh1[d].size() * sg.kc));
-        blk.b1.push_back(up_f32(tile_bias(any(p + ".convs1." + std::to_string(d) + ".1.bias").data, sg.g)));
-        blk.w2.push_back(up_w(p2, sg.n2, (int)blk.sh2[d].size() * sg.kc));
-        blk.b2.push_back(up_f32(tile_bias(any(p + ".convs2." + std::to_string(d) + ".1.bias").data, sg.g)));
+        blk.w1.push_back(up_w(p1, n1, (int)blk.sh1[d].size() * kc1));
+        blk.b1.push_back(up_f32(tile_bias(any(p + ".convs1." + std::to_string(d) + ".1.bias").data, ga)));
+        blk.w2.push_back(up_w(p2, n2, (int)blk.sh2[d].size() * kc2));
+        blk.b2.push_back(up_f32(tile_bias(any(p + ".convs2." + std::to_string(d) + ".1.bias").data, gb)));
       }
       sg.blocks.push_back(std::move(blk));
     }
@@ -170,9 +189,14 @@ void Engine<OT>::pack_vocoder() {
   v.k_out = (int)wo.dims[2];
   {   // output conv on the last stage's (possibly grouped) rows; N = g outputs per row, padded to 4 (16-byte f32 rows)
     const VocStage& last = v.stages.back();
-    v.g_out = last.g;
-    v.kc_out = last.kc;
-    if (v.g_out > 4) fail("vocoder: unsupported channel count in the last stage");
+    v.g_out = 1;
+    v.kc_out = last.cp;
+    if (!last.padded)
+      for (int g : {1, 2, 4})
+        if ((g * last.c) % BK == 0 && g * last.c <= 128 && v.hop % g == 0) {
+          v.g_out = g;
+          v.kc_out = g * last.c;
+        }
     const std::vector<float> po = conv_pack_grouped(wo, v.g_out, 1, 4, v.kc_out, v.sh_out);
     v.w_out = up_w(po, 4, (int)v.sh_out.size() * v.kc_out);
     v.b_out = up_f32(tile_bias(any("output_conv.1.bias").data, v.g_out));
@@ -361,9 +385,7 @@ void Engine<OT>::voc_body(const float* mel, const float* scale, const float* shi
     float* x[4] = {nullptr, nullptr, nullptr, nullptr};
     for (int j = 0; j < v.n_blk; ++j) x[j] = vb_x_[j].template as<float>();
     // operand tensors of this stage: [T][cw] with cw = C (grouped rows, no padding) or C padded to a K block
-    const int cw = sg.g > 1 ? sg.c : sg.cp;
-    const long long tg = tn / sg.g;                  // GEMM rows per clip
-    if (tn % sg.g != 0) fail("vocoder: stage length not a multiple of the row group");
+    const int cw = sg.padded ? sg.cp : sg.c;
     // operand of every block's first conv + the blocks' own copies of the residual stream
     launch_k(voc_lrelu_cast<OT>, blocks_for(rows * (cw / 8)), dim3(256), st, (const float*)c, rows, sg.c, cw, 0.1f, xa,
              x[0], v.n_blk > 1 ? x[1] : (float*)nullptr, v.n_blk > 2 ? x[2] : (float*)nullptr);
@@ -382,15 +404,17 @@ void Engine<OT>::voc_body(const float* mel, const float* scale, const float* shi
         }
         {   // xt = convs1[d](x): LeakyReLU + dilated conv (residual_block.py:253); the LeakyReLU of convs2 is fused
           GemmParams gp = base();
-          shift_segs(gp, a_in, sg.kc, tg, blk.sh1[d]);
-          voc_gemm(gp, blk.w1[d], sg.n1, (int)blk.sh1[d].size() * sg.kc, blk.b1[d], (int)tg, B, VOC_OT, ta, tg * sg.n1, sg.n1,
-                   0.1f, st);
+          const int g = blk.g1[d], kc = sg.padded ? sg.cp : g * sg.c, n = kc;
+          const long long tg = tn / g;
+          shift_segs(gp, a_in, kc, tg, blk.sh1[d]);
+          voc_gemm(gp, blk.w1[d], n, (int)blk.sh1[d].size() * kc, blk.b1[d], (int)tg, B, VOC_OT, ta, tg * n, n, 0.1f, st);
         }
         {   // x = convs2[d](xt) + x (residual_block.py:255-256)
           GemmParams gp = base();
-          shift_segs(gp, ta, sg.kc, tg, blk.sh2[d]);
-          voc_gemm(gp, blk.w2[d], sg.n2, (int)blk.sh2[d].size() * sg.kc, blk.b2[d], (int)tg, B, VOC_RESID, x[j], tg * sg.n2,
-                   sg.n2, 1.0f, st);
+          const int g = blk.g2[d], kc = sg.padded ? sg.cp : g * sg.c, n = g * sg.c;
+          const long long tg = tn / g;
+          shift_segs(gp, ta, kc, tg, blk.sh2[d]);
+          voc_gemm(gp, blk.w2[d], n, (int)blk.sh2[d].size() * kc, blk.b2[d], (int)tg, B, VOC_RESID, x[j], tg * n, n, 1.0f, st);
         }
       }
     }
