@@ -1,7 +1,7 @@
 """Timing of the conditioning front half (content encoder, GST style encoder) and of the whole `Serenade.inference`
 on one GPU, next to the CPU oracle (port of the reference modules) on the host cores.
 
-    python tools/bench_frontend.py [out.txt]
+    python tests/bench_frontend.py [out.txt]
 """
 import os
 import sys

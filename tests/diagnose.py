@@ -1,12 +1,12 @@
 """GPU-box diagnostic: stage-by-stage error table vs the oracle (never stops at the first bad stage) and a
-quick CUDA-event timing of the solve.  Writes gpurun_out/diagnose.txt.   python tools/diagnose.py [--time]"""
+quick CUDA-event timing of the solve.  Writes gpurun_out/diagnose.txt.   python tests/diagnose.py [--time]"""
 import os
 import sys
 import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))   # (this file lives there: it runs the oracle as the checker)
 
 import torch  # noqa: E402
 

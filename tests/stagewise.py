@@ -1,4 +1,4 @@
-"""Stage-by-stage comparison of the CUDA path with the oracle (shared by the GPU tests and tools/diagnose.py).
+"""Stage-by-stage comparison of the CUDA path with the oracle (shared by the GPU tests and tests/diagnose.py).
 
 The C ABI's debug hook (srn_debug_enable / srn_debug_fetch) keeps named intermediates of one estimator call
 as channels-last (nb, rows, cols) f32; the oracle's `tap` callback yields the matching block outputs, and

@@ -9,11 +9,11 @@ mkdir -p $O
 nvidia-smi --query-gpu=name,clocks.max.sm,clocks.sm,power.limit --format=csv > $O/${TAG}_smi.txt 2>&1
 timeout 900 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?" | tee -a $O/${TAG}_pytest.log
 tail -5 $O/${TAG}_pytest.log
-timeout 300 python tools/diagnose.py --tf32 > $O/${TAG}_diag_tf32.log 2>&1; echo "diag tf32 rc=$?"; cp $O/diagnose.txt $O/${TAG}_diagnose_tf32.txt
+timeout 300 python tests/diagnose.py --tf32 > $O/${TAG}_diag_tf32.log 2>&1; echo "diag tf32 rc=$?"; cp $O/diagnose.txt $O/${TAG}_diagnose_tf32.txt
 grep -E "final|lengths" $O/${TAG}_diagnose_tf32.txt | head
-timeout 300 python tools/diagnose.py --time > $O/${TAG}_diag_bf16.log 2>&1; echo "diag bf16 rc=$?"; cp $O/diagnose.txt $O/${TAG}_diagnose_bf16.txt
+timeout 300 python tests/diagnose.py --time > $O/${TAG}_diag_bf16.log 2>&1; echo "diag bf16 rc=$?"; cp $O/diagnose.txt $O/${TAG}_diagnose_bf16.txt
 grep "B=" $O/${TAG}_diagnose_bf16.txt
-SRN_DISABLE_PDL=1 timeout 300 python tools/diagnose.py --time > $O/${TAG}_diag_nopdl.log 2>&1; echo "diag nopdl rc=$?"
+SRN_DISABLE_PDL=1 timeout 300 python tests/diagnose.py --time > $O/${TAG}_diag_nopdl.log 2>&1; echo "diag nopdl rc=$?"
 grep "B=" $O/${TAG}_diag_nopdl.log
 timeout 600 python bench.py > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench rc=$?"
 tail -c 2500 $O/${TAG}_bench.json
