@@ -121,7 +121,7 @@ void Engine<OT>::pack_vocoder() {
     sg.b_up = up_f32(bu);
     // Row grouping.  The activations of a stage are flat [T][C] arrays, so a convolution may read and write them as
     // [T / g][g C] for any g that divides the stage length: g C must be whole K blocks (no padding), at most one
-    // 128-column tile, and the conv's distinct row shifts must fit the GEMM's K segments.  Per conv the g with the
+    // 256-column tile, and the conv's distinct row shifts must fit the GEMM's K segments.  Per conv the g with the
     // fewest K blocks per time step wins (ties: the larger g - fuller tiles, all epilogue warps busy).
     int hop_here = v.hop * s;
     const int seg_limit = OpTraits<OT>::kTF32 ? 12 : 24;
@@ -137,8 +137,8 @@ void Engine<OT>::pack_vocoder() {
     auto pick_g = [&](int k, int d) {        // 0 = no unpadded grouping possible
       int best = 0;
       double best_cost = 1e30;
-      for (int g : {1, 2, 4}) {
-        if ((g * co) % BK != 0 || g * co > 128 || hop_here % g != 0) continue;
+      for (int g : {1, 2, 4, 8}) {
+        if ((g * co) % BK != 0 || g * co > 256 || hop_here % g != 0) continue;
         const int ns = n_shifts(g, k, d);
         if (ns > seg_limit) continue;
         const double cost = (double)ns * (g * co / BK) / g;
