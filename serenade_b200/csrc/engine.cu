@@ -33,6 +33,7 @@ static void configure_bn() {
   configure_one<OT, BN, EPI_ROWMAX>();
   configure_one<OT, BN, EPI_EXP>();
   configure_one<OT, BN, EPI_PV>();
+  configure_one<OT, BN, EPI_RESID_ACT>();
 }
 
 template <typename OT>

@@ -203,7 +203,8 @@ class Engine : public EngineBase {
   bool decoder_present_ = false;
   void pack_vocoder();
   void voc_gemm(GemmParams& gp, const OT* W, int N, int K, const float* bias, int M, int nbatch, int mode, void* out,
-                long long out_bstride, int ldo, float slope, cudaStream_t st);
+                long long out_bstride, int ldo, float slope, cudaStream_t st, const float* resid = nullptr,
+                OT* act_out = nullptr);
   void pack_frontend();
   void pack_decoder(size_t n_est);
   void front_gemm(GemmParams& gp, const OT* W, int N, int K, const float* bias, int M, int nbatch, bool f32_out,

@@ -14,7 +14,7 @@
 namespace srn {
 
 namespace {
-enum VocOut { VOC_F32 = 0, VOC_OT = 1, VOC_RESID = 2 };
+enum VocOut { VOC_F32 = 0, VOC_OT = 1, VOC_RESID = 2, VOC_RESID_ACT = 3 };
 inline std::vector<float> pad_to(const std::vector<float>& v, size_t n) {
   std::vector<float> o(n, 0.f);
   std::copy(v.begin(), v.end(), o.begin());
@@ -207,7 +207,8 @@ void Engine<OT>::pack_vocoder() {
 // One GEMM of the vocoder.  The A segments of `gp` are already set.
 template <typename OT>
 void Engine<OT>::voc_gemm(GemmParams& gp, const OT* W, int N, int K, const float* bias, int M, int nbatch, int mode,
-                          void* out, long long out_bstride, int ldo, float slope, cudaStream_t st) {
+                          void* out, long long out_bstride, int ldo, float slope, cudaStream_t st, const float* resid,
+                          OT* act_out) {
   const int mtiles = cdiv(M, 256);
   const int bn = pick_bn(N, (long long)mtiles * nbatch);
   set_B_weight<OT>(gp, W, N, K, bn);
@@ -221,6 +222,13 @@ void Engine<OT>::voc_gemm(GemmParams& gp, const OT* W, int N, int K, const float
   if (mode == VOC_OT) {
     gp.epi = EPI_STORE_OT;
     set_D<OT>(gp, static_cast<OT*>(out), N, M, out_bstride, ldo, nbatch);
+  } else if (mode == VOC_RESID_ACT) {
+    // out f32 = resid + conv (resid may be `out` itself); act_out = LeakyReLU(out) as the next conv's operand
+    if (sizeof(OT) != 2 || N % 64 != 0) fail("vocoder: fused residual + activation needs 2-byte operands and N % 64 == 0");
+    gp.epi = EPI_RESID_ACT;
+    set_D<float>(gp, static_cast<float*>(out), N, M, out_bstride, ldo, nbatch);
+    gp.mapR = make_tmap_3d(resid, sizeof(float), N, M, nbatch, ldo, (uint64_t)out_bstride, 32, 32);
+    gp.mapD2 = make_tmap_3d(act_out, sizeof(OT), N, M, nbatch, ldo, (uint64_t)out_bstride, 128 / sizeof(OT), 32);
   } else {
     gp.epi = mode == VOC_RESID ? EPI_RESID_F32 : EPI_STORE_F32;
     if (mode == VOC_RESID) {
@@ -386,18 +394,24 @@ void Engine<OT>::voc_body(const float* mel, const float* scale, const float* shi
     for (int j = 0; j < v.n_blk; ++j) x[j] = vb_x_[j].template as<float>();
     // operand tensors of this stage: [T][cw] with cw = C (grouped rows, no padding) or C padded to a K block
     const int cw = sg.padded ? sg.cp : sg.c;
-    // operand of every block's first conv + the blocks' own copies of the residual stream
+    // 2-byte operands, unpadded rows: every second conv adds its residual from a TMA-loaded box, stores the f32
+    // stream AND its LeakyReLU'd operand copy (EPI_RESID_ACT) - no cast pass between dilations, and the blocks'
+    // streams start from `c` directly (no copies).  Otherwise: cast kernels + in-place reduce-add.
+    const bool fuse = sizeof(OT) == 2 && !sg.padded;
+    // operand of every block's first conv [+ the blocks' own copies of the residual stream]
     launch_k(voc_lrelu_cast<OT>, blocks_for(rows * (cw / 8)), dim3(256), st, (const float*)c, rows, sg.c, cw, 0.1f, xa,
-             x[0], v.n_blk > 1 ? x[1] : (float*)nullptr, v.n_blk > 2 ? x[2] : (float*)nullptr);
+             fuse ? (float*)nullptr : x[0], !fuse && v.n_blk > 1 ? x[1] : (float*)nullptr,
+             !fuse && v.n_blk > 2 ? x[2] : (float*)nullptr);
     ++launches;
-    if (v.n_blk > 3) SRN_CUDA(cudaMemcpyAsync(x[3], c, (size_t)rows * sg.c * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    if (!fuse && v.n_blk > 3)
+      SRN_CUDA(cudaMemcpyAsync(x[3], c, (size_t)rows * sg.c * sizeof(float), cudaMemcpyDeviceToDevice, st));
     for (int j = 0; j < v.n_blk; ++j) {
       const VocBlock& blk = sg.blocks[j];
       for (int d = 0; d < v.n_dil; ++d) {
         // every block's first operand is LeakyReLU(c) = xa, shared; afterwards LeakyReLU of its own stream
         OT* a_in = xa;
-        if (d > 0) {
-          a_in = ub;      // (free here: ua holds this stage's input only until the transposed conv above has run)
+        if (d > 0) a_in = ub;      // (free here: ua holds this stage's input only until the transposed conv above has run)
+        if (d > 0 && !fuse) {
           launch_k(voc_lrelu_cast<OT>, blocks_for(rows * (cw / 8)), dim3(256), st, (const float*)x[j], rows, sg.c, cw,
                    0.1f, a_in, (float*)nullptr, (float*)nullptr, (float*)nullptr);
           ++launches;
@@ -414,7 +428,11 @@ void Engine<OT>::voc_body(const float* mel, const float* scale, const float* shi
           const int g = blk.g2[d], kc = sg.padded ? sg.cp : g * sg.c, n = g * sg.c;
           const long long tg = tn / g;
           shift_segs(gp, ta, kc, tg, blk.sh2[d]);
-          voc_gemm(gp, blk.w2[d], n, (int)blk.sh2[d].size() * kc, blk.b2[d], (int)tg, B, VOC_RESID, x[j], tg * n, n, 1.0f, st);
+          if (fuse && (d == 0 || d + 1 < v.n_dil))      // (d == 0: the residual is c, not x[j]; the last operand copy is unused)
+            voc_gemm(gp, blk.w2[d], n, (int)blk.sh2[d].size() * kc, blk.b2[d], (int)tg, B, VOC_RESID_ACT, x[j], tg * n, n, 0.1f,
+                     st, d == 0 ? c : x[j], ub);
+          else
+            voc_gemm(gp, blk.w2[d], n, (int)blk.sh2[d].size() * kc, blk.b2[d], (int)tg, B, VOC_RESID, x[j], tg * n, n, 1.0f, st);
         }
       }
     }

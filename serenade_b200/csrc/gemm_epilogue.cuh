@@ -61,8 +61,9 @@ __device__ __forceinline__ void stager_put(Stager& s, int lane, const float (&v)
 #endif
 template <typename OutT>
 __device__ __forceinline__ void stager_flush(Stager& s, int lane, const GemmParams& p, int col, int row0, int batch,
-                                             bool reduce_add = false) {
+                                             bool reduce_add = false, const CUtensorMap* map = nullptr) {
   if (s.fill < 128) return;
+  if (map == nullptr) map = &p.mapD;
 #if SRN_DIRECT_STORE
   __syncwarp();
   constexpr int kPiece = 16 / (int)sizeof(OutT);
@@ -89,12 +90,12 @@ __device__ __forceinline__ void stager_flush(Stager& s, int lane, const GemmPara
       // out += box, the addition done by the L2 (f32, every element touched once: deterministic): the residual
       // stream is updated in place without the SM ever reading it
       asm volatile("cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
-                       reinterpret_cast<uint64_t>(&p.mapD)),
+                       reinterpret_cast<uint64_t>(map)),
                    "r"(s.box()), "r"(col), "r"(row0), "r"(batch)
                    : "memory");
     } else {
       asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
-                       reinterpret_cast<uint64_t>(&p.mapD)),
+                       reinterpret_cast<uint64_t>(map)),
                    "r"(s.box()), "r"(col), "r"(row0), "r"(batch)
                    : "memory");
     }

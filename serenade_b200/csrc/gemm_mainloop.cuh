@@ -233,7 +233,10 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       // instruction (clock64 trace: 2750 clk per chunk, all L1 wavefronts).  Its two output boxes per tile need only
       // ONE staging box in flight, so the warp's second box receives the residual chunk by chunk through TMA, one
       // chunk ahead (kResidTma); the other precisions keep the register path.
-      constexpr bool kResidTma = EPI == EPI_RESID_OT && sizeof(OT) == 2 && !SRN_DIRECT_STORE;
+      // EPI_RESID_ACT: the same residual box, but the sum goes back INTO the box and is stored from there as the f32
+      // stream (mapD) while its activated 2-byte copy leaves through the warp's other box (mapD2).
+      constexpr bool kAct = EPI == EPI_RESID_ACT && sizeof(OT) == 2;
+      constexpr bool kResidTma = (EPI == EPI_RESID_OT || kAct) && sizeof(OT) == 2 && !SRN_DIRECT_STORE;
       constexpr bool kResid = (EPI == EPI_RESID_OT && !kResidTma) || (EPI == EPI_RESID_F32 && SRN_DIRECT_STORE);
       float4 r4[kResid ? 8 : 1];
       const float4* rs = nullptr;
@@ -247,6 +250,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       if constexpr (kResidTma) {
         __syncwarp();      // the previous tile's reads of the residual box are done
         if (lane == 0 && nvalid > 0) {
+          if constexpr (kAct) tma_store_wait_read<0>();      // ... and so is the store of its last chunk
           mbar_expect_tx(&resid_bar[warp - 2], 4096);
           tma_load_3d(reinterpret_cast<void*>(smem + CFG::kStgOff + (warp - 2) * 8192 + 4096), &p.mapR, &resid_bar[warp - 2],
                       n0 + c_first * 32, row0, b);
@@ -302,11 +306,27 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
                          : "r"(rbox + ((i ^ (lane & 7)) << 4)));
             v[4 * i + 0] += rv.x; v[4 * i + 1] += rv.y; v[4 * i + 2] += rv.z; v[4 * i + 3] += rv.w;
           }
-          __syncwarp();      // every lane has its row: the box may receive the next chunk
-          if (lane == 0 && cc + 1 < nvalid) {
-            mbar_expect_tx(&resid_bar[warp - 2], 4096);
-            tma_load_3d(reinterpret_cast<void*>(smem + CFG::kStgOff + (warp - 2) * 8192 + 4096), &p.mapR,
-                        &resid_bar[warp - 2], nc + 32, row0, b);
+          if constexpr (kAct) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              st_shared_v4(rbox + ((i ^ (lane & 7)) << 4), __float_as_uint(v[4 * i + 0]), __float_as_uint(v[4 * i + 1]),
+                           __float_as_uint(v[4 * i + 2]), __float_as_uint(v[4 * i + 3]));
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                               reinterpret_cast<uint64_t>(&p.mapD)),
+                           "r"(st.base + 4096), "r"(nc), "r"(row0), "r"(b)
+                           : "memory");
+              tma_store_commit();
+            }
+          } else {
+            __syncwarp();      // every lane has its row: the box may receive the next chunk
+            if (lane == 0 && cc + 1 < nvalid) {
+              mbar_expect_tx(&resid_bar[warp - 2], 4096);
+              tma_load_3d(reinterpret_cast<void*>(smem + CFG::kStgOff + (warp - 2) * 8192 + 4096), &p.mapR,
+                          &resid_bar[warp - 2], nc + 32, row0, b);
+            }
           }
         }
         if constexpr (kResid) {
@@ -333,6 +353,14 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           for (int j = 0; j < NCH / 2; ++j) kbits = j == cc ? keybits[j] : kbits;    // keeps keybits[] in registers
         }
         epilogue_chunk<OT, EPI>(p, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss, racc, rowc, kbits, gn_ok);
+        if constexpr (kAct) {
+          if (lane == 0 && cc + 1 < nvalid) {      // the box's store has been read: fetch the next residual chunk
+            tma_store_wait_read<0>();
+            mbar_expect_tx(&resid_bar[warp - 2], 4096);
+            tma_load_3d(reinterpret_cast<void*>(smem + CFG::kStgOff + (warp - 2) * 8192 + 4096), &p.mapR,
+                        &resid_bar[warp - 2], nc + 32, row0, b);
+          }
+        }
         if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
           // one partial per 64-key slice, whatever the tile shape: the order in which the row sum is formed (here
           // and in the P~ V epilogue) is then independent of BN, i.e. of the batch size the plan was built for
