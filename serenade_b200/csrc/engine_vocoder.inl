@@ -227,7 +227,8 @@ void Engine<OT>::voc_gemm(GemmParams& gp, const OT* W, int N, int K, const float
     if (sizeof(OT) != 2 || N % 64 != 0) fail("vocoder: fused residual + activation needs 2-byte operands and N % 64 == 0");
     gp.epi = EPI_RESID_ACT;
     set_D<float>(gp, static_cast<float*>(out), N, M, out_bstride, ldo, nbatch);
-    gp.mapR = make_tmap_3d(resid, sizeof(float), N, M, nbatch, ldo, (uint64_t)out_bstride, 32, 32);
+    gp.resid = resid;      // null: no residual, only the two stores
+    if (resid != nullptr) gp.mapR = make_tmap_3d(resid, sizeof(float), N, M, nbatch, ldo, (uint64_t)out_bstride, 32, 32);
     gp.mapD2 = make_tmap_3d(act_out, sizeof(OT), N, M, nbatch, ldo, (uint64_t)out_bstride, 128 / sizeof(OT), 32);
   } else {
     gp.epi = mode == VOC_RESID ? EPI_RESID_F32 : EPI_STORE_F32;
@@ -382,27 +383,34 @@ void Engine<OT>::voc_body(const float* mel, const float* scale, const float* shi
     const VocStage& sg = v.stages[i];
     const long long tn = t * sg.s, rows = (long long)B * tn;
     if (tn > 0x7fffffffLL / 2) fail("vocoder: sequence too long");
+    // 2-byte operands, unpadded rows: every second conv adds its residual from a TMA-loaded box, stores the f32
+    // stream AND its LeakyReLU'd operand copy (EPI_RESID_ACT) - no cast pass between dilations, and the blocks'
+    // streams start from `c` directly (no copies).  Otherwise: cast kernels + in-place reduce-add.
+    const bool fuse = sizeof(OT) == 2 && !sg.padded;
+    const bool up_act = fuse && (sg.s * sg.c) % 64 == 0;
     {   // ConvTranspose1d as one GEMM over rows q-1, q, q+1; the output [T][s C] is [s T][C]
       GemmParams gp = base();
       set_A<OT>(gp, 0, ua, cin_p, (int)t, t, cin_p, B);
       add_seg(gp, 0, 0, -1, cin_p / BK);
       add_seg(gp, 0, 0, 0, cin_p / BK);
       add_seg(gp, 0, 0, 1, cin_p / BK);
-      voc_gemm(gp, sg.w_up, sg.s * sg.c, 3 * cin_p, sg.b_up, (int)t, B, VOC_F32, c, t * sg.s * sg.c, sg.s * sg.c, 1.0f, st);
+      if (up_act)      // c and xa = LeakyReLU(c), the operand of every block's first conv, from one epilogue
+        voc_gemm(gp, sg.w_up, sg.s * sg.c, 3 * cin_p, sg.b_up, (int)t, B, VOC_RESID_ACT, c, t * sg.s * sg.c, sg.s * sg.c, 0.1f,
+                 st, nullptr, xa);
+      else
+        voc_gemm(gp, sg.w_up, sg.s * sg.c, 3 * cin_p, sg.b_up, (int)t, B, VOC_F32, c, t * sg.s * sg.c, sg.s * sg.c, 1.0f, st);
     }
     float* x[4] = {nullptr, nullptr, nullptr, nullptr};
     for (int j = 0; j < v.n_blk; ++j) x[j] = vb_x_[j].template as<float>();
     // operand tensors of this stage: [T][cw] with cw = C (grouped rows, no padding) or C padded to a K block
     const int cw = sg.padded ? sg.cp : sg.c;
-    // 2-byte operands, unpadded rows: every second conv adds its residual from a TMA-loaded box, stores the f32
-    // stream AND its LeakyReLU'd operand copy (EPI_RESID_ACT) - no cast pass between dilations, and the blocks'
-    // streams start from `c` directly (no copies).  Otherwise: cast kernels + in-place reduce-add.
-    const bool fuse = sizeof(OT) == 2 && !sg.padded;
     // operand of every block's first conv [+ the blocks' own copies of the residual stream]
-    launch_k(voc_lrelu_cast<OT>, blocks_for(rows * (cw / 8)), dim3(256), st, (const float*)c, rows, sg.c, cw, 0.1f, xa,
-             fuse ? (float*)nullptr : x[0], !fuse && v.n_blk > 1 ? x[1] : (float*)nullptr,
-             !fuse && v.n_blk > 2 ? x[2] : (float*)nullptr);
-    ++launches;
+    if (!up_act) {
+      launch_k(voc_lrelu_cast<OT>, blocks_for(rows * (cw / 8)), dim3(256), st, (const float*)c, rows, sg.c, cw, 0.1f, xa,
+               fuse ? (float*)nullptr : x[0], !fuse && v.n_blk > 1 ? x[1] : (float*)nullptr,
+               !fuse && v.n_blk > 2 ? x[2] : (float*)nullptr);
+      ++launches;
+    }
     if (!fuse && v.n_blk > 3)
       SRN_CUDA(cudaMemcpyAsync(x[3], c, (size_t)rows * sg.c * sizeof(float), cudaMemcpyDeviceToDevice, st));
     for (int j = 0; j < v.n_blk; ++j) {

@@ -247,9 +247,10 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           for (int i = 0; i < 8; ++i) r4[i] = rs[i];
         }
       }
+      const bool has_res = !kAct || p.resid != nullptr;      // EPI_RESID_ACT without a residual: store + activated copy
       if constexpr (kResidTma) {
         __syncwarp();      // the previous tile's reads of the residual box are done
-        if (lane == 0 && nvalid > 0) {
+        if (lane == 0 && nvalid > 0 && has_res) {
           if constexpr (kAct) tma_store_wait_read<0>();      // ... and so is the store of its last chunk
           mbar_expect_tx(&resid_bar[warp - 2], 4096);
           tma_load_3d(reinterpret_cast<void*>(smem + CFG::kStgOff + (warp - 2) * 8192 + 4096), &p.mapR, &resid_bar[warp - 2],
@@ -295,16 +296,21 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           if (lane == 0) mbar_arrive_cluster(tepi_addr + as * 8);
         }
         if constexpr (kResidTma) {
-          mbar_wait(&resid_bar[warp - 2], rphase);
-          rphase ^= 1;
           const uint32_t rbox = st.base + 4096 + lane * 128;
+          if (has_res) {
+            mbar_wait(&resid_bar[warp - 2], rphase);
+            rphase ^= 1;
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            float4 rv;
-            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
-                         : "=f"(rv.x), "=f"(rv.y), "=f"(rv.z), "=f"(rv.w)
-                         : "r"(rbox + ((i ^ (lane & 7)) << 4)));
-            v[4 * i + 0] += rv.x; v[4 * i + 1] += rv.y; v[4 * i + 2] += rv.z; v[4 * i + 3] += rv.w;
+            for (int i = 0; i < 8; ++i) {
+              float4 rv;
+              asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                           : "=f"(rv.x), "=f"(rv.y), "=f"(rv.z), "=f"(rv.w)
+                           : "r"(rbox + ((i ^ (lane & 7)) << 4)));
+              v[4 * i + 0] += rv.x; v[4 * i + 1] += rv.y; v[4 * i + 2] += rv.z; v[4 * i + 3] += rv.w;
+            }
+          } else {
+            if (lane == 0) tma_store_wait_read<0>();      // the box's previous store has been read
+            __syncwarp();
           }
           if constexpr (kAct) {
 #pragma unroll
@@ -354,7 +360,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         }
         epilogue_chunk<OT, EPI>(p, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss, racc, rowc, kbits, gn_ok);
         if constexpr (kAct) {
-          if (lane == 0 && cc + 1 < nvalid) {      // the box's store has been read: fetch the next residual chunk
+          if (lane == 0 && cc + 1 < nvalid && has_res) {      // the box's store has been read: fetch the next residual chunk
             tma_store_wait_read<0>();
             mbar_expect_tx(&resid_bar[warp - 2], 4096);
             tma_load_3d(reinterpret_cast<void*>(smem + CFG::kStgOff + (warp - 2) * 8192 + 4096), &p.mapR,
