@@ -55,6 +55,22 @@ int srn_finalize_weights(SrnHandle* h);
 int srn_estimator_forward(SrnHandle* h, const float* x, const float* mu, const uint8_t* mask, const float* spk,
                           float t, int32_t B, int32_t T, float* v_out, void* stream);
 
+/* The same with one time per clip, t_host[B] (HOST): Decoder.forward accepts a vector t (decoder.py:401-402), which is
+ * how CFM.compute_loss calls it (flow_matching.py:115,123). */
+int srn_estimator_forward_t(SrnHandle* h, const float* x, const float* mu, const uint8_t* mask, const float* spk,
+                            const float* t_host, int32_t B, int32_t T, float* v_out, void* stream);
+
+/* CFM.compute_loss, FORWARD VALUE ONLY (flow_matching.py:95-133; what trainers/ssc.py evaluates on the dev set under
+ * no_grad): given the target x1, the noise z and the times t_host[B] the reference would draw,
+ *   y = (1 - (1 - sigma_min) t) z + t x1,  u = x1 - (1 - sigma_min) z,
+ *   loss = sum(((estimator(y, mask, mu, t, spk) - u) * mask_l)^2) / (sum(mask_l) * n_feats); without mask_l the sum runs
+ *   over every frame (padded ones too, as the reference's does) and the divisor is sum(mask) * n_feats.
+ * x1, z, y_out (B, n_feats, T) f32 DEVICE; mask, mask_l (B, T) u8 DEVICE (mask_l nullable); loss_out one f32 on the
+ * DEVICE.  There is no backward pass in this library. */
+int srn_cfm_loss(SrnHandle* h, const float* x1, const float* z, const float* t_host, const float* mu, const uint8_t* mask,
+                 const float* spk, const uint8_t* mask_l, int32_t B, int32_t T, float sigma_min, float* y_out,
+                 float* loss_out, void* stream);
+
 /* x <- solve_euler(x, t_span, mu, mask, spk) in place on DEVICE memory.  t_span is a HOST array of
  * n_steps + 1 f32 values.  blend_mask / blend_src (DEVICE, nullable): optional infill blend, after
  * every step x[b,:,t] = blend_src[b,:,t] where blend_mask[b,t] != 0.  The reference has no blend

@@ -184,6 +184,23 @@ def cfm_inference(sd, mu, mask, n_timesteps=10, temperature=0.667, spks=None, ou
         return solve_euler(sd, z, t_span, mu, mask, spks)
 
 
+def compute_loss(sd, x1, mask, mu, spks, z, t, mask_l=None, sigma_min: float = 1e-4, heads: int = 4):
+    """flow_matching.py:95-133 with the random draws made explicit: `t` (B,) is what `torch.rand([b, 1, 1])` gave and
+    `z` what `torch.randn_like(x1)` gave.  Returns (loss, y) like the reference."""
+    t = t.reshape(-1, 1, 1).to(torch.float32)
+    y = (1 - (1 - sigma_min) * t) * z + t * x1
+    u = x1 - (1 - sigma_min) * z
+    denoised = estimator_forward(sd, y, mask, mu, t.squeeze(), spks, heads)
+    if mask_l is not None:
+        denoised = denoised * mask_l
+        u = u * mask_l
+        den = torch.sum(mask_l) * u.shape[1]
+    else:
+        den = torch.sum(mask) * u.shape[1]
+    loss = F.mse_loss(denoised, u, reduction="sum") / den
+    return loss, y
+
+
 def time_grid(t_span: torch.Tensor):
     """The (t_k, dt_k) sequence solve_euler visits, with the reference's fp32 running-sum wobble."""
     t, dt = t_span[0].clone(), t_span[1] - t_span[0]

@@ -209,17 +209,25 @@ class Decoder(nn.Module):
         spk = speaker_features.detach().to(device=dev, dtype=torch.float32).contiguous()
         m8 = _as_mask_u8(mask, B, T, dev)
         out = torch.empty_like(xf)
-        tval = float(t.reshape(-1)[0]) if torch.is_tensor(t) else float(t)
+        tv = t.detach().reshape(-1).to("cpu", torch.float32) if torch.is_tensor(t) else torch.tensor([float(t)])
+        if tv.numel() not in (1, B):
+            raise ValueError(f"t must be a scalar or hold one time per clip ({B}), got {tv.numel()} values")
         with torch.cuda.device(dev):
             st = torch.cuda.current_stream(dev).cuda_stream
-            _lib.check(eng.lib.srn_estimator_forward(eng.h, xf.data_ptr(), muf.data_ptr(), m8.data_ptr(),
-                                                     spk.data_ptr(), C.c_float(tval), B, T, out.data_ptr(),
-                                                     C.c_void_p(st)), "srn_estimator_forward")
+            if tv.numel() == 1:
+                _lib.check(eng.lib.srn_estimator_forward(eng.h, xf.data_ptr(), muf.data_ptr(), m8.data_ptr(),
+                                                         spk.data_ptr(), C.c_float(float(tv[0])), B, T, out.data_ptr(),
+                                                         C.c_void_p(st)), "srn_estimator_forward")
+            else:       # one time per clip (decoder.py:401-402), as CFM.compute_loss calls it
+                tarr = (C.c_float * B)(*tv.tolist())
+                _lib.check(eng.lib.srn_estimator_forward_t(eng.h, xf.data_ptr(), muf.data_ptr(), m8.data_ptr(),
+                                                           spk.data_ptr(), tarr, B, T, out.data_ptr(), C.c_void_p(st)),
+                           "srn_estimator_forward_t")
         return out
 
 
 class CFM(nn.Module):
-    """Reference flow_matching.py:9-93 (inference side).  `compute_loss` (training) is out of scope."""
+    """Reference flow_matching.py:9-133: inference, and the forward value of `compute_loss` (no backward pass)."""
 
     def __init__(self, in_channels=80, out_channels=80, solver="euler", sigma_min=1e-4, spk_embed_dim=256,
                  decoder_channels=(512, 512), decoder_attention_head_dim=256, precision="bf16", gn_stats="padded"):
@@ -237,9 +245,39 @@ class CFM(nn.Module):
     def forward(self, x1, mask, mu, spks, mask_l=None):
         return self.compute_loss(x1, mask, mu, spks, mask_l)
 
-    def compute_loss(self, *a, **k):
-        raise NotImplementedError("training (CFM.compute_loss) is outside the B200 decode path; "
-                                  "train with the reference and load the checkpoint here")
+    @torch.inference_mode()
+    def compute_loss(self, x1, mask, mu, spks, mask_l=None, *, z=None, t=None):
+        """Reference flow_matching.py:95-133, FORWARD VALUE ONLY -> (loss, y): the number `trainers/ssc.py` logs on the
+        dev set.  The returned tensors carry no graph (this library has no backward pass; train with the reference).
+        `t` (B,) and `z` like x1 are drawn as the reference draws them (device generator, t first) unless given."""
+        B, _, T = mu.shape
+        dev = mu.device
+        if t is None:
+            t = torch.rand([B, 1, 1], device=dev, dtype=torch.float32)
+        if z is None:
+            z = torch.randn_like(x1, dtype=torch.float32)
+        est = self.estimator
+        est._check_inputs(x1, mask, mu, spks)
+        eng = est.engine(dev)
+        x1f = x1.detach().to(device=dev, dtype=torch.float32).contiguous()
+        zf = z.detach().to(device=dev, dtype=torch.float32).contiguous()
+        muf = mu.detach().to(torch.float32).contiguous()
+        spk = spks.detach().to(device=dev, dtype=torch.float32).contiguous()
+        m8 = _as_mask_u8(mask, B, T, dev)
+        l8 = _as_mask_u8(mask_l, B, T, dev) if mask_l is not None else None
+        tv = t.detach().reshape(-1).to("cpu", torch.float32)
+        if tv.numel() != B:
+            raise ValueError(f"t must hold one time per clip ({B})")
+        tarr = (C.c_float * B)(*tv.tolist())
+        y = torch.empty_like(x1f)
+        loss = torch.empty((), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            st = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(eng.lib.srn_cfm_loss(eng.h, x1f.data_ptr(), zf.data_ptr(), tarr, muf.data_ptr(), m8.data_ptr(),
+                                            spk.data_ptr(), l8.data_ptr() if l8 is not None else None, B, T,
+                                            C.c_float(self.sigma_min), y.data_ptr(), loss.data_ptr(), C.c_void_p(st)),
+                       "srn_cfm_loss")
+        return loss, y
 
     @torch.inference_mode()
     def inference(self, mu, mask, n_timesteps=10, temperature=0.667, spks=None):

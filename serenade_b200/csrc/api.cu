@@ -122,6 +122,27 @@ SRN_EXPORT int srn_estimator_forward(SrnHandle* h, const float* x, const float* 
   SRN_API_END
 }
 
+SRN_EXPORT int srn_estimator_forward_t(SrnHandle* h, const float* x, const float* mu, const uint8_t* mask, const float* spk,
+                                       const float* t_host, int32_t B, int32_t T, float* v_out, void* stream) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (!x || !mu || !mask || !spk || !t_host || !v_out) srn::fail("srn_estimator_forward_t: null argument");
+  if (B < 1 || T < 2) srn::fail("srn_estimator_forward_t: need B >= 1 and T >= 2 (got B=%d T=%d)", B, T);
+  h->eng->estimator_forward_t(x, mu, mask, spk, t_host, B, T, v_out, static_cast<cudaStream_t>(stream));
+  SRN_API_END
+}
+
+SRN_EXPORT int srn_cfm_loss(SrnHandle* h, const float* x1, const float* z, const float* t_host, const float* mu,
+                            const uint8_t* mask, const float* spk, const uint8_t* mask_l, int32_t B, int32_t T,
+                            float sigma_min, float* y_out, float* loss_out, void* stream) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (!x1 || !z || !t_host || !mu || !mask || !spk || !y_out || !loss_out) srn::fail("srn_cfm_loss: null argument");
+  if (B < 1 || T < 2) srn::fail("srn_cfm_loss: need B >= 1 and T >= 2 (got B=%d T=%d)", B, T);
+  h->eng->cfm_loss(x1, z, t_host, mu, mask, spk, mask_l, B, T, sigma_min, y_out, loss_out, static_cast<cudaStream_t>(stream));
+  SRN_API_END
+}
+
 SRN_EXPORT int srn_solve_euler(SrnHandle* h, float* x_inout, const float* mu, const uint8_t* mask, const float* spk,
                     const float* t_span_host, int32_t n_steps, int32_t B, int32_t T, const uint8_t* blend_mask,
                     const float* blend_src, void* stream) {

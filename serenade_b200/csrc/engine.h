@@ -26,6 +26,13 @@ class EngineBase {
   virtual void finalize_weights() = 0;
   virtual void estimator_forward(const float* x, const float* mu, const uint8_t* mask, const float* spk, float t,
                                  int B, int T, float* v_out, cudaStream_t st) = 0;
+  // per-clip times t[B] (host): what Decoder.forward does when t is a vector (decoder.py:401-402)
+  virtual void estimator_forward_t(const float* x, const float* mu, const uint8_t* mask, const float* spk,
+                                   const float* t_host, int B, int T, float* v_out, cudaStream_t st) = 0;
+  // CFM.compute_loss forward value (flow_matching.py:95-133) for given noise z and times t; no gradients
+  virtual void cfm_loss(const float* x1, const float* z, const float* t_host, const float* mu, const uint8_t* mask,
+                        const float* spk, const uint8_t* mask_l, int B, int T, float sigma_min, float* y_out,
+                        float* loss_out, cudaStream_t st) = 0;
   virtual void solve_euler(float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
                            int n_steps, int B, int T, const uint8_t* blend_mask, const float* blend_src,
                            cudaStream_t st) = 0;

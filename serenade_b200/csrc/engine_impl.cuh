@@ -119,6 +119,11 @@ class Engine : public EngineBase {
   void finalize_weights() override;
   void estimator_forward(const float* x, const float* mu, const uint8_t* mask, const float* spk, float t, int B,
                          int T, float* v_out, cudaStream_t st) override;
+  void estimator_forward_t(const float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_host,
+                           int B, int T, float* v_out, cudaStream_t st) override;
+  void cfm_loss(const float* x1, const float* z, const float* t_host, const float* mu, const uint8_t* mask,
+                const float* spk, const uint8_t* mask_l, int B, int T, float sigma_min, float* y_out, float* loss_out,
+                cudaStream_t st) override;
   void solve_euler(float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
                    int n_steps, int B, int T, const uint8_t* blend_mask, const float* blend_src,
                    cudaStream_t st) override;
@@ -211,6 +216,8 @@ class Engine : public EngineBase {
                   void* out, long long out_bstride, int ldo, float slope, cudaStream_t st);
   std::list<Plan<OT>> plans_;
   bool blend_active_ = false;
+  int tb_bstride_ = 0;          // 512 while an estimator call with per-clip times runs (estimator_forward_t)
+  DevBuf loss_v_, loss_part_, loss_lmask_;
   cudaStream_t capture_stream_ = nullptr;
 
   // weights

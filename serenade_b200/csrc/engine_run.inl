@@ -175,7 +175,7 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
                                      : nullptr;
       dim3 grid(cdiv(L.T, rpb), B);
       launch_k(gn_apply_kernel<OT>, grid, dim3(256), st, op.y, op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma,
-               op.beta, tb, mask, pl.Tp, L.mask_step, static_cast<OT*>(op.out), rpb, nvalid);
+               op.beta, tb, mask, pl.Tp, L.mask_step, static_cast<OT*>(op.out), rpb, nvalid, tb_bstride_);
       ++launches;
     } break;
     case OP_GN_RES_SPK_LN: {
@@ -309,6 +309,60 @@ void Engine<OT>::estimator_forward(const float* x, const float* mu, const uint8_
   blend_active_ = false;
   prepass(pl, std::vector<float>{t}, std::vector<float>{0.f}, st);
   run_forward(pl, 0, v_out, false, st);
+}
+
+// Decoder.forward with one time per clip (decoder.py:401-402: `t` may be a vector; CFM.compute_loss draws one per
+// sample).  The time path is the only place where t enters: the prepass computes B time biases per resnet instead of
+// one per Euler step, and gn_apply picks its clip's.
+template <typename OT>
+void Engine<OT>::estimator_forward_t(const float* x, const float* mu, const uint8_t* mask, const float* spk,
+                                     const float* t_host, int B, int T, float* v_out, cudaStream_t st) {
+  Plan<OT>& pl = get_plan(B, T);
+  ensure_step_buffers(pl, B, cfg_.in_channels, (int)resnets_.size());
+  stage_inputs(pl, x, mu, mask, spk, cudaMemcpyDeviceToDevice, st);
+  const std::vector<float> ts(t_host, t_host + B), zeros(B, 0.f);
+  SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, ts.data(), (size_t)B * 4, cudaMemcpyHostToDevice, st));
+  SRN_CUDA(cudaMemcpyAsync(pl.dts.p, zeros.data(), (size_t)B * 4, cudaMemcpyHostToDevice, st));
+  SRN_CUDA(cudaStreamSynchronize(st));   // ts / zeros are host temporaries
+  blend_active_ = false;
+  prepass(pl, ts, zeros, st);
+  tb_bstride_ = 512;
+  try {
+    run_forward(pl, 0, v_out, false, st);
+  } catch (...) {
+    tb_bstride_ = 0;
+    throw;
+  }
+  tb_bstride_ = 0;
+}
+
+// CFM.compute_loss, forward value only (flow_matching.py:95-133; the validation loss of trainers/ssc.py).  The caller
+// supplies the noise z and the times t the reference would draw; y (the conditional flow) is returned like the
+// reference does.  No gradients: the backward pass is not built.
+template <typename OT>
+void Engine<OT>::cfm_loss(const float* x1, const float* z, const float* t_host, const float* mu, const uint8_t* mask,
+                          const float* spk, const uint8_t* mask_l, int B, int T, float sigma_min, float* y_out,
+                          float* loss_out, cudaStream_t st) {
+  Plan<OT>& pl = get_plan(B, T);
+  const int C = cfg_.out_channels;
+  const long long n = (long long)B * C * T;
+  const float oms = (float)(1.0 - (double)sigma_min);
+  ensure_step_buffers(pl, B, cfg_.in_channels, (int)resnets_.size());
+  const int nblk = 1024;
+  if (loss_v_.bytes < (size_t)n * 4) loss_v_.alloc((size_t)n * 4);
+  if (loss_part_.bytes < (size_t)nblk * 16) loss_part_.alloc((size_t)nblk * 16);
+  // t on the device first: the mix kernel reads it (estimator_forward_t stages the same values again)
+  SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, t_host, (size_t)B * 4, cudaMemcpyHostToDevice, st));
+  SRN_CUDA(cudaStreamSynchronize(st));
+  launch_k(cfm_mix_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), st, x1, z, (const float*)pl.tsteps.template as<float>(),
+           (long long)C * T, n, oms, y_out);
+  ++launches;
+  estimator_forward_t(y_out, mu, mask, spk, t_host, B, T, loss_v_.template as<float>(), st);
+  launch_k(cfm_loss_partial_kernel, dim3(nblk), dim3(256), st, (const float*)loss_v_.template as<float>(), x1, z, mask_l,
+           mask_l != nullptr ? mask_l : mask, T, C, T, n, oms, loss_part_.template as<double>());
+  launch_k(cfm_loss_final_kernel, dim3(1), dim3(32), st, (const double*)loss_part_.template as<double>(), nblk, C, loss_out);
+  launches += 2;
+  SRN_CUDA(cudaGetLastError());
 }
 
 template <typename OT>

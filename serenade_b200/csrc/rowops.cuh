@@ -199,7 +199,8 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                                        const float* __restrict__ tbias, const uint8_t* __restrict__ mask,
                                                        int mask_bstride, int mask_step, OT* __restrict__ out,
-                                                       int rows_per_block, const int* __restrict__ nvalid) {
+                                                       int rows_per_block, const int* __restrict__ nvalid,
+                                                       int tbias_bstride) {
   __shared__ float stats[16];
   __shared__ double red[256];
   pdl_launch_dependents();
@@ -215,7 +216,7 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__
   float ga[8], be[8], tb[8];
   load8(gamma + c, ga);
   load8(beta + c, be);
-  if (tbias != nullptr) load8(tbias + c, tb);
+  if (tbias != nullptr) load8(tbias + (long long)b * tbias_bstride + c, tb);      // (stride 0: one t for the batch)
   else {
 #pragma unroll
     for (int i = 0; i < 8; ++i) tb[i] = 0.f;
@@ -506,6 +507,69 @@ __global__ void sinusoid_kernel(const float* __restrict__ ts, int dim, float e /
     emb[(long long)s * dim + j] = sinf(a);
     emb[(long long)s * dim + half + j] = cosf(a);
   }
+}
+
+// ------------------------------------------------------------------------------------------------
+// CFM.compute_loss, forward value (flow_matching.py:112-133), channels-first f32 [B][C][T].
+// y = (1 - (1 - sigma) t_b) z + t_b x1 with torch's eager rounding (separate multiplies and adds, no FMA).
+__global__ void __launch_bounds__(256) cfm_mix_kernel(const float* __restrict__ x1, const float* __restrict__ z,
+                                                      const float* __restrict__ t, long long per_clip, long long n,
+                                                      float one_minus_sigma, float* __restrict__ y) {
+  pdl_wait();
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  const float tb = t[i / per_clip];
+  const float a = __fsub_rn(1.0f, __fmul_rn(one_minus_sigma, tb));
+  y[i] = __fadd_rn(__fmul_rn(a, z[i]), __fmul_rn(tb, x1[i]));
+}
+
+// partial[2 * block] = sum over the block's elements of ((v - u) * m)^2 with u = x1 - (1 - sigma) z and m = sel (null:
+// every frame - without mask_l the reference sums over the padded frames too, where v = 0 but u is not);
+// partial[2 * block + 1] = number of frames with cnt != 0 it saw in channel 0 (the divisor).  Doubles, fixed order.
+__global__ void __launch_bounds__(256) cfm_loss_partial_kernel(const float* __restrict__ v, const float* __restrict__ x1,
+                                                               const float* __restrict__ z,
+                                                               const uint8_t* __restrict__ sel,
+                                                               const uint8_t* __restrict__ cntm, int lmask_bstride, int C,
+                                                               int T, long long n, float one_minus_sigma,
+                                                               double* __restrict__ partial) {
+  __shared__ double red[2][256];
+  pdl_wait();      // v comes from the estimator's last GEMM, which releases its dependents early
+  double acc = 0.0, cnt = 0.0;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+    const int tt = (int)(i % T);
+    const long long bc = i / T;
+    const int c = (int)(bc % C), b = (int)(bc / C);
+    const long long mi = (long long)b * lmask_bstride + tt;
+    if (sel == nullptr || sel[mi] != 0) {
+      const float u = __fsub_rn(x1[i], __fmul_rn(one_minus_sigma, z[i]));
+      const double d = (double)v[i] - (double)u;
+      acc += d * d;
+    }
+    if (c == 0 && cntm[mi] != 0) cnt += 1.0;
+  }
+  red[0][threadIdx.x] = acc;
+  red[1][threadIdx.x] = cnt;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) {
+      red[0][threadIdx.x] += red[0][threadIdx.x + s];
+      red[1][threadIdx.x] += red[1][threadIdx.x + s];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    partial[2 * blockIdx.x] = red[0][0];
+    partial[2 * blockIdx.x + 1] = red[1][0];
+  }
+}
+
+// loss = sum / (frames * C)   (flow_matching.py:128-132)
+__global__ void cfm_loss_final_kernel(const double* __restrict__ partial, int nblocks, int C, float* __restrict__ loss) {
+  pdl_wait();
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  double s = 0.0, c = 0.0;
+  for (int i = 0; i < nblocks; ++i) { s += partial[2 * i]; c += partial[2 * i + 1]; }
+  *loss = (float)(s / (c * (double)C));
 }
 
 }  // namespace srn
