@@ -41,6 +41,8 @@ enum EpiMode : int {
   EPI_RESID_ACT = 10,  // 2-byte OT only: x f32 (mapD) = resid (mapR) + acc + bias; second output (mapD2) OT = leaky_relu(x, act_slope)
 };
 
+constexpr int kWinRows = 192;      // rows of an A window (window mode): 128 + the largest shift span
+
 struct KSeg {
   int src;    // 0 / 1: which A tensor map
   int col0;   // first column (elements) inside that tensor
@@ -105,6 +107,12 @@ struct GemmParams {
   int d_hcol;       // output column offset per h (elements), e.g. 512 for the per-head attention output
   int d_zbatch;     // output batch coordinate: 1 -> z, 0 -> b
   unsigned long long* trace;   // -DSRN_TRACE=1 builds: per-CTA clock64 stamps of the kernel's phases (srn_profile_ops)
+  // Window mode (convolutions: all K segments read the same source columns at different row shifts).  Instead of one
+  // 128-row A box per (segment, K block), each CTA loads ONE kWinRows-row window per K block - rows
+  // m0 + win_min .. - and the segments' MMAs address shifted 128-row views of it through the smem descriptor.
+  // Cuts the L2 -> SM operand traffic of a k-tap conv by up to k.  mapA[0] must have kWinRows-row boxes.
+  int win;          // 0 = off; 1 = on; 3 = on, descriptors carry the matrix base offset ((addr >> 7) & 7)
+  int win_min;      // smallest row shift of the segments (max - min <= kWinRows - 128)
   int dbg_mode;     // profiling experiments only (SRN_DBG_MODE, srn_profile_ops): bit 0 = no TMA loads, bit 1 = no MMAs,
                     // bit 2 = no epilogue (results are garbage)
   // EPI_ROWMAX / EPI_EXP / EPI_PV: per-row softmax statistics, one entry per 64-key slice:

@@ -26,7 +26,12 @@ struct GemmCfg {
   static constexpr int kBarOff = kStgOff + 8 * 8192;          // barriers + tmem slot (256 B)
   static constexpr int kRedOff = kBarOff + 256;               // GroupNorm partial reduction scratch (256 B)
   static constexpr int kBiasOff = kRedOff + 256;              // per epilogue warp: its bias slice (8 x 512 B)
-  static constexpr int kSmemBytes = kBiasOff + 8 * 512 + 1024;     // + alignment slack
+  static constexpr int kWinBarOff = kBiasOff + 8 * 512;       // window mode: its own barriers (256 B)
+  static constexpr int kSmemBytes = kWinBarOff + 256 + 1024;  // + alignment slack
+  // window mode re-partitions the operand stages: two A windows, the rest is a ring of B stages
+  static constexpr int kWinABytes = kWinRows * 128;
+  static constexpr int kWinBStages = (kStages * kStageBytes - 2 * kWinABytes) / kBBytes;
+  static_assert(kWinBStages >= 3 && 4 + 2 * kWinBStages <= 32, "window-mode barriers fit their 256 bytes");
   static constexpr int kThreads = 320;
   static constexpr int kTmemCols = 2 * BN;
   static_assert(kStgOff % 1024 == 0, "staging boxes must be 1024-byte aligned for SWIZZLE_128B");

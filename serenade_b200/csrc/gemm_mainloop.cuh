@@ -32,6 +32,10 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   uint64_t* tempty_bar = tfull_bar + 2;         // [2] accumulator stage drained by the epilogue
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
   uint64_t* resid_bar = reinterpret_cast<uint64_t*>(smem + CFG::kBarOff + 128);   // [8] one per epilogue warp (kResidTma)
+  uint64_t* wa_full = reinterpret_cast<uint64_t*>(smem + CFG::kWinBarOff);      // window mode: [2] A windows
+  uint64_t* wa_empty = wa_full + 2;
+  uint64_t* wb_full = wa_empty + 2;                                             // [kWinBStages] B ring
+  uint64_t* wb_empty = wb_full + CFG::kWinBStages;
   float* gn_red = reinterpret_cast<float*>(smem + CFG::kRedOff);   // [2 buffers][4 quarters][NG][2]
 
   const int warp = threadIdx.x >> 5;
@@ -66,6 +70,10 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       mbar_init(&tempty_bar[s], 16);    // one arrival per epilogue warp of both CTAs (leader's copy is used)
     }
     for (int s = 0; s < 8; ++s) mbar_init(&resid_bar[s], 1);
+    if (p.win) {
+      for (int s = 0; s < 2; ++s) { mbar_init(&wa_full[s], 1); mbar_init(&wa_empty[s], 1); }
+      for (int s = 0; s < CFG::kWinBStages; ++s) { mbar_init(&wb_full[s], 1); mbar_init(&wb_empty[s], 1); }
+    }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc_2sm<CFG::kTmemCols>(tmem_slot);
@@ -80,6 +88,36 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     if (elect_one()) {
       // ------------------------------------------------------------ TMA producer
       uint32_t stage = 0, phase = 0;
+      if (!MC && p.win) {
+        // window mode: per K block one A window (all the segments' rows) + one B box per segment
+        uint32_t wa = 0, wap = 0, wb = 0, wbp = 0;
+        const int kcb = p.seg[0].nblk;
+        for (int tile = pair0; tile < total_tiles; tile += npairs) {
+          const int z = tile / tiles_mn;
+          const int rem = tile - z * tiles_mn;
+          const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
+          const int n0 = (rem % ntn_u) * BN;
+          const int b = z / p.HB;
+          const int h = z - b * p.HB;
+          const int a_batch = p.a_zbatch ? z : b;
+          const int b_batch = p.b_batch_mode == 0 ? 0 : (p.b_batch_mode == 1 ? b : z);
+          const int b_row = n0 + (int)rank * (BN / 2) + h * p.b_hrow;
+          for (int cb = 0; cb < kcb; ++cb) {
+            mbar_wait(&wa_empty[wa], wap ^ 1);
+            if (rank == 0) mbar_expect_tx(&wa_full[wa], 2 * CFG::kWinABytes);
+            tma_load_3d_2sm(smem + wa * CFG::kWinABytes, &p.mapA[0], map_to_cta(&wa_full[wa], leader),
+                            p.seg[0].col0 + cb * BK + h * p.a_hcol, m0 + p.win_min, a_batch);
+            if (++wa == 2) { wa = 0; wap ^= 1; }
+            for (int s = 0; s < p.nseg; ++s) {
+              mbar_wait(&wb_empty[wb], wbp ^ 1);
+              if (rank == 0) mbar_expect_tx(&wb_full[wb], 2 * CFG::kBBytes);
+              tma_load_3d_2sm(smem + 2 * CFG::kWinABytes + wb * CFG::kBBytes, &p.mapB, map_to_cta(&wb_full[wb], leader),
+                              p.b_col0 + (s * kcb + cb) * BK + h * p.b_hcol, b_row, b_batch);
+              if (++wb == (uint32_t)CFG::kWinBStages) { wb = 0; wbp ^= 1; }
+            }
+          }
+        }
+      } else
       for (int tile = pair0; tile < total_tiles; tile += npairs) {
         const int z = tile / tiles_mn;
         const int rem = tile - z * tiles_mn;
@@ -127,6 +165,36 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       constexpr uint32_t idesc = make_idesc(TR::kFmt, 256, BN);
       uint32_t stage = 0, phase = 0;
       uint32_t it = 0;
+      if (!MC && p.win) {
+        uint32_t wa = 0, wap = 0, wb = 0, wbp = 0;
+        const int kcb = p.seg[0].nblk;
+        const bool boff = (p.win & 2) != 0;
+        for (int tile = pair0; tile < total_tiles; tile += npairs, ++it) {
+          const uint32_t as = it & 1;
+          mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t tacc = tmem_base + as * BN;
+          for (int cb = 0; cb < kcb; ++cb) {
+            mbar_wait(&wa_full[wa], wap);
+            tc_fence_after();
+            const uint32_t wbase = smem_u32(smem + wa * CFG::kWinABytes);
+            for (int s = 0; s < p.nseg; ++s) {
+              mbar_wait(&wb_full[wb], wbp);
+              tc_fence_after();
+              // the segment's 128 rows start (shift - win_min) rows into the window
+              const uint64_t da = make_kmajor_sw128_desc_rows(wbase + (uint32_t)(p.seg[s].shift - p.win_min) * 128u, boff);
+              const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem + 2 * CFG::kWinABytes + wb * CFG::kBBytes));
+#pragma unroll
+              for (int k = 0; k < 4; ++k) umma_pair<TR::kKind>(tacc, da + 2 * k, db + 2 * k, idesc, (cb | s | k) != 0);
+              tc_commit_mask(&wb_empty[wb], 0x3);
+              if (++wb == (uint32_t)CFG::kWinBStages) { wb = 0; wbp ^= 1; }
+            }
+            tc_commit_mask(&wa_empty[wa], 0x3);
+            if (++wa == 2) { wa = 0; wap ^= 1; }
+          }
+          tc_commit_mask(&tfull_bar[as], (uint16_t)(0x3u << leader));
+        }
+      } else
       for (int tile = pair0; tile < total_tiles; tile += npairs, ++it) {
         const uint32_t as = it & 1;
         mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);

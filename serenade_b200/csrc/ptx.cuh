@@ -146,6 +146,14 @@ __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
   return d;
 }
 
+// The same for a start address that is a whole number of 128-byte rows, but not of 8-row swizzle atoms, into a tile
+// (window mode): the swizzle phase of the first row goes into the matrix-base-offset field, bits [49,52).
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc_rows(uint32_t smem_addr, bool with_base_offset) {
+  uint64_t d = make_kmajor_sw128_desc(smem_addr);
+  if (with_base_offset) d |= static_cast<uint64_t>((smem_addr >> 7) & 7) << 49;
+  return d;
+}
+
 // Instruction descriptor for kind::f16 / kind::tf32 with fp32 accumulation, both operands K-major.
 //   bits [4,6) D format (1 = f32)   bits [7,10) A format   bits [10,13) B format  (0 f16, 1 bf16, 2 tf32)
 //   bit 15 / 16 A / B major (0 = K)  bits [17,23) N >> 3    bits [24,29) M >> 4
