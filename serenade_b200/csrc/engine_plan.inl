@@ -76,6 +76,36 @@ inline void add_seg(GemmParams& gp, int src, int col0, int shift, int nblk) {
   gp.seg[gp.nseg++] = KSeg{src, col0, shift, nblk};
   gp.nkb += nblk;
 }
+// Window mode (gemm.cuh: GemmParams::win) for a convolution whose K segments are row shifts of ONE operand with the
+// weights packed [tap][channel]: one kWinRows-row A window per K block then serves every tap.  Call after the
+// add_seg calls; (ptr, cols, rows, alloc_rows, ld, nbatch) as given to set_A.  2-byte operands only (the TF32-class
+// mode doubles the segments for its hi / lo weights).  SRN_WIN=0 switches it off for A/B runs.
+inline int win_mode() {
+  static const int m = [] {
+    const char* e = getenv("SRN_WIN");
+    return e != nullptr ? atoi(e) : 1;
+  }();
+  return m;
+}
+template <typename OT>
+void maybe_window(GemmParams& gp, const OT* ptr, int cols, int rows, long long alloc_rows, int ld, int nbatch) {
+  static const int min_seg = [] {
+    const char* e = getenv("SRN_WIN_MINSEG");
+    return e != nullptr ? atoi(e) : 4;
+  }();
+  if (win_mode() == 0 || sizeof(OT) != 2 || gp.nseg < min_seg) return;
+  int mn = gp.seg[0].shift, mx = mn;
+  for (int i = 0; i < gp.nseg; ++i) {
+    if (gp.seg[i].src != 0 || gp.seg[i].col0 != gp.seg[0].col0 || gp.seg[i].nblk != gp.seg[0].nblk) return;
+    mn = std::min(mn, gp.seg[i].shift);
+    mx = std::max(mx, gp.seg[i].shift);
+  }
+  if (mx - mn > kWinRows - 128) return;
+  gp.mapA[0] = make_tmap_3d(ptr, sizeof(OT), cols, rows, nbatch, ld, (uint64_t)alloc_rows * ld, OpTraits<OT>::kBK, kWinRows);
+  gp.mapA[1] = gp.mapA[0];
+  gp.win = win_mode();
+  gp.win_min = mn;
+}
 // row_tiles = number of 256-row pair tiles; one CTA pair per SM pair (74 on a B200)
 inline int pick_bn(int N, long long row_tiles) {
   const long long nt256 = (N + 255) / 256, nt128 = (N + 127) / 128;
@@ -110,6 +140,7 @@ void Engine<OT>::add_resnet(Plan<OT>& pl, int ridx, int level, const OT* src0, i
       add_seg(gp, 0, 0, shift, ac0 / BK);
       if (a1 != nullptr) add_seg(gp, 1, 0, shift, ac1 / BK);
     }
+    if (a1 == nullptr) maybe_window<OT>(gp, a0, ac0, L.T, L.R, ald0, B);
     op.bn = pick_bn(512, tiles);
     set_B_weight<OT>(gp, W, 512, taps * (ac0 + ac1), op.bn);
     gp.N = 512;
@@ -436,6 +467,7 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
     GemmParams& gp = op.gp;
     set_A<OT>(gp, 0, src, 512, L.T, L.R, 512, B);
     for (int k = 0; k < 3; ++k) add_seg(gp, 0, 0, k - 1, 512 / BK);
+    maybe_window<OT>(gp, src, 512, L.T, L.R, 512, B);
     op.bn = pick_bn(512, (long long)L.mtiles * B);
     set_B_weight<OT>(gp, w.w, 512, 1536, op.bn);
     gp.N = 512;
@@ -547,6 +579,7 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
     GemmParams& gp = op.gp;
     set_A<OT>(gp, 0, cv, 512, T, pl.Tp, 512, B);
     for (int k = 0; k < 3; ++k) add_seg(gp, 0, 0, k - 1, 512 / BK);
+    maybe_window<OT>(gp, cv, 512, T, pl.Tp, 512, B);
     op.bn = pick_bn(512, tiles0);
     set_B_weight<OT>(gp, final_conv_.w, 512, 1536, op.bn);
     gp.N = 512;

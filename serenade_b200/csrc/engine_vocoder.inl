@@ -354,31 +354,19 @@ void Engine<OT>::voc_body(const float* mel, const float* scale, const float* shi
     return gp;
   };
   auto blocks_for = [](long long n) { return dim3((unsigned)((n + 255) / 256)); };
-  // Window mode (gemm.cuh: GemmParams::win): the segments of a conv are row shifts of one operand, so one
-  // kWinRows-row A window per K block serves all of them.  SRN_WIN=0 switches it off (A/B runs).
-  static const int win_mode = [] {
-    const char* e = getenv("SRN_WIN");
-    return e != nullptr ? atoi(e) : 1;
-  }();
-  auto maybe_window = [&](GemmParams& gp, const OT* a, int cols, long long rows_per_clip) {
-    if (win_mode == 0 || sizeof(OT) != 2 || gp.nseg < 2) return;
-    int mn = gp.seg[0].shift, mx = mn;
-    for (int i = 1; i < gp.nseg; ++i) { mn = std::min(mn, gp.seg[i].shift); mx = std::max(mx, gp.seg[i].shift); }
-    if (mx - mn > kWinRows - 128) return;
-    gp.mapA[0] = make_tmap_3d(a, sizeof(OT), cols, rows_per_clip, B, cols, (uint64_t)rows_per_clip * cols, BK, kWinRows);
-    gp.mapA[1] = gp.mapA[0];
-    gp.win = win_mode;
-    gp.win_min = mn;
+  // Window mode (engine_plan.inl: maybe_window): the segments of a conv are row shifts of one operand
+  auto maybe_win = [&](GemmParams& gp, const OT* a, int cols, long long rows_per_clip) {
+    maybe_window<OT>(gp, a, cols, (int)rows_per_clip, rows_per_clip, cols, B);
   };
   auto conv_segs = [&](GemmParams& gp, const OT* a, int cp, int t, int k, int d) {
     set_A<OT>(gp, 0, a, cp, t, t, cp, B);
     for (int j = 0; j < k; ++j) add_seg(gp, 0, 0, (j - (k - 1) / 2) * d, cp / BK);
-    maybe_window(gp, a, cp, t);
+    maybe_win(gp, a, cp, t);
   };
   auto shift_segs = [&](GemmParams& gp, const OT* a, int kc, long long rows_per_clip, const std::vector<int>& shifts) {
     set_A<OT>(gp, 0, a, kc, (int)rows_per_clip, rows_per_clip, kc, B);
     for (int sh : shifts) add_seg(gp, 0, 0, sh, kc / BK);
-    maybe_window(gp, a, kc, rows_per_clip);
+    maybe_win(gp, a, kc, rows_per_clip);
   };
   OT* ua = vb_ua_[0].template as<OT>();
   OT* ub = vb_ua_[1].template as<OT>();
@@ -412,7 +400,7 @@ void Engine<OT>::voc_body(const float* mel, const float* scale, const float* shi
       add_seg(gp, 0, 0, -1, cin_p / BK);
       add_seg(gp, 0, 0, 0, cin_p / BK);
       add_seg(gp, 0, 0, 1, cin_p / BK);
-      maybe_window(gp, ua, cin_p, t);
+      maybe_win(gp, ua, cin_p, t);
       if (up_act)      // c and xa = LeakyReLU(c), the operand of every block's first conv, from one epilogue
         voc_gemm(gp, sg.w_up, sg.s * sg.c, 3 * cin_p, sg.b_up, (int)t, B, VOC_RESID_ACT, c, t * sg.s * sg.c, sg.s * sg.c, 0.1f,
                  st, nullptr, xa);
