@@ -99,7 +99,6 @@ template <typename OT>
 void Engine<OT>::launch_gemm(const GemmParams& gp, int bn, dim3 grid, cudaStream_t st) {
   if (gp.nkb < 1 || gp.nseg < 1) fail("gemm with empty K");
   if (gp.epi == EPI_RESID_F32 && gp.resid != gp.out) fail("EPI_RESID_F32 updates its residual in place (TMA reduce-add)");
-  if (gp.epi == EPI_RESID_ACT && sizeof(OT) != 2) fail("EPI_RESID_ACT needs 2-byte operands");
   if (gp.ab_fp8) {
     if (gp.epi != EPI_ROWMAX) fail("e4m3 operands are only used by the row-max pass");
     if (bn == 256) launch_gemm_impl<Fp8, 256, EPI_ROWMAX>(gp, grid, num_sms_, st);

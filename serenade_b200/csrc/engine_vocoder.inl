@@ -224,7 +224,7 @@ void Engine<OT>::voc_gemm(GemmParams& gp, const OT* W, int N, int K, const float
     set_D<OT>(gp, static_cast<OT*>(out), N, M, out_bstride, ldo, nbatch);
   } else if (mode == VOC_RESID_ACT) {
     // out f32 = resid + conv (resid may be `out` itself); act_out = LeakyReLU(out) as the next conv's operand
-    if (sizeof(OT) != 2 || N % 64 != 0) fail("vocoder: fused residual + activation needs 2-byte operands and N % 64 == 0");
+    if (N % (128 / (int)sizeof(OT)) != 0) fail("vocoder: fused residual + activation needs whole 128-byte operand rows");
     gp.epi = EPI_RESID_ACT;
     set_D<float>(gp, static_cast<float*>(out), N, M, out_bstride, ldo, nbatch);
     gp.resid = resid;      // null: no residual, only the two stores
@@ -389,11 +389,11 @@ void Engine<OT>::voc_body(const float* mel, const float* scale, const float* shi
     const VocStage& sg = v.stages[i];
     const long long tn = t * sg.s, rows = (long long)B * tn;
     if (tn > 0x7fffffffLL / 2) fail("vocoder: sequence too long");
-    // 2-byte operands, unpadded rows: every second conv adds its residual from a TMA-loaded box, stores the f32
+    // Unpadded rows: every second conv adds its residual from a TMA-loaded box, stores the f32
     // stream AND its LeakyReLU'd operand copy (EPI_RESID_ACT) - no cast pass between dilations, and the blocks'
     // streams start from `c` directly (no copies).  Otherwise: cast kernels + in-place reduce-add.
-    const bool fuse = sizeof(OT) == 2 && !sg.padded;
-    const bool up_act = fuse && (sg.s * sg.c) % 64 == 0;
+    const bool fuse = !sg.padded;
+    const bool up_act = fuse && (sg.s * sg.c) % (128 / (int)sizeof(OT)) == 0;
     {   // ConvTranspose1d as one GEMM over rows q-1, q, q+1; the output [T][s C] is [s T][C]
       GemmParams gp = base();
       set_A<OT>(gp, 0, ua, cin_p, (int)t, t, cin_p, B);

@@ -38,7 +38,7 @@ enum EpiMode : int {
   EPI_ROWMAX = 7,      // no tensor output: stat_max[z][key slice of 64][row] = max over the slice's valid keys of acc*alpha
   EPI_EXP = 8,         // out OT = exp(acc*alpha - rowmax) (0 at masked keys), stat_sum[...] = partial row sums (f32)
   EPI_PV = 9,          // out OT = acc / rowsum
-  EPI_RESID_ACT = 10,  // 2-byte OT only: x f32 (mapD) = resid (mapR) + acc + bias; second output (mapD2) OT = leaky_relu(x, act_slope)
+  EPI_RESID_ACT = 10,  // x f32 (mapD) = [resid (mapR) +] acc + bias; second output (mapD2) OT = leaky_relu(x, act_slope)
 };
 
 constexpr int kWinRows = 192;      // rows of an A window (window mode): 128 + the largest shift span

@@ -121,17 +121,16 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
   } else if constexpr (EPI == EPI_RESID_ACT) {
     // v is the updated f32 stream (the caller added the residual and stored it from the residual box): emit its
     // activated OT copy, the next convolution's operand, through the warp's other box
-    if constexpr (sizeof(OT) == 2) {
-      if (st.fill == 0) {
-        if (lane == 0) tma_store_wait_read<0>();
-        __syncwarp();
-      }
-#pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.act_slope;
-      stager_put<OT, 32>(st, lane, v);
-      stager_flush<OT>(st, lane, p, nc + 32 - kOtCols, row0, batch, false, &p.mapD2);
-      st.buf = 0;
+    if (st.fill == 0) {
+      if (lane == 0) tma_store_wait_read<0>();
+      __syncwarp();
     }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.act_slope;
+    round_op(v);
+    stager_put<OT, 32>(st, lane, v);
+    stager_flush<OT>(st, lane, p, nc + 32 - kOtCols, row0, batch, false, &p.mapD2);
+    st.buf = 0;
   } else if constexpr (EPI == EPI_GEGLU) {
     float o[16];
 #pragma unroll

@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
             }
           }
         }
-      } else
+      } else      // (the per-segment boxes of the plain path follow as the else branch)
       for (int tile = pair0; tile < total_tiles; tile += npairs) {
         const int z = tile / tiles_mn;
         const int rem = tile - z * tiles_mn;
@@ -194,7 +194,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           }
           tc_commit_mask(&tfull_bar[as], (uint16_t)(0x3u << leader));
         }
-      } else
+      } else      // (plain path)
       for (int tile = pair0; tile < total_tiles; tile += npairs, ++it) {
         const uint32_t as = it & 1;
         mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
@@ -303,8 +303,8 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       // chunk ahead (kResidTma); the other precisions keep the register path.
       // EPI_RESID_ACT: the same residual box, but the sum goes back INTO the box and is stored from there as the f32
       // stream (mapD) while its activated 2-byte copy leaves through the warp's other box (mapD2).
-      constexpr bool kAct = EPI == EPI_RESID_ACT && sizeof(OT) == 2;
-      constexpr bool kResidTma = (EPI == EPI_RESID_OT || kAct) && sizeof(OT) == 2 && !SRN_DIRECT_STORE;
+      constexpr bool kAct = EPI == EPI_RESID_ACT && !SRN_DIRECT_STORE;
+      constexpr bool kResidTma = ((EPI == EPI_RESID_OT && sizeof(OT) == 2) || kAct) && !SRN_DIRECT_STORE;
       constexpr bool kResid = (EPI == EPI_RESID_OT && !kResidTma) || (EPI == EPI_RESID_F32 && SRN_DIRECT_STORE);
       float4 r4[kResid ? 8 : 1];
       const float4* rs = nullptr;

@@ -78,3 +78,35 @@ def test_weight_norm_checkpoint_wrapper_statistics_and_batch_independence():
     with pytest.raises(RuntimeError):
         g.inference_batch(mel)                                       # CPU tensor: no fallback path
     g.close()
+
+
+def test_window_mode_agrees_with_per_tap_boxes(tmp_path):
+    """The convolutions' window mode (gemm.cuh: GemmParams::win - one A window per K block, taps addressed through
+    the UMMA descriptor) against the plain per-tap operand boxes (SRN_WIN=0, read once per process: subprocesses).
+    Same products in a different fp32 accumulation order: a last-bit difference flips a bf16 rounding now and then
+    and ~40 layers amplify that, so the two bf16-mode waveforms differ by about half of what either differs from the
+    fp32 reference (measured 4.5e-3 vs 7.4e-3); the gate is the bf16 tolerance.  The golden tests above run with the
+    window on (the default) and their errors are the same as with per-tap boxes (7.3e-3 .. 9.1e-3)."""
+    import subprocess
+    import sys
+    import numpy as np
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, numpy as np, torch\n"
+        f"sys.path.insert(0, {root!r})\n"
+        "import serenade_b200 as S\n"
+        "g = S.HiFiGANGenerator()\n"
+        "g.load_state_dict(S.make_vocoder_state_dict(seed=0), strict=True)\n"
+        "mel = S.make_vocoder_input(300, batch=2, seed=41).to('cuda:0')\n"
+        "np.save(sys.argv[1], g.decode(mel).cpu().numpy())\n"
+    )
+    outs = []
+    for mode in ("0", "1"):
+        path = str(tmp_path / f"w{mode}.npy")
+        env = dict(os.environ, SRN_WIN=mode)
+        subprocess.run([sys.executable, "-c", code, path], check=True, env=env, timeout=300)
+        outs.append(torch.from_numpy(np.load(path)))
+    err = rel_l2(outs[1], outs[0])
+    _report(f"window mode vs per-tap boxes (2 x 300 frames, bf16): rel_l2 {err:.3e}")
+    assert err < TOL["bf16"]
+    assert not torch.equal(outs[1], torch.zeros_like(outs[1]))
