@@ -9,6 +9,9 @@ namespace srn {
 // full barrier of the destination's own pair leader), which removes a quarter of the operand traffic of every k-block
 // (the SM<->L2 fabric, not the tensor pipe, bounds this kernel: DESIGN.md 3.1).  A stage is free when BOTH pairs have
 // consumed it (empty barriers count two commits, multicast to all four CTAs).
+#ifndef SRN_EPI_PREFETCH
+#define SRN_EPI_PREFETCH 1
+#endif
 #if SRN_TRACE
 #define SRN_STAMP(k) do { if (p.trace != nullptr) p.trace[blockIdx.x * 8 + (k)] = (unsigned long long)clock64(); } while (0)
 #else
@@ -233,6 +236,24 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     float* bias_s = reinterpret_cast<float*>(smem + CFG::kBiasOff) + (warp - 2) * 128;   // this warp's bias slice
     const uint32_t tepi_addr = map_to_cta(&tempty_bar[0], leader);
     uint32_t it = 0;
+    // Per-row / per-key side inputs of the softmax epilogues, requested one tile ahead (SRN_EPI_PREFETCH): the clock64
+    // trace showed expscores at 9.9 k clocks per tile with a 4.6 k chunk loop - the rest was the serial chain of
+    // dependent L2 round trips (16 slice maxima four at a time, then the key mask) in front of every tile.
+    float pre_s[16];          // slice statistics 0..15 of this lane's row
+    uint8_t pre_k[NCH / 2];   // key-mask bytes of this lane's key in each of the warp's chunks (0 beyond N)
+    auto stat_issue = [&](int zz, int rr, bool ok, int j0, float (&s)[16]) {
+      const float* sp = (EPI == EPI_EXP ? p.stat_max : p.stat_sum) + (long long)zz * p.stat_n * p.stat_ld + rr;
+#pragma unroll
+      for (int u = 0; u < 16; ++u)
+        s[u] = (ok && j0 + u < p.stat_n) ? sp[(long long)(j0 + u) * p.stat_ld] : (EPI == EPI_EXP ? -INFINITY : 0.f);
+    };
+    auto key_issue = [&](int bb, int key0, uint8_t (&k)[NCH / 2]) {
+#pragma unroll
+      for (int cc = 0; cc < NCH / 2; ++cc) {
+        const int key = key0 + cc * 32 + lane;
+        k[cc] = key < p.N ? p.keymask[(long long)bb * p.keymask_bstride + (long long)key * p.keymask_step] : (uint8_t)0;
+      }
+    };
     for (int tile = pair0; tile < total_tiles; tile += npairs, ++it) {
       const int z = tile / tiles_mn;
       const int rem = tile - z * tiles_mn;
@@ -266,27 +287,24 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       float gs = 0.f, gss = 0.f;
       float racc = EPI == EPI_ROWMAX ? -INFINITY : 0.f, rowc = 0.f;
       if constexpr (EPI == EPI_EXP || EPI == EPI_PV) {     // per-row constants from the statistics of the earlier pass
+        // slices 0..15 of this row were requested while the previous tile's chunks were processed (pre_s); only the
+        // first tile of a CTA and rows with more than 16 slices wait for loads here, 16 in flight at a time
+        float a = EPI == EPI_EXP ? -INFINITY : 0.f;
+        for (int j0 = 0; j0 < p.stat_n; j0 += 16) {
+          if (j0 > 0 || !SRN_EPI_PREFETCH || it == 0) stat_issue(z, row, row_ok, j0, pre_s);
+#pragma unroll
+          for (int u = 0; u < 16; ++u) a = EPI == EPI_EXP ? fmaxf(a, pre_s[u]) : a + pre_s[u];
+        }
         if (row_ok) {
-          const float* sp = (EPI == EPI_EXP ? p.stat_max : p.stat_sum) + (long long)z * p.stat_n * p.stat_ld + row;
-          float a = EPI == EPI_EXP ? -INFINITY : 0.f;
-#pragma unroll 4
-          for (int j = 0; j < p.stat_n; ++j) {
-            const float s = sp[(long long)j * p.stat_ld];
-            a = EPI == EPI_EXP ? fmaxf(a, s) : a + s;
-          }
           if constexpr (EPI == EPI_EXP) rowc = (a == -INFINITY ? 0.f : a) * 1.4426950408889634f;   // fully masked row: P = 0
           else rowc = a > 0.f ? 1.0f / a : 0.f;
         }
       }
       uint32_t keybits[NCH / 2];
       if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
+        if (!SRN_EPI_PREFETCH || it == 0) key_issue(b, n0 + c_first * 32, pre_k);
 #pragma unroll
-        for (int cc = 0; cc < NCH / 2; ++cc) {
-          const int key = n0 + (c_first + cc) * 32 + lane;
-          const bool kv = key < p.N &&
-                          p.keymask[(long long)b * p.keymask_bstride + (long long)key * p.keymask_step] != 0;
-          keybits[cc] = __ballot_sync(0xffffffffu, kv);
-        }
+        for (int cc = 0; cc < NCH / 2; ++cc) keybits[cc] = __ballot_sync(0xffffffffu, pre_k[cc] != 0);
       }
       if (has_bias) {       // this warp's bias slice -> smem (read back as broadcasts, one vector per 4 columns)
         const int col = n0 + c_first * 32 + lane * 4;
@@ -335,6 +353,20 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(tepi_addr + as * 8);
+      }
+      if constexpr (SRN_EPI_PREFETCH && (EPI == EPI_EXP || EPI == EPI_PV || EPI == EPI_ROWMAX)) {
+        // the next tile's side inputs: in flight during this tile's chunks
+        const int tn = tile + npairs;
+        if (tn < total_tiles) {
+          const int zn = tn / tiles_mn;
+          const int remn = tn - zn * tiles_mn;
+          if constexpr (EPI != EPI_ROWMAX) {
+            const int rown = ((remn / ntn_u) * 2 + (int)rank) * 128 + q * 32 + lane;
+            stat_issue(zn, rown, rown < p.M, 0, pre_s);
+          }
+          if constexpr (EPI != EPI_PV)
+            key_issue(zn / p.HB, ((remn % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN + c_first * 32, pre_k);
+        }
       }
 #pragma unroll 1
       for (int cc = 0; cc < nvalid; ++cc) {
