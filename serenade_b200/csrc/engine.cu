@@ -14,6 +14,12 @@ static void configure_one() {
   SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 GemmCfg<BN>::kSmemBytes));
   SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
+  if constexpr (!std::is_same<OT, float>::value && !SRN_MC &&
+                (EPI == EPI_QKV || EPI == EPI_GEGLU || EPI == EPI_ROWMAX || EPI == EPI_EXP)) {
+    SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  GemmCfg<BN, true>::kSmemBytes));
+    SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, false, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
+  }
 #if SRN_MC
   if (BN == 256)
     SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, 256, EPI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -29,15 +29,33 @@ static void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t
   SRN_CUDA(cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...));
 }
 
-template <typename OT, int BN, int EPI>
+// A-stationary layout (gemm_mainloop.cuh): K fits the A slots, one K segment, at least two N tiles per row block.
+// Built, bit-identical, measured on one box (profiles/r01_ab_astationary.txt) and NOT adopted: with half the operand
+// bytes per tile the K = 512 GEMMs got no faster with the epilogue switched off (QKV 60.8 vs 56.9 us, Q K^T 57.3 vs
+// 46.6 us) - the operand feed is not what bounds them - so it is opt-in (SRN_ASTAT=1) for further experiments.
+static bool astat_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("SRN_ASTAT");
+    return e != nullptr && e[0] == '1';
+  }();
+  return on;
+}
+template <typename OT, int BN>
+static bool astat_ok(const GemmParams& gp, dim3 grid) {
+  if (std::is_same<OT, float>::value || !astat_enabled()) return false;
+  if (gp.nseg != 1 || gp.win != 0 || (gp.dbg_mode & 3) != 0 || grid.x < 2 || gp.nkb > 8) return false;
+  return (kAsOpBytes - gp.nkb * GemmCfg<BN, true>::kABytes) / GemmCfg<BN, true>::kBBytes >= 3;
+}
+
+template <typename OT, int BN, int EPI, bool AS = false>
 static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t st) {
   gp.ntn = (int)grid.x;
   gp.ntm = (int)grid.y;
   gp.nz = (int)grid.z;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof cfg);
-  cfg.blockDim = dim3(GemmCfg<BN>::kThreads);
-  cfg.dynamicSmemBytes = GemmCfg<BN>::kSmemBytes;
+  cfg.blockDim = dim3(GemmCfg<BN, AS>::kThreads);
+  cfg.dynamicSmemBytes = GemmCfg<BN, AS>::kSmemBytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -74,7 +92,19 @@ static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t
   const long long tiles = (long long)grid.x * grid.y * grid.z;                 // 256 x BN tiles, one per CTA pair
   const unsigned pairs = (unsigned)std::min<long long>(tiles, num_sms / 2);    // persistent: one pair per SM pair
   cfg.gridDim = dim3(2 * pairs);
-  SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, BN, EPI, false>, gp));
+  SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, BN, EPI, false, AS>, gp));
+}
+
+// the epilogues that have an A-stationary instantiation (2-byte / 1-byte operands only)
+template <typename OT, int BN, int EPI>
+static void launch_gemm_as(const GemmParams& gp, dim3 grid, int num_sms, cudaStream_t st) {
+  if constexpr (!std::is_same<OT, float>::value && !SRN_MC) {
+    if (astat_ok<OT, BN>(gp, grid)) {
+      launch_gemm_impl<OT, BN, EPI, true>(gp, grid, num_sms, st);
+      return;
+    }
+  }
+  launch_gemm_impl<OT, BN, EPI>(gp, grid, num_sms, st);
 }
 
 template <typename OT, int BN>
@@ -84,11 +114,11 @@ static void launch_gemm_bn(const GemmParams& gp, dim3 grid, int num_sms, cudaStr
     case EPI_STORE_OT: launch_gemm_impl<OT, BN, EPI_STORE_OT>(gp, grid, num_sms, st); break;
     case EPI_RESID_F32: launch_gemm_impl<OT, BN, EPI_RESID_F32>(gp, grid, num_sms, st); break;
     case EPI_RESID_OT: launch_gemm_impl<OT, BN, EPI_RESID_OT>(gp, grid, num_sms, st); break;
-    case EPI_GEGLU: launch_gemm_impl<OT, BN, EPI_GEGLU>(gp, grid, num_sms, st); break;
-    case EPI_QKV: launch_gemm_impl<OT, BN, EPI_QKV>(gp, grid, num_sms, st); break;
+    case EPI_GEGLU: launch_gemm_as<OT, BN, EPI_GEGLU>(gp, grid, num_sms, st); break;
+    case EPI_QKV: launch_gemm_as<OT, BN, EPI_QKV>(gp, grid, num_sms, st); break;
     case EPI_EULER: launch_gemm_impl<OT, BN, EPI_EULER>(gp, grid, num_sms, st); break;
-    case EPI_ROWMAX: launch_gemm_impl<OT, BN, EPI_ROWMAX>(gp, grid, num_sms, st); break;
-    case EPI_EXP: launch_gemm_impl<OT, BN, EPI_EXP>(gp, grid, num_sms, st); break;
+    case EPI_ROWMAX: launch_gemm_as<OT, BN, EPI_ROWMAX>(gp, grid, num_sms, st); break;
+    case EPI_EXP: launch_gemm_as<OT, BN, EPI_EXP>(gp, grid, num_sms, st); break;
     case EPI_PV: launch_gemm_impl<OT, BN, EPI_PV>(gp, grid, num_sms, st); break;
     case EPI_RESID_ACT: launch_gemm_impl<OT, BN, EPI_RESID_ACT>(gp, grid, num_sms, st); break;
     default: fail("unknown GEMM epilogue %d", gp.epi);
@@ -101,8 +131,8 @@ void Engine<OT>::launch_gemm(const GemmParams& gp, int bn, dim3 grid, cudaStream
   if (gp.epi == EPI_RESID_F32 && gp.resid != gp.out) fail("EPI_RESID_F32 updates its residual in place (TMA reduce-add)");
   if (gp.ab_fp8) {
     if (gp.epi != EPI_ROWMAX) fail("e4m3 operands are only used by the row-max pass");
-    if (bn == 256) launch_gemm_impl<Fp8, 256, EPI_ROWMAX>(gp, grid, num_sms_, st);
-    else launch_gemm_impl<Fp8, 128, EPI_ROWMAX>(gp, grid, num_sms_, st);
+    if (bn == 256) launch_gemm_as<Fp8, 256, EPI_ROWMAX>(gp, grid, num_sms_, st);
+    else launch_gemm_as<Fp8, 128, EPI_ROWMAX>(gp, grid, num_sms_, st);
   } else if (bn == 256) launch_gemm_bn<OT, 256>(gp, grid, num_sms_, st);
   else launch_gemm_bn<OT, 128>(gp, grid, num_sms_, st);
   ++launches;
@@ -132,6 +162,19 @@ void Engine<OT>::capture_tap(const Plan<OT>& pl, const Tap& tap, cudaStream_t st
       }
   }
   debug_tensors[tap.name] = std::move(d);
+}
+
+// Rows per block of a (row blocks, B) row-kernel grid: `dflt` when that grid fits one wave of `slots` resident blocks,
+// else the smallest multiple of `gran` that makes it fit (SRN_ROW_ONEWAVE=0: always `dflt`).
+static int row_rpb(int T, int B, int slots, int gran, int dflt) {
+  static const bool onewave = [] {
+    const char* e = getenv("SRN_ROW_ONEWAVE");
+    return !(e != nullptr && e[0] == '0');
+  }();
+  if (!onewave || (long long)cdiv(T, dflt) * B <= slots || slots / B < 1) return dflt;
+  const int per_b = slots / B;
+  int rpb = cdiv(cdiv(T, per_b), gran) * gran;
+  return rpb < dflt ? dflt : rpb;
 }
 
 template <typename OT>
@@ -169,7 +212,9 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
       ++launches;
     } break;
     case OP_GN_APPLY: {
-      const int rpb = 16;     // same-box A/B: 16 rows per block 66 us per call, 32 rows 76 us, 8 rows 78 us
+      // rows per block: 16 (same-box A/B: 66 us per call against 76 us with 32 rows and 78 us with 8), or - SRN_ROW_ONEWAVE -
+      // the smallest multiple of 4 that fits the launch in one wave of resident blocks (4 per SM)
+      const int rpb = row_rpb(L.T, B, 4 * num_sms_, 4, 16);
       const float* tb = op.use_tbias ? pl.tb.template as<float>() + ((size_t)op.resnet_idx * pl.tb_steps + step) * 512
                                      : nullptr;
       dim3 grid(cdiv(L.T, rpb), B);
@@ -178,7 +223,10 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
       ++launches;
     } break;
     case OP_GN_RES_SPK_LN: {
-      const int rpb = 32;     // same-box A/B: 32 rows per block 138 us per call, 16 rows 152 us, 8 rows 167 us
+      // rows per block: 32 (same-box A/B: 138 us per call, 16 rows 152 us, 8 rows 167 us); the per-block prologue
+      // (GroupNorm statistics + folded constants) is about half of a 32-row block's time, so a launch that needs more
+      // than one wave of resident blocks (2 per SM) gets the smallest multiple of 8 that fits it in one wave instead
+      const int rpb = row_rpb(L.T, B, 2 * num_sms_, 8, 32);
       dim3 grid(cdiv(L.T, rpb), B);
       const float* sc = pl.spk_scale.template as<float>() + (size_t)op.resnet_idx * B * 512;
       const float* sb = pl.spk_bias.template as<float>() + (size_t)op.resnet_idx * B * 512;

@@ -14,6 +14,7 @@ struct Stager {
   uint32_t base;     // shared address of this warp's 8 KB, 1024-byte aligned
   uint32_t buf;      // which box is being filled
   uint32_t fill;     // bytes of the current 128-byte row already written
+  uint32_t one;      // 1: a single 4 KB box (A-stationary layout) - every fill waits for the previous store's reads
   __device__ __forceinline__ uint32_t box() const { return base + buf * 4096; }
 };
 
@@ -25,7 +26,10 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 // Before the first write into a box: the TMA store issued two boxes ago must have finished reading it.
 __device__ __forceinline__ void stager_acquire(Stager& s, int lane) {
   if (s.fill == 0) {
-    if (lane == 0) tma_store_wait_read<1>();
+    if (lane == 0) {
+      if (s.one) tma_store_wait_read<0>();
+      else tma_store_wait_read<1>();
+    }
     __syncwarp();
   }
 }
@@ -102,7 +106,7 @@ __device__ __forceinline__ void stager_flush(Stager& s, int lane, const GemmPara
     tma_store_commit();
   }
 #endif
-  s.buf ^= 1;
+  if (!s.one) s.buf ^= 1;
   s.fill = 0;
 }
 
@@ -110,7 +114,10 @@ __device__ __forceinline__ void stager_flush(Stager& s, int lane, const GemmPara
 template <typename OutT>
 __device__ __forceinline__ void stager_store_transposed(Stager& s, int lane, const float (&v)[32],
                                                         const CUtensorMap* map, int s0, int d0, int batch) {
-  if (lane == 0) tma_store_wait_read<1>();
+  if (lane == 0) {
+    if (s.one) tma_store_wait_read<0>();
+    else tma_store_wait_read<1>();
+  }
   __syncwarp();
   const uint32_t box = s.box();
 #pragma unroll
@@ -132,7 +139,7 @@ __device__ __forceinline__ void stager_store_transposed(Stager& s, int lane, con
                  : "memory");
     tma_store_commit();
   }
-  s.buf ^= 1;
+  if (!s.one) s.buf ^= 1;
   s.fill = 0;
 }
 

@@ -16,17 +16,23 @@
 
 namespace srn {
 
-template <int BN>
+// AS = A-stationary layout (gemm_mainloop.cuh): the whole K extent of this CTA's 128 A rows stays in shared memory
+// while the pair sweeps the N tiles of that row block (K <= 8 blocks), B streams through a ring; the epilogue warps
+// get ONE staging box each instead of two to make room.
+constexpr int kAsOpBytes = 176 * 1024;    // A slots (8 x 16 KB at most) + B ring
+template <int BN, bool AS = false>
 struct GemmCfg {
   static constexpr int kStages = BN == 256 ? 4 : 5;
   static constexpr int kABytes = 128 * 128;            // this CTA's 128 rows of the pair's 256-row A tile
   static constexpr int kBBytes = (BN / 2) * 128;       // this CTA's half of the B tile's BN rows
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStgOff = kStages * kStageBytes;       // epilogue staging: 8 warps x 2 x 4 KB
-  static constexpr int kBarOff = kStgOff + 8 * 8192;          // barriers + tmem slot (256 B)
+  static constexpr int kOpBytes = AS ? kAsOpBytes : kStages * kStageBytes;
+  static constexpr int kStgWarp = AS ? 4096 : 8192;           // staging bytes per epilogue warp
+  static constexpr int kStgOff = kOpBytes;                    // epilogue staging: 8 warps x kStgWarp
+  static constexpr int kBarOff = kStgOff + 8 * kStgWarp;      // barriers + tmem slot (256 B)
   static constexpr int kRedOff = kBarOff + 256;               // GroupNorm partial reduction scratch (256 B)
   static constexpr int kBiasOff = kRedOff + 256;              // per epilogue warp: its bias slice (8 x 512 B)
-  static constexpr int kWinBarOff = kBiasOff + 8 * 512;       // window mode: its own barriers (256 B)
+  static constexpr int kWinBarOff = kBiasOff + 8 * 512;       // window mode / A-stationary mode: their own barriers (256 B)
   static constexpr int kSmemBytes = kWinBarOff + 256 + 1024;  // + alignment slack
   // window mode re-partitions the operand stages: two A windows, the rest is a ring of B stages
   static constexpr int kWinABytes = kWinRows * 128;
@@ -35,6 +41,7 @@ struct GemmCfg {
   static constexpr int kThreads = 320;
   static constexpr int kTmemCols = 2 * BN;
   static_assert(kStgOff % 1024 == 0, "staging boxes must be 1024-byte aligned for SWIZZLE_128B");
+  static_assert(kSmemBytes <= 227 * 1024, "shared memory per CTA");
 };
 
 // Build-time experiment (-DSRN_EXP2_FMA=1): every other exponential of the EPI_EXP epilogue on the FMA pipes.

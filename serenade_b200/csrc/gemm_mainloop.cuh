@@ -9,6 +9,9 @@ namespace srn {
 // full barrier of the destination's own pair leader), which removes a quarter of the operand traffic of every k-block
 // (the SM<->L2 fabric, not the tensor pipe, bounds this kernel: DESIGN.md 3.1).  A stage is free when BOTH pairs have
 // consumed it (empty barriers count two commits, multicast to all four CTAs).
+#ifndef SRN_ONEBOX
+#define SRN_ONEBOX 0      // experiment: single staging box per epilogue warp in the default layout too
+#endif
 #ifndef SRN_EPI_PREFETCH
 #define SRN_EPI_PREFETCH 1
 #endif
@@ -18,10 +21,17 @@ namespace srn {
 #define SRN_STAMP(k) do { } while (0)
 #endif
 
-template <typename OT, int BN, int EPI, bool MC>
+// AS = A-stationary (K <= 8 blocks, one K segment, several N tiles per row block; QKV / GEGLU / Q K^T): every K = 512
+// GEMM of the step sat at the SM<->L2 wall (clock64 trace: 7.0 - 8.3 k clocks per 256 x 256 tile against 4.1 k of MMA
+// time, 256 KB of operands per CTA and tile).  Here a pair owns a CONTIGUOUS range of tiles, N fastest; the A rows of
+// a row block are loaded once into K-block slots that stay put while B streams through a ring (half the operand bytes
+// per tile).  Slot kb is refilled for the next row block as soon as the last N tile's MMAs on it have committed.
+template <typename OT, int BN, int EPI, bool MC, bool AS = false>
 __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
   using TR = OpTraits<OT>;
-  using CFG = GemmCfg<BN>;
+  using CFG = GemmCfg<BN, AS>;
+  static_assert(!AS || (!MC && (EPI == EPI_QKV || EPI == EPI_GEGLU || EPI == EPI_ROWMAX || EPI == EPI_EXP)),
+                "A-stationary layout: single-box epilogues only");
   constexpr int STAGES = CFG::kStages;
   constexpr int BK = TR::kBK;
   constexpr int NCH = BN / 32;          // 32-column chunks per tile
@@ -53,6 +63,19 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   const uint32_t leader = crank & ~1u;           // cluster rank of this pair's leader
   const int pair0 = blockIdx.x / CL;
   const int npairs = gridDim.x / CL;
+  // tiles of this pair: pair0, pair0 + npairs, ... (default) or one contiguous range (AS)
+  int t_begin = pair0, t_end = total_tiles, t_step = npairs;
+  if constexpr (AS) {
+    const int tq = total_tiles / npairs, tr = total_tiles - tq * npairs;
+    t_begin = pair0 * tq + (pair0 < tr ? pair0 : tr);
+    t_end = t_begin + tq + (pair0 < tr ? 1 : 0);
+    t_step = 1;
+  }
+  uint64_t* as_a_full = wa_full;            // AS: [8] A K-block slots (shares the window-mode barrier block)
+  uint64_t* as_a_empty = as_a_full + 8;
+  uint64_t* as_b_full = as_a_empty + 8;     // [<= 8] B ring
+  uint64_t* as_b_empty = as_b_full + 8;
+  const int as_nb = AS ? min(8, (CFG::kOpBytes - p.nkb * CFG::kABytes) / CFG::kBBytes) : 0;
 
   pdl_launch_dependents();
   if (threadIdx.x == 0) SRN_STAMP(0);
@@ -73,7 +96,9 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       mbar_init(&tempty_bar[s], 16);    // one arrival per epilogue warp of both CTAs (leader's copy is used)
     }
     for (int s = 0; s < 8; ++s) mbar_init(&resid_bar[s], 1);
-    if (p.win) {
+    if constexpr (AS) {
+      for (int s = 0; s < 32; ++s) mbar_init(&as_a_full[s], 1);
+    } else if (p.win) {
       for (int s = 0; s < 2; ++s) { mbar_init(&wa_full[s], 1); mbar_init(&wa_empty[s], 1); }
       for (int s = 0; s < CFG::kWinBStages; ++s) { mbar_init(&wb_full[s], 1); mbar_init(&wb_empty[s], 1); }
     }
@@ -91,6 +116,40 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     if (elect_one()) {
       // ------------------------------------------------------------ TMA producer
       uint32_t stage = 0, phase = 0;
+      if constexpr (AS) {
+        uint32_t bs = 0, bph = 0, agen = 0;
+        int cur = -1;
+        const KSeg sg = p.seg[0];
+        uint8_t* sb0 = smem + p.nkb * CFG::kABytes;
+        for (int tile = t_begin; tile < t_end; ++tile) {
+          const int z = tile / tiles_mn;
+          const int rem = tile - z * tiles_mn;
+          const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
+          const int n0 = (rem % ntn_u) * BN;
+          const int b = z / p.HB;
+          const int h = z - b * p.HB;
+          const int a_batch = p.a_zbatch ? z : b;
+          const int b_batch = p.b_batch_mode == 0 ? 0 : (p.b_batch_mode == 1 ? b : z);
+          const int b_row = n0 + (int)rank * (BN / 2) + h * p.b_hrow;
+          const int akey = tile / ntn_u;
+          const bool newa = akey != cur;
+          cur = akey;
+          for (int kb = 0; kb < p.nkb; ++kb) {
+            if (newa) {      // (slot kb was released by the previous row block's last tile)
+              mbar_wait(&as_a_empty[kb], (agen & 1) ^ 1);
+              if (rank == 0) mbar_expect_tx(&as_a_full[kb], 2 * CFG::kABytes);
+              tma_load_3d_2sm(smem + kb * CFG::kABytes, &p.mapA[sg.src], map_to_cta(&as_a_full[kb], leader),
+                              sg.col0 + kb * BK + h * p.a_hcol, m0 + sg.shift, a_batch);
+            }
+            mbar_wait(&as_b_empty[bs], bph ^ 1);
+            if (rank == 0) mbar_expect_tx(&as_b_full[bs], 2 * CFG::kBBytes);
+            tma_load_3d_2sm(sb0 + bs * CFG::kBBytes, &p.mapB, map_to_cta(&as_b_full[bs], leader),
+                            p.b_col0 + kb * BK + h * p.b_hcol, b_row, b_batch);
+            if (++bs == (uint32_t)as_nb) { bs = 0; bph ^= 1; }
+          }
+          if (newa) ++agen;
+        }
+      } else
       if (!MC && p.win) {
         // window mode: per K block one A window (all the segments' rows) + one B box per segment
         uint32_t wa = 0, wap = 0, wb = 0, wbp = 0;
@@ -168,6 +227,38 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       constexpr uint32_t idesc = make_idesc(TR::kFmt, 256, BN);
       uint32_t stage = 0, phase = 0;
       uint32_t it = 0;
+      if constexpr (AS) {
+        uint32_t bs = 0, bph = 0, agen = 0;
+        int cur = -1;
+        const uint32_t sa0 = smem_u32(smem);
+        const uint32_t sb0 = sa0 + (uint32_t)(p.nkb * CFG::kABytes);
+        for (int tile = t_begin; tile < t_end; ++tile, ++it) {
+          const int akey = tile / ntn_u;
+          const bool newa = akey != cur;
+          cur = akey;
+          const bool lasta = tile + 1 == t_end || (tile + 1) / ntn_u != akey;
+          const uint32_t as = it & 1;
+          mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t tacc = tmem_base + as * BN;
+          for (int kb = 0; kb < p.nkb; ++kb) {
+            if (newa) mbar_wait(&as_a_full[kb], agen & 1);
+            mbar_wait(&as_b_full[bs], bph);
+            tc_fence_after();
+            if (it == 0 && kb == 0) SRN_STAMP(2);
+            const uint64_t da = make_kmajor_sw128_desc(sa0 + (uint32_t)(kb * CFG::kABytes));
+            const uint64_t db = make_kmajor_sw128_desc(sb0 + bs * (uint32_t)CFG::kBBytes);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_pair<TR::kKind>(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            tc_commit_mask(&as_b_empty[bs], 0x3);
+            if (lasta) tc_commit_mask(&as_a_empty[kb], 0x3);     // the next row block may overwrite this slot
+            if (++bs == (uint32_t)as_nb) { bs = 0; bph ^= 1; }
+          }
+          tc_commit_mask(&tfull_bar[as], (uint16_t)(0x3u << leader));
+          SRN_STAMP(3);
+          if (newa) ++agen;
+        }
+      } else
       if (!MC && p.win) {
         uint32_t wa = 0, wap = 0, wb = 0, wbp = 0;
         const int kcb = p.seg[0].nblk;
@@ -227,9 +318,10 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     const int q = warp & 3;                 // TMEM lane quarter this warp may access (warp id % 4)
     const int sub = (warp - 2) >> 2;        // which half of the tile's columns
     Stager st;
-    st.base = smem_u32(smem + CFG::kStgOff + (warp - 2) * 8192);
+    st.base = smem_u32(smem + CFG::kStgOff + (warp - 2) * CFG::kStgWarp);
     st.buf = 0;
     st.fill = 0;
+    st.one = (AS || SRN_ONEBOX) ? 1u : 0u;
     uint32_t rphase = 0;      // parity of this warp's residual barrier (kResidTma)
     const bool has_bias = p.bias != nullptr;
     const bool has_alpha = p.alpha != 1.0f;
@@ -254,7 +346,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         k[cc] = key < p.N ? p.keymask[(long long)bb * p.keymask_bstride + (long long)key * p.keymask_step] : (uint8_t)0;
       }
     };
-    for (int tile = pair0; tile < total_tiles; tile += npairs, ++it) {
+    for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
       const int z = tile / tiles_mn;
       const int rem = tile - z * tiles_mn;
       const int mt = (rem / ntn_u) * 2 + (int)rank;     // 128-row tile index inside the batch entry
@@ -356,8 +448,8 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       }
       if constexpr (SRN_EPI_PREFETCH && (EPI == EPI_EXP || EPI == EPI_PV || EPI == EPI_ROWMAX)) {
         // the next tile's side inputs: in flight during this tile's chunks
-        const int tn = tile + npairs;
-        if (tn < total_tiles) {
+        const int tn = tile + t_step;
+        if (tn < t_end) {
           const int zn = tn / tiles_mn;
           const int remn = tn - zn * tiles_mn;
           if constexpr (EPI != EPI_ROWMAX) {

@@ -181,12 +181,19 @@ __device__ __forceinline__ void gn_reduce_stats(const float* __restrict__ part, 
   }
   __syncthreads();
   if (t < 8) {
+    // (double divisions and square roots are long software sequences on this chip and sit on every block's critical
+    //  path: a float seed plus one Newton step in double gives 1/n and 1/sqrt(var + eps) to ~1e-14)
     const double n = 64.0 * (double)(nvalid != nullptr ? max(nvalid[b], 1) : T);
-    const double mean = red[2 * t] / n;
-    double var = red[2 * t + 1] / n - mean * mean;
+    double inv_n = (double)(1.0f / (float)n);
+    inv_n = inv_n * (2.0 - n * inv_n);
+    const double mean = red[2 * t] * inv_n;
+    double var = red[2 * t + 1] * inv_n - mean * mean;
     if (var < 0.0) var = 0.0;
+    const double x = var + 1e-5;
+    double r = (double)rsqrtf((float)x);
+    r = r * (1.5 - 0.5 * x * r * r);
     stats[2 * t] = (float)mean;
-    stats[2 * t + 1] = (float)(1.0 / sqrt(var + 1e-5));
+    stats[2 * t + 1] = (float)r;
   }
   __syncthreads();
 }
@@ -194,7 +201,7 @@ __device__ __forceinline__ void gn_reduce_stats(const float* __restrict__ part, 
 // ------------------------------------------------------------------------------------------------
 // out = (Mish(GN(y)) + tbias) * mask      (tbias may be null).  256 threads = 4 rows x 64 threads x 8 ch.
 template <typename OT>
-__global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__ y, const float* __restrict__ part,
+__global__ void __launch_bounds__(256, 4) gn_apply_kernel(const float* __restrict__ y, const float* __restrict__ part,
                                                        int mtiles, int T, long long bstride,
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                                        const float* __restrict__ tbias, const uint8_t* __restrict__ mask,
@@ -205,17 +212,17 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const float* __restrict__
   __shared__ double red[256];
   pdl_launch_dependents();
   ROW_STAMP(0);
+  const int c = (threadIdx.x & 63) * 8;
+  const int g = c >> 6;
+  float ga[8], be[8], tb[8];
+  load8(gamma + c, ga);       // weights: not produced by an earlier kernel, fetched under the previous kernel's tail
+  load8(beta + c, be);
   pdl_wait();
   ROW_STAMP(1);
   const int b = blockIdx.y;
   gn_reduce_stats(part, b, mtiles, T, nvalid, stats, red);
   ROW_STAMP(2);
-  const int c = (threadIdx.x & 63) * 8;
-  const int g = c >> 6;
   const float mean = stats[2 * g], rstd = stats[2 * g + 1];
-  float ga[8], be[8], tb[8];
-  load8(gamma + c, ga);
-  load8(beta + c, be);
   if (tbias != nullptr) load8(tbias + (long long)b * tbias_bstride + c, tb);      // (stride 0: one t for the batch)
   else {
 #pragma unroll
@@ -264,6 +271,13 @@ __global__ void __launch_bounds__(256, SRN_GNRES_MINBLOCKS) gn_res_spk_ln(const 
   __shared__ __align__(16) float cst[6][kC];     // folded GN scale / shift, speaker scale / bias, LN gain / bias
   pdl_launch_dependents();
   ROW_STAMP(0);
+  // weights (not produced by an earlier kernel): fetched under the previous kernel's tail, two channels per thread
+  float wg[2], wb[2], wlg[2], wlb[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int c = threadIdx.x + k * 256;
+    wg[k] = gamma[c]; wb[k] = beta[c]; wlg[k] = ln_g[c]; wlb[k] = ln_b[c];
+  }
   pdl_wait();
   ROW_STAMP(1);
   const int b = blockIdx.y;
@@ -285,15 +299,24 @@ __global__ void __launch_bounds__(256, SRN_GNRES_MINBLOCKS) gn_res_spk_ln(const 
 #if SRN_GNRES_PREFETCH
   if (r < r1) fetch(r);
 #endif
+  float wsc[2], wsb[2];      // (written once per solve by the prepass: read after the wait, in flight during the statistics)
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int c = threadIdx.x + k * 256;
+    wsc[k] = spk_scale[(long long)b * kC + c];
+    wsb[k] = spk_bias[(long long)b * kC + c];
+  }
   gn_reduce_stats(part, b, mtiles, T, nvalid, stats, red);
-  for (int c = threadIdx.x; c < kC; c += 256) {
-    const float a = stats[2 * (c >> 6) + 1] * gamma[c];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int c = threadIdx.x + k * 256;
+    const float a = stats[2 * (c >> 6) + 1] * wg[k];
     cst[0][c] = a;
-    cst[1][c] = beta[c] - stats[2 * (c >> 6)] * a;
-    cst[2][c] = spk_scale[(long long)b * kC + c];
-    cst[3][c] = spk_bias[(long long)b * kC + c];
-    cst[4][c] = ln_g[c];
-    cst[5][c] = ln_b[c];
+    cst[1][c] = wb[k] - stats[2 * (c >> 6)] * a;
+    cst[2][c] = wsc[k];
+    cst[3][c] = wsb[k];
+    cst[4][c] = wlg[k];
+    cst[5][c] = wlb[k];
   }
   __syncthreads();
   ROW_STAMP(2);
