@@ -141,7 +141,8 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
   } else if constexpr (EPI == EPI_GEGLU) {
     float o[16];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) o[i] = v[2 * i] * gelu_erf(v[2 * i + 1]);
+    for (int i = 0; i < 16; ++i)
+      o[i] = v[2 * i] * ((SRN_GELU_TAIL && sizeof(OT) == 2) ? gelu_tail(v[2 * i + 1]) : gelu_erf(v[2 * i + 1]));
     if constexpr (sizeof(OT) == 4) {
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
