@@ -106,6 +106,17 @@ void maybe_window(GemmParams& gp, const OT* ptr, int cols, int rows, long long a
   gp.win = win_mode();
   gp.win_min = mn;
 }
+// Attention passes in (batch, head) slices whose P~ stays in the L2: opt-in experiment (SRN_ATTN_SLICES=1).  Measured
+// on one box at C2 (profiles/r01_ab_attn_slices.txt): two slices of 65 MB instead of one 131 MB P~ cost more in the
+// extra launches than the L2 residency returns (exp 2 x 37 vs 65 us, P~ V 2 x 41 vs 67 us, solve 24.2 - 24.6 vs 23.6 ms).
+constexpr size_t kPSliceBytes = 68u << 20;
+inline bool attn_slices() {
+  static const bool on = [] {
+    const char* e = getenv("SRN_ATTN_SLICES");
+    return e != nullptr && e[0] == '1';
+  }();
+  return on;
+}
 // row_tiles = number of 256-row pair tiles; one CTA pair per SM pair (74 on a B200)
 inline int pick_bn(int N, long long row_tiles) {
   const long long nt256 = (N + 255) / 256, nt128 = (N + 127) / 128;
@@ -249,6 +260,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
   const int sc_bn = pick_bn(S, tiles * H);
   const int stat_n = cdiv(S, 64);          // one (max, sum) partial per row per 64-key slice
   if ((size_t)B * H * stat_n * L.Sp * 4 > pl.smax.bytes) fail("softmax statistics buffer too small");
+  Op exp_op;
   for (int pass = 0; pass < 2; ++pass) {
     Op op;
     op.gp = base_gemm(pl, level);
@@ -291,7 +303,8 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.d_zbatch = 1;
     op.grid = dim3(cdiv(S, op.bn), L.mtiles, B * H);
     if (pass == 1) op.tap = Tap{"P", P, 1, S, S, Sp, (long long)S * Sp, B * H, 0};
-    push(op, pass == 0 ? "rowmax" : "expscores");
+    if (pass == 0) push(op, "rowmax");
+    else exp_op = op;
   }
   {  // O[b, :, h*512:(h+1)*512] = (P~[b,h] V[b,h]) / rowsum
     Op op;
@@ -319,7 +332,26 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.d_hcol = 512;
     op.grid = dim3(512 / op.bn, L.mtiles, B * H);
     op.tap = Tap{"ao", ao, 1, S, 2048, 2048, gp.out_bstride, B, 0};
-    push(op, "pv");
+    // P~ of the whole (batch, head) range is B H S Sp elements - 131 MB at C2's full rate, 2.3 GB at C5 - more than the
+    // 126 MB L2.  With SRN_ATTN_SLICES=1 both passes run slice by slice over the (batch, head) range, a slice's P~
+    // (<= kPSliceBytes) being consumed by its P~ V launch right after it was written (measured: not a gain, see above).
+    const int BH = B * H;
+    const size_t z_bytes = (size_t)S * Sp * sizeof(OT);
+    int nsl = attn_slices() ? (int)std::min<size_t>((size_t)BH, (z_bytes * BH + kPSliceBytes - 1) / kPSliceBytes) : 1;
+    // ... but never fewer than about four waves of tiles per launch (74 CTA pairs)
+    const long long tiles_z = (long long)cdiv(S, sc_bn) * L.mtiles;
+    while (nsl > 1 && tiles_z * (BH / nsl) < 4 * 74) --nsl;
+    const int zper = cdiv(BH, nsl);
+    for (int z0 = 0; z0 < BH; z0 += zper) {
+      const int nz = std::min(zper, BH - z0);
+      Op e = exp_op, v = op;
+      e.gp.z0 = z0;
+      e.grid.z = nz;
+      v.gp.z0 = z0;
+      v.grid.z = nz;
+      push(e, "expscores");
+      push(v, "pv");
+    }
   }
   {  // h = attn_out W_o^T + b_o + h    (transformer.py:304)
     Op op;

@@ -646,7 +646,7 @@ std::string Engine<OT>::profile_ops(int B, int T, int reps) {
     switch (op.kind) {
       case OP_GEMM:
         kind = op.bn == 256 ? "gemm_bn256" : "gemm_bn128";
-        flops = 2.0 * (double)op.gp.M * op.gp.N * ((double)op.gp.nkb * (op.gp.ab_fp8 ? 128 : BK)) * (double)(B * op.gp.HB);
+        flops = 2.0 * (double)op.gp.M * op.gp.N * ((double)op.gp.nkb * (op.gp.ab_fp8 ? 128 : BK)) * (double)op.grid.z;
         break;
       case OP_PACKX: kind = "pack_cf_to_cl"; bytes = (double)B * cfg_.out_channels * T * (4 + es); break;
       case OP_GN_APPLY: kind = "gn_apply"; bytes = rows * 512 * (4 + es); break;

@@ -60,6 +60,7 @@ struct GemmParams {
   int nseg;
   int nkb;          // total K blocks
   int ntn, ntm, nz; // tile grid: N tiles, M tiles, batch entries (persistent CTAs loop over ntn*ntm*nz tiles)
+  int z0;           // first batch entry of this launch (the attention passes may run a slice of the (batch, head) range)
   int M;            // valid rows per batch entry
   int N;            // valid output columns
   int HB;           // inner batch (heads): blockIdx.z = b * HB + h

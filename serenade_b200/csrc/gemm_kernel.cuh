@@ -50,6 +50,9 @@ struct GemmCfg {
 #ifndef SRN_EXP2_FMA
 #define SRN_EXP2_FMA 0
 #endif
+#ifndef SRN_KEY_FASTPATH
+#define SRN_KEY_FASTPATH 1
+#endif
 // 2^x without the special-function unit: round-to-nearest split x = n + f through the 1.5 * 2^23 trick (n lands in the
 // low mantissa bits of t), degree-4 near-minimax polynomial for 2^f on [-0.5, 0.5] (max relative error 3.6e-6 in f32
 // evaluation), exponent added as an integer.  x is clamped to >= -125 (result 2^-125 instead of 0: irrelevant next to a
@@ -179,20 +182,52 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
       stager_store_transposed<OT>(st, lane, v, &p.mapD2, row0, nc - p.split_n, batch);
     }
   } else if constexpr (EPI == EPI_ROWMAX) {
+    if (SRN_KEY_FASTPATH && keybits == 0xffffffffu) {      // all 32 keys of the chunk take part (warp-uniform): no selects
+      float m0 = racc, m1 = -INFINITY;
 #pragma unroll
-    for (int i = 0; i < 32; ++i)
-      if ((keybits >> i) & 1u) racc = fmaxf(racc, v[i] * p.alpha);
+      for (int i = 0; i < 32; i += 2) {
+        m0 = fmaxf(m0, v[i] * p.alpha);
+        m1 = fmaxf(m1, v[i + 1] * p.alpha);
+      }
+      racc = fmaxf(m0, m1);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if ((keybits >> i) & 1u) racc = fmaxf(racc, v[i] * p.alpha);
+    }
   } else if constexpr (EPI == EPI_EXP) {
     // (32768 exponentials per CTA and tile = 2048 clocks of MUFU.EX2; see SRN_EXP2_FMA above)
     const float sc = p.alpha * 1.4426950408889634f;
+    if (SRN_KEY_FASTPATH && keybits == 0xffffffffu) {
+      // all 32 keys take part (every chunk but a row's last ones and padded batches): no per-element select, and the
+      // row sum as four interleaved partial sums instead of one 32-long dependent chain.  The order of the additions
+      // is fixed per 64-key slice whatever the tile shape, so "alone == inside a batch" stays bit-exact.
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      float e;
-      const float x = fmaf(v[i], sc, -rowc);
-      if (SRN_EXP2_FMA && (i & 1)) e = exp2_fma(x);
-      else asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x));
-      v[i] = ((keybits >> i) & 1u) ? e : 0.f;
-      racc += v[i];
+      for (int i = 0; i < 32; i += 4) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float x = fmaf(v[i + k], sc, -rowc);
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(v[i + k]) : "f"(x));
+        }
+        s0 += v[i]; s1 += v[i + 1]; s2 += v[i + 2]; s3 += v[i + 3];
+      }
+      racc += (s0 + s1) + (s2 + s3);
+    } else {
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float e;
+          const float x = fmaf(v[i + k], sc, -rowc);
+          if (SRN_EXP2_FMA && (k & 1)) e = exp2_fma(x);
+          else asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x));
+          v[i + k] = ((keybits >> (i + k)) & 1u) ? e : 0.f;
+        }
+        s0 += v[i]; s1 += v[i + 1]; s2 += v[i + 2]; s3 += v[i + 3];
+      }
+      racc += (s0 + s1) + (s2 + s3);
     }
     round_op(v);
     stager_acquire(st, lane);

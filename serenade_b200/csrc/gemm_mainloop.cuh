@@ -122,8 +122,8 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         const KSeg sg = p.seg[0];
         uint8_t* sb0 = smem + p.nkb * CFG::kABytes;
         for (int tile = t_begin; tile < t_end; ++tile) {
-          const int z = tile / tiles_mn;
-          const int rem = tile - z * tiles_mn;
+          const int z = tile / tiles_mn + p.z0;
+          const int rem = tile % tiles_mn;
           const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
           const int n0 = (rem % ntn_u) * BN;
           const int b = z / p.HB;
@@ -155,8 +155,8 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         uint32_t wa = 0, wap = 0, wb = 0, wbp = 0;
         const int kcb = p.seg[0].nblk;
         for (int tile = pair0; tile < total_tiles; tile += npairs) {
-          const int z = tile / tiles_mn;
-          const int rem = tile - z * tiles_mn;
+          const int z = tile / tiles_mn + p.z0;
+          const int rem = tile % tiles_mn;
           const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
           const int n0 = (rem % ntn_u) * BN;
           const int b = z / p.HB;
@@ -181,8 +181,8 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         }
       } else      // (the per-segment boxes of the plain path follow as the else branch)
       for (int tile = pair0; tile < total_tiles; tile += npairs) {
-        const int z = tile / tiles_mn;
-        const int rem = tile - z * tiles_mn;
+        const int z = tile / tiles_mn + p.z0;
+        const int rem = tile % tiles_mn;
         const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
         const int n0 = ((rem % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN;     // may lie beyond N for the odd last unit (all zero)
         const int b = z / p.HB;
@@ -347,8 +347,8 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       }
     };
     for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
-      const int z = tile / tiles_mn;
-      const int rem = tile - z * tiles_mn;
+      const int z = tile / tiles_mn + p.z0;
+      const int rem = tile % tiles_mn;
       const int mt = (rem / ntn_u) * 2 + (int)rank;     // 128-row tile index inside the batch entry
       const int m0 = mt * 128;
       const int n0 = ((rem % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN;
@@ -450,8 +450,8 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         // the next tile's side inputs: in flight during this tile's chunks
         const int tn = tile + t_step;
         if (tn < t_end) {
-          const int zn = tn / tiles_mn;
-          const int remn = tn - zn * tiles_mn;
+          const int zn = tn / tiles_mn + p.z0;
+          const int remn = tn % tiles_mn;
           if constexpr (EPI != EPI_ROWMAX) {
             const int rown = ((remn / ntn_u) * 2 + (int)rank) * 128 + q * 32 + lane;
             stat_issue(zn, rown, rown < p.M, 0, pre_s);
