@@ -170,9 +170,11 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
         asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(hi) : "f"(v[4 * i + 3]), "f"(v[4 * i + 2]));
         w[i] = (uint32_t)lo | ((uint32_t)hi << 16);
       }
-      uint4* g8 = reinterpret_cast<uint4*>(p.out8 + (long long)batch * p.out8_bstride + (long long)row * p.ld8 + nc);
-      g8[0] = make_uint4(w[0], w[1], w[2], w[3]);
-      g8[1] = make_uint4(w[4], w[5], w[6], w[7]);
+      // one 256-bit store per lane (STG.256, sm_100): a whole 32-byte sector at once instead of two half-sector writes
+      uint8_t* g8 = p.out8 + (long long)batch * p.out8_bstride + (long long)row * p.ld8 + nc;
+      asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(g8), "r"(w[0]), "r"(w[1]), "r"(w[2]),
+                   "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+                   : "memory");
     }
     if (nc < p.split_n) {
       stager_acquire(st, lane);
