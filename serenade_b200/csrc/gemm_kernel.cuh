@@ -159,6 +159,10 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     stager_flush<OT>(st, lane, p, (nc >> 1) + 16 - kOtCols, row0, batch);
   } else if constexpr (EPI == EPI_QKV) {
     round_op(v);
+    if (p.qk_norm2 != nullptr && nc < p.split_n) {      // (gs: this row's squared norm over the warp's Q | K columns)
+#pragma unroll
+      for (int i = 0; i < 32; ++i) gs = fmaf(v[i], v[i], gs);
+    }
     if (nc < p.split_n && p.out8 != nullptr && row_ok) {
       // e4m3 copy of Q | K for the row-max pass, 32 bytes per lane and chunk straight to global memory (staging it
       // through a TMA box was measured and is slower: it needs the chunk loop unrolled and a third box)

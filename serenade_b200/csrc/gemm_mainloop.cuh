@@ -111,6 +111,13 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();     // everything above overlapped with the previous kernel's tail
   if (threadIdx.x == 0) SRN_STAMP(1);
+  // shift-free softmax: every score of this launch is provably within +-75 (attn_flags_kernel) - the row-max pass has
+  // nothing to do, the exp pass uses shift 0
+  bool noshift = false;
+  if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
+    noshift = p.noshift != nullptr && *reinterpret_cast<const volatile int*>(p.noshift) != 0;
+    if (EPI == EPI_ROWMAX && noshift) t_end = t_begin;
+  }
 
   if (warp == 0) {
     if (elect_one()) {
@@ -154,7 +161,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         // window mode: per K block one A window (all the segments' rows) + one B box per segment
         uint32_t wa = 0, wap = 0, wb = 0, wbp = 0;
         const int kcb = p.seg[0].nblk;
-        for (int tile = pair0; tile < total_tiles; tile += npairs) {
+        for (int tile = t_begin; tile < t_end; tile += t_step) {
           const int z = tile / tiles_mn + p.z0;
           const int rem = tile % tiles_mn;
           const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
@@ -180,7 +187,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           }
         }
       } else      // (the per-segment boxes of the plain path follow as the else branch)
-      for (int tile = pair0; tile < total_tiles; tile += npairs) {
+      for (int tile = t_begin; tile < t_end; tile += t_step) {
         const int z = tile / tiles_mn + p.z0;
         const int rem = tile % tiles_mn;
         const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
@@ -263,7 +270,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         uint32_t wa = 0, wap = 0, wb = 0, wbp = 0;
         const int kcb = p.seg[0].nblk;
         const bool boff = (p.win & 2) != 0;
-        for (int tile = pair0; tile < total_tiles; tile += npairs, ++it) {
+        for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
           const uint32_t as = it & 1;
           mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
           tc_fence_after();
@@ -289,7 +296,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           tc_commit_mask(&tfull_bar[as], (uint16_t)(0x3u << leader));
         }
       } else      // (plain path)
-      for (int tile = pair0; tile < total_tiles; tile += npairs, ++it) {
+      for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
         const uint32_t as = it & 1;
         mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -382,13 +389,13 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         // slices 0..15 of this row were requested while the previous tile's chunks were processed (pre_s); only the
         // first tile of a CTA and rows with more than 16 slices wait for loads here, 16 in flight at a time
         float a = EPI == EPI_EXP ? -INFINITY : 0.f;
-        for (int j0 = 0; j0 < p.stat_n; j0 += 16) {
+        for (int j0 = 0; j0 < ((EPI == EPI_EXP && noshift) ? 0 : p.stat_n); j0 += 16) {
           if (j0 > 0 || !SRN_EPI_PREFETCH || it == 0) stat_issue(z, row, row_ok, j0, pre_s);
 #pragma unroll
           for (int u = 0; u < 16; ++u) a = EPI == EPI_EXP ? fmaxf(a, pre_s[u]) : a + pre_s[u];
         }
         if (row_ok) {
-          if constexpr (EPI == EPI_EXP) rowc = (a == -INFINITY ? 0.f : a) * 1.4426950408889634f;   // fully masked row: P = 0
+          if constexpr (EPI == EPI_EXP) rowc = (a == -INFINITY || noshift ? 0.f : a) * 1.4426950408889634f;   // fully masked row: P = 0
           else rowc = a > 0.f ? 1.0f / a : 0.f;
         }
       }
@@ -454,7 +461,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           const int remn = tn % tiles_mn;
           if constexpr (EPI != EPI_ROWMAX) {
             const int rown = ((remn / ntn_u) * 2 + (int)rank) * 128 + q * 32 + lane;
-            stat_issue(zn, rown, rown < p.M, 0, pre_s);
+            if (!(EPI == EPI_EXP && noshift)) stat_issue(zn, rown, rown < p.M, 0, pre_s);
           }
           if constexpr (EPI != EPI_PV)
             key_issue(zn / p.HB, ((remn % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN + c_first * 32, pre_k);
@@ -576,6 +583,22 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
               red[(q * NG + (c >> 1)) * 2 + 1] = ss;
             }
             gs = 0.f; gss = 0.f;
+          }
+        }
+      }
+      if constexpr (EPI == EPI_QKV) {
+        // largest squared norm over this warp's rows of its Q | K column part -> atomic max (non-negative floats order
+        // like their bit patterns); an upper bound of every |q . k| follows from these in attn_flags_kernel
+        const int col0 = n0 + c_first * 32;
+        if (p.qk_norm2 != nullptr && nvalid > 0 && col0 < p.split_n) {
+          float m = row_ok ? gs : 0.f;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+          if (lane == 0) {
+            const int isk = col0 >= (p.split_n >> 1) ? 1 : 0;
+            const int cc0 = col0 - isk * (p.split_n >> 1);
+            atomicMax(reinterpret_cast<int*>(p.qk_norm2) + (b * 4 + (cc0 >> 9)) * 16 + isk * 8 + ((cc0 & 511) >> 6),
+                      __float_as_int(m));
           }
         }
       }

@@ -107,6 +107,27 @@ def test_golden_vectors_per_step_gate_tf32(name, cfm_tf32, dev):
     assert ex < TF32_STEP_TOL
 
 
+@pytest.mark.parametrize("precision,tol", [("tf32", 2e-3), ("bf16", 3e-2)])
+def test_large_logits_take_the_shifted_softmax(jitter_sd, dev, precision, tol):
+    """The shift-free softmax shortcut (attn_flags_kernel) must switch itself off when the Cauchy-Schwarz bound of the
+    scores exceeds 75: with W_q scaled by 4 the bound is ~200 and the real scores reach +-40, so exp() without the
+    row maximum would lose the small terms / overflow at larger scales.  Parity against the oracle on the same weights
+    (diffusers Attention -> F.scaled_dot_product_attention semantics)."""
+    import serenade_b200 as S
+    from oracle import cfm_oracle as O
+    sd = {k: (v * 4.0 if k.endswith("attn1.to_q.weight") else v.clone()) for k, v in jitter_sd.items()}
+    cfm = _make_cfm(sd, precision)
+    b = S.make_batch([200, 150], n_steps=2, seed=33)
+    t = torch.tensor(0.41)
+    v = cfm.estimator(b.z.to(dev), b.mask.to(dev), b.mu.to(dev), t, b.spks.to(dev)).cpu()
+    with torch.inference_mode():
+        v_ref = O.estimator_forward(sd, b.z, b.mask, b.mu, t, b.spks)
+    e = rel_l2(v, v_ref)
+    _report(f"large_logits_{precision}.txt", f"W_q x 4 ({precision}): per-step rel_l2={e:.3e}")
+    assert torch.isfinite(v).all()
+    assert e < tol
+
+
 def test_solver_matches_oracle_mixed_lengths(cfm_jitter, jitter_sd, dev):
     import serenade_b200 as S
     from oracle import cfm_oracle as O
