@@ -44,7 +44,7 @@ struct ConvW {
   float* b = nullptr;
 };
 
-enum OpKind : int { OP_GEMM, OP_PACKX, OP_GN_APPLY, OP_GN_RES_SPK_LN, OP_LAYERNORM, OP_ATTN_FLAGS };
+enum OpKind : int { OP_GEMM, OP_PACKX, OP_GN_APPLY, OP_GN_RES_SPK_LN, OP_LAYERNORM };
 
 struct Tap {
   const char* name = nullptr;   // debug tensor name (null = none)
@@ -94,7 +94,7 @@ struct Plan {
   Level lv[2];
   DevBuf xin, y, r, gnpart, a1, hres, ln, qk, vt, smax, ssum, P, ao, gg, hid0, hid1, hc, cv;
   DevBuf qk8;      // e4m3 copy of Q | K (row-max pass operands)
-  DevBuf qk_norm2, noshift;   // shift-free softmax test: [B * 4][16] squared-norm maxima, [1] flag (attn_flags_kernel)
+  DevBuf qk_norm2, noshift;   // shift-free softmax test: [B * 4][16] squared-norm maxima, [1] flag (EPI_ROWMAX prologue)
   DevBuf x_state, mask, spk_in, mu_in, spk_scale, spk_bias, tsteps, dts, temb0, temb1, temb2, tb;
   DevBuf blend_mask, blend_src;
   DevBuf nvalid;      // [2][B] unmasked frames per batch entry at full / half rate (valid-frame GroupNorm mode)

@@ -106,8 +106,8 @@ void maybe_window(GemmParams& gp, const OT* ptr, int cols, int rows, long long a
   gp.win = win_mode();
   gp.win_min = mn;
 }
-// Shift-free softmax when every score is provably within +-75 (attn_flags_kernel); SRN_NOSHIFT=0: always run the
-// row-max pass.
+// Shift-free softmax when every score is provably within +-64 (gemm_mainloop.cuh, EPI_ROWMAX prologue); SRN_NOSHIFT=0:
+// always run the row-max pass.
 inline bool noshift_enabled() {
   static const bool on = [] {
     const char* e = getenv("SRN_NOSHIFT");
@@ -259,16 +259,15 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.mapD2 = make_tmap_3d(vt, sizeof(OT), S, 2048, B, Sp, (uint64_t)2048 * Sp, 32, 32, false);
     op.grid = dim3(6144 / op.bn, L.mtiles, B);
     op.tap = Tap{"qk", qk, 1, S, 4096, 4096, gp.out_bstride, B, 0};
-    if (noshift_enabled()) gp.qk_norm2 = pl.qk_norm2.template as<float>();
+    if (noshift_enabled() && B * H <= 1024) {
+      gp.qk_norm2 = pl.qk_norm2.template as<float>();
+      gp.rowmask = pl.mask.template as<uint8_t>();      // (EPI_QKV only uses it to keep padded frames out of the norms)
+      gp.mask_bstride = pl.Tp;
+      gp.mask_step = L.mask_step;
+    }
     push(op, "qkv");
   }
-  if (noshift_enabled()) {      // can this block's softmax run without a shift?  (rowops.cuh: attn_flags_kernel)
-    Op op;
-    op.kind = OP_ATTN_FLAGS;
-    op.name = tag + ".flags";
-    op.level = level;
-    pl.ops.push_back(op);
-  }
+
   // Attention without a score matrix in HBM.  Q K^T runs twice on the tensor cores: pass 1 keeps only per-row
   // maxima (key-masked), pass 2 recomputes the tile, writes P~ = exp(s - rowmax) in operand precision and partial
   // row sums; P~ V then divides by the row sum in its epilogue.  Replaces scores f32 write + read and the softmax
@@ -308,7 +307,11 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.stat_sum = pl.ssum.template as<float>();
     gp.stat_n = stat_n;
     gp.stat_ld = L.Sp;
-    if (noshift_enabled()) gp.noshift = pl.noshift.template as<int>();
+    if (noshift_enabled() && B * H <= 1024) {      // shift-free softmax test: evaluated by the row-max pass, consumed by the exp pass
+      gp.noshift = pl.noshift.template as<int>();
+      gp.qk_norm2 = pl.qk_norm2.template as<float>();
+      gp.nz_norm = B * H;
+    }
     gp.keymask = pl.mask.template as<uint8_t>();
     gp.keymask_bstride = pl.Tp;
     gp.keymask_step = L.mask_step;
@@ -469,7 +472,7 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
   pl.qk.alloc(rows * 4096 * es);
   if (rowmax_fp8()) pl.qk8.alloc(rows * 4096);
   pl.qk_norm2.alloc((size_t)B * H * 16 * 4);
-  pl.noshift.alloc(16);
+  pl.noshift.alloc((size_t)B * H * 4);
   pl.vt.alloc((size_t)B * 2048 * pl.lv[0].Sp * es);
   {  // softmax statistics: one (max, sum) partial per row per 128-column (or 64-column) slice of the score GEMM
     const size_t n128 = 2 * (size_t)cdiv(T, 128);

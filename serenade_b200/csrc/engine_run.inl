@@ -235,11 +235,6 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
                nvalid);
       ++launches;
     } break;
-    case OP_ATTN_FLAGS: {
-      launch_k(attn_flags_kernel, dim3(1), dim3(256), st, pl.qk_norm2.template as<float>(), B * 4, 1.0f / sqrtf(512.0f),
-               pl.noshift.template as<int>());
-      ++launches;
-    } break;
     case OP_LAYERNORM: {
       const long long nrows = (long long)B * L.R;
       launch_k(layernorm_kernel<OT>, dim3((unsigned)((nrows + 7) / 8)), dim3(256), st, pl.hres.template as<float>(), nrows,
@@ -657,7 +652,6 @@ std::string Engine<OT>::profile_ops(int B, int T, int reps) {
       case OP_GN_APPLY: kind = "gn_apply"; bytes = rows * 512 * (4 + es); break;
       case OP_GN_RES_SPK_LN: kind = "gn_res_spk_ln"; bytes = rows * 512 * (4 + 4 + 4 + es); break;
       case OP_LAYERNORM: kind = "layernorm"; bytes = rows * 512 * (4 + es); break;
-      case OP_ATTN_FLAGS: kind = "attn_flags"; break;
     }
     char buf[512];
     snprintf(buf, sizeof buf, "%s{\"op\": \"%s\", \"kernel\": \"%s\", \"ms\": %.6f, \"flops\": %.6e, \"bytes\": %.6e}",

@@ -122,12 +122,14 @@ struct GemmParams {
   float* stat_sum;
   int stat_n;
   int stat_ld;
-  // Shift-free softmax (attn_flags_kernel, rowops.cuh).  EPI_QKV: qk_norm2[(b * 4 + h) * 16 + (K ? 8 : 0) + part] collects
+  // Shift-free softmax (test in the EPI_ROWMAX prologue, gemm_mainloop.cuh).  EPI_QKV: qk_norm2[(b * 4 + h) * 16 + (K ? 8 : 0) + part] collects
   // (atomic max of float bits) the largest squared norm of a 64..128-column part of any Q / K row of head h.
-  // EPI_ROWMAX / EPI_EXP: *noshift != 0 means every |score| of this launch is provably <= 75, exp needs no shift:
-  // the row-max pass returns at once and the exp pass uses shift 0.
+  // EPI_ROWMAX evaluates the test per (batch, head) entry (gemm_mainloop.cuh), writes noshift[z] and skips the tiles of
+  // entries whose |score| is provably <= 64; EPI_EXP runs those entries with shift 0 (and clears the maxima for the
+  // next attention block).
   float* qk_norm2;
-  const int* noshift;
+  int* noshift;
+  int nz_norm;      // number of (batch, head) entries of qk_norm2
   const uint8_t* keymask;   // (B, keys): key k of batch b takes part iff keymask[b*keymask_bstride + k*keymask_step] != 0
   int keymask_bstride;
   int keymask_step;

@@ -202,6 +202,10 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
         if ((keybits >> i) & 1u) racc = fmaxf(racc, v[i] * p.alpha);
     }
   } else if constexpr (EPI == EPI_EXP) {
+    // exponent clamp at 64 log2 e: never active on a valid query row (shifted rows sit near 0, shift-free entries are
+    // proven within +-64), it only keeps the garbage rows of PADDED query frames finite in the shift-free case (their
+    // norms do not enter the test, so that a clip's decision does not depend on the padding its batch gives it)
+    constexpr float kExpArgMax = 92.332482f;
     // (32768 exponentials per CTA and tile = 2048 clocks of MUFU.EX2; see SRN_EXP2_FMA above)
     const float sc = p.alpha * 1.4426950408889634f;
     if (SRN_KEY_FASTPATH && keybits == 0xffffffffu) {
@@ -213,7 +217,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
       for (int i = 0; i < 32; i += 4) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          const float x = fmaf(v[i + k], sc, -rowc);
+          const float x = fminf(fmaf(v[i + k], sc, -rowc), kExpArgMax);
           asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(v[i + k]) : "f"(x));
         }
         s0 += v[i]; s1 += v[i + 1]; s2 += v[i + 2]; s3 += v[i + 3];
@@ -226,7 +230,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           float e;
-          const float x = fmaf(v[i + k], sc, -rowc);
+          const float x = fminf(fmaf(v[i + k], sc, -rowc), kExpArgMax);
           if (SRN_EXP2_FMA && (k & 1)) e = exp2_fma(x);
           else asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x));
           v[i + k] = ((keybits >> (i + k)) & 1u) ? e : 0.f;

@@ -111,13 +111,46 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();     // everything above overlapped with the previous kernel's tail
   if (threadIdx.x == 0) SRN_STAMP(1);
-  // shift-free softmax: every score of this launch is provably within +-75 (attn_flags_kernel) - the row-max pass has
-  // nothing to do, the exp pass uses shift 0
-  bool noshift = false;
-  if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
-    noshift = p.noshift != nullptr && *reinterpret_cast<const volatile int*>(p.noshift) != 0;
-    if (EPI == EPI_ROWMAX && noshift) t_end = t_begin;
+  // Shift-free softmax, decided per (batch, head) entry z (so a clip's result never depends on what else is in the
+  // batch): s_ns[z - z0] != 0 means every score of that entry is provably within +-64 - its row-max tiles are skipped
+  // and its exp tiles run with shift 0.
+  __shared__ uint8_t s_ns[(EPI == EPI_ROWMAX || EPI == EPI_EXP) ? 1024 : 4];
+  if constexpr (EPI == EPI_ROWMAX) {
+    // The test itself (every CTA, redundantly: 16 L2 loads per entry).  qk_norm2[z * 16 + {0..7 Q, 8..15 K parts}] holds
+    // the largest squared norm of each column part of any Q / K row of entry z (atomic maxima from the QKV epilogue); by
+    // Cauchy-Schwarz |q . k| alpha <= sqrt(sum maxq * sum maxk) alpha.  Bound <= 64: exp(score) can neither overflow
+    // (e^64 = 6.2e27: a row of 10^5 keys times |v| <= 10^3 stays below 1e36 in the f32 accumulators of P~ V) nor
+    // underflow (e^-64 = 1.6e-28), and softmax is invariant to the shift.
+    for (int z = threadIdx.x; z < p.nz && z < 1024; z += blockDim.x) {
+      uint8_t ok = 0;
+      if (p.qk_norm2 != nullptr) {
+        float q = 0.f, k = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          q += p.qk_norm2[z * 16 + i];
+          k += p.qk_norm2[z * 16 + 8 + i];
+        }
+        const float bound = sqrtf(q * k) * p.alpha * 1.01f;    // (1 %: the operands are rounded after the norms were taken)
+        ok = bound <= 64.0f ? 1 : 0;                            // (NaN / Inf fail the test)
+        if (blockIdx.x == 0) p.noshift[z] = ok;                 // for the exp pass
+      }
+      s_ns[z] = ok;
+    }
+    __syncthreads();
   }
+  if constexpr (EPI == EPI_EXP) {
+    for (int z = threadIdx.x; z < p.nz && z < 1024; z += blockDim.x)
+      s_ns[z] = p.noshift != nullptr ? (uint8_t)(*reinterpret_cast<const volatile int*>(p.noshift + p.z0 + z)) : (uint8_t)0;
+    if (p.qk_norm2 != nullptr && blockIdx.x == 0 && p.z0 == 0)     // the row-max pass has read the maxima: clear them
+      for (int i = threadIdx.x; i < p.nz_norm * 16; i += blockDim.x) p.qk_norm2[i] = 0.f;
+    __syncthreads();
+  }
+  // (row-max pass: tiles of shift-free entries are skipped by all three roles; not in the A-stationary experiment,
+  //  whose slot bookkeeping assumes every tile is visited - there the pass simply runs)
+  auto skip_tile = [&](int z) -> bool {
+    if constexpr (EPI == EPI_ROWMAX && !AS) return s_ns[z - p.z0] != 0;
+    else return false;
+  };
 
   if (warp == 0) {
     if (elect_one()) {
@@ -189,6 +222,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       } else      // (the per-segment boxes of the plain path follow as the else branch)
       for (int tile = t_begin; tile < t_end; tile += t_step) {
         const int z = tile / tiles_mn + p.z0;
+        if (skip_tile(z)) continue;
         const int rem = tile % tiles_mn;
         const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
         const int n0 = ((rem % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN;     // may lie beyond N for the odd last unit (all zero)
@@ -297,6 +331,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         }
       } else      // (plain path)
       for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
+        if (skip_tile(tile / tiles_mn + p.z0)) { --it; continue; }
         const uint32_t as = it & 1;
         mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -353,8 +388,11 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         k[cc] = key < p.N ? p.keymask[(long long)bb * p.keymask_bstride + (long long)key * p.keymask_step] : (uint8_t)0;
       }
     };
+    int pre_tile = -1;        // the tile pre_s / pre_k were requested for
     for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
       const int z = tile / tiles_mn + p.z0;
+      if (skip_tile(z)) { --it; continue; }
+      const bool noshift = EPI == EPI_EXP && s_ns[z - p.z0] != 0;
       const int rem = tile % tiles_mn;
       const int mt = (rem / ntn_u) * 2 + (int)rank;     // 128-row tile index inside the batch entry
       const int m0 = mt * 128;
@@ -390,7 +428,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         // first tile of a CTA and rows with more than 16 slices wait for loads here, 16 in flight at a time
         float a = EPI == EPI_EXP ? -INFINITY : 0.f;
         for (int j0 = 0; j0 < ((EPI == EPI_EXP && noshift) ? 0 : p.stat_n); j0 += 16) {
-          if (j0 > 0 || !SRN_EPI_PREFETCH || it == 0) stat_issue(z, row, row_ok, j0, pre_s);
+          if (j0 > 0 || !SRN_EPI_PREFETCH || pre_tile != tile) stat_issue(z, row, row_ok, j0, pre_s);
 #pragma unroll
           for (int u = 0; u < 16; ++u) a = EPI == EPI_EXP ? fmaxf(a, pre_s[u]) : a + pre_s[u];
         }
@@ -401,7 +439,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       }
       uint32_t keybits[NCH / 2];
       if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
-        if (!SRN_EPI_PREFETCH || it == 0) key_issue(b, n0 + c_first * 32, pre_k);
+        if (!SRN_EPI_PREFETCH || pre_tile != tile) key_issue(b, n0 + c_first * 32, pre_k);
 #pragma unroll
         for (int cc = 0; cc < NCH / 2; ++cc) keybits[cc] = __ballot_sync(0xffffffffu, pre_k[cc] != 0);
       }
@@ -459,9 +497,10 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         if (tn < t_end) {
           const int zn = tn / tiles_mn + p.z0;
           const int remn = tn % tiles_mn;
+          pre_tile = tn;        // (a skipped tile's values are simply never used)
           if constexpr (EPI != EPI_ROWMAX) {
             const int rown = ((remn / ntn_u) * 2 + (int)rank) * 128 + q * 32 + lane;
-            if (!(EPI == EPI_EXP && noshift)) stat_issue(zn, rown, rown < p.M, 0, pre_s);
+            if (!(EPI == EPI_EXP && s_ns[zn - p.z0] != 0)) stat_issue(zn, rown, rown < p.M, 0, pre_s);
           }
           if constexpr (EPI != EPI_PV)
             key_issue(zn / p.HB, ((remn % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN + c_first * 32, pre_k);
@@ -575,6 +614,23 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
             racc = EPI == EPI_ROWMAX ? -INFINITY : 0.f;
           }
         }
+        if constexpr (EPI == EPI_QKV) {
+          // a 64-column part of a head is complete (always 64, whatever the tile shape: the test must not depend on the
+          // batch the plan was built for): largest squared norm over this warp's VALID rows -> atomic max (non-negative
+          // floats order like their bit patterns); padded frames are no keys, and see EPI_EXP for padded queries
+          if (p.qk_norm2 != nullptr && (c & 1) && nc < p.split_n) {
+            float m = (row_ok && mk != 0.f) ? gs : 0.f;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+            if (lane == 0) {
+              const int isk = nc >= (p.split_n >> 1) ? 1 : 0;
+              const int cc0 = nc - isk * (p.split_n >> 1);
+              atomicMax(reinterpret_cast<int*>(p.qk_norm2) + (b * 4 + (cc0 >> 9)) * 16 + isk * 8 + ((cc0 & 511) >> 6),
+                        __float_as_int(m));
+            }
+            gs = 0.f;
+          }
+        }
         if constexpr (EPI == EPI_STORE_F32) {
           if (p.gn_part != nullptr && (c & 1)) {   // a 64-channel group is complete
             const float s = warp_sum_f(gs), ss = warp_sum_f(gss);
@@ -583,22 +639,6 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
               red[(q * NG + (c >> 1)) * 2 + 1] = ss;
             }
             gs = 0.f; gss = 0.f;
-          }
-        }
-      }
-      if constexpr (EPI == EPI_QKV) {
-        // largest squared norm over this warp's rows of its Q | K column part -> atomic max (non-negative floats order
-        // like their bit patterns); an upper bound of every |q . k| follows from these in attn_flags_kernel
-        const int col0 = n0 + c_first * 32;
-        if (p.qk_norm2 != nullptr && nvalid > 0 && col0 < p.split_n) {
-          float m = row_ok ? gs : 0.f;
-#pragma unroll
-          for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-          if (lane == 0) {
-            const int isk = col0 >= (p.split_n >> 1) ? 1 : 0;
-            const int cc0 = col0 - isk * (p.split_n >> 1);
-            atomicMax(reinterpret_cast<int*>(p.qk_norm2) + (b * 4 + (cc0 >> 9)) * 16 + isk * 8 + ((cc0 & 511) >> 6),
-                      __float_as_int(m));
           }
         }
       }

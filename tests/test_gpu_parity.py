@@ -109,8 +109,8 @@ def test_golden_vectors_per_step_gate_tf32(name, cfm_tf32, dev):
 
 @pytest.mark.parametrize("precision,tol", [("tf32", 2e-3), ("bf16", 3e-2)])
 def test_large_logits_take_the_shifted_softmax(jitter_sd, dev, precision, tol):
-    """The shift-free softmax shortcut (attn_flags_kernel) must switch itself off when the Cauchy-Schwarz bound of the
-    scores exceeds 75: with W_q scaled by 4 the bound is ~200 and the real scores reach +-40, so exp() without the
+    """The shift-free softmax shortcut (EPI_ROWMAX prologue, gemm_mainloop.cuh) must switch itself off when the Cauchy-Schwarz bound of the
+    scores exceeds 64: with W_q scaled by 4 the bound is ~200 and the real scores reach +-40, so exp() without the
     row maximum would lose the small terms / overflow at larger scales.  Parity against the oracle on the same weights
     (diffusers Attention -> F.scaled_dot_product_attention semantics)."""
     import serenade_b200 as S
