@@ -311,6 +311,8 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
       gp.noshift = pl.noshift.template as<int>();
       gp.qk_norm2 = pl.qk_norm2.template as<float>();
       gp.nz_norm = B * H;
+      static const float nmax = getenv("SRN_NOSHIFT_MAX") ? (float)atof(getenv("SRN_NOSHIFT_MAX")) : 64.0f;
+      gp.noshift_max = nmax < 64.0f ? nmax : 64.0f;      // (tests lower it to get shifted and shift-free entries in one launch)
     }
     gp.keymask = pl.mask.template as<uint8_t>();
     gp.keymask_bstride = pl.Tp;

@@ -130,6 +130,7 @@ struct GemmParams {
   float* qk_norm2;
   int* noshift;
   int nz_norm;      // number of (batch, head) entries of qk_norm2
+  float noshift_max; // the bound below which an entry runs shift-free (64; SRN_NOSHIFT_MAX overrides it for tests)
   const uint8_t* keymask;   // (B, keys): key k of batch b takes part iff keymask[b*keymask_bstride + k*keymask_step] != 0
   int keymask_bstride;
   int keymask_step;

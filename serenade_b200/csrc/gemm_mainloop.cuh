@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           k += p.qk_norm2[z * 16 + 8 + i];
         }
         const float bound = sqrtf(q * k) * p.alpha * 1.01f;    // (1 %: the operands are rounded after the norms were taken)
-        ok = bound <= 64.0f ? 1 : 0;                            // (NaN / Inf fail the test)
+        ok = bound <= p.noshift_max ? 1 : 0;                    // (NaN / Inf fail the test)
         if (blockIdx.x == 0) p.noshift[z] = ok;                 // for the exp pass
       }
       s_ns[z] = ok;
