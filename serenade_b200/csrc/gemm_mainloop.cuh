@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   // (row-max pass: tiles of shift-free entries are skipped by all three roles; not in the A-stationary experiment,
   //  whose slot bookkeeping assumes every tile is visited - there the pass simply runs)
   auto skip_tile = [&](int z) -> bool {
-    if constexpr (EPI == EPI_ROWMAX && !AS) return s_ns[z - p.z0] != 0;
+    if constexpr (EPI == EPI_ROWMAX && !AS) return p.qk_norm2 != nullptr && s_ns[z - p.z0] != 0;     // (null beyond 1024 entries)
     else return false;
   };
 
@@ -392,7 +392,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
       const int z = tile / tiles_mn + p.z0;
       if (skip_tile(z)) { --it; continue; }
-      const bool noshift = EPI == EPI_EXP && s_ns[z - p.z0] != 0;
+      const bool noshift = EPI == EPI_EXP && p.noshift != nullptr && s_ns[z - p.z0] != 0;
       const int rem = tile % tiles_mn;
       const int mt = (rem / ntn_u) * 2 + (int)rank;     // 128-row tile index inside the batch entry
       const int m0 = mt * 128;
@@ -500,7 +500,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           pre_tile = tn;        // (a skipped tile's values are simply never used)
           if constexpr (EPI != EPI_ROWMAX) {
             const int rown = ((remn / ntn_u) * 2 + (int)rank) * 128 + q * 32 + lane;
-            if (!(EPI == EPI_EXP && s_ns[zn - p.z0] != 0)) stat_issue(zn, rown, rown < p.M, 0, pre_s);
+            if (!(EPI == EPI_EXP && p.noshift != nullptr && s_ns[zn - p.z0] != 0)) stat_issue(zn, rown, rown < p.M, 0, pre_s);
           }
           if constexpr (EPI != EPI_PV)
             key_issue(zn / p.HB, ((remn % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN + c_first * 32, pre_k);
