@@ -97,6 +97,7 @@ struct Plan {
   DevBuf qk_norm2, noshift;   // shift-free softmax test: [B * 4][16] squared-norm maxima, [1] flag (EPI_ROWMAX prologue)
   DevBuf x_state, mask, spk_in, mu_in, spk_scale, spk_bias, tsteps, dts, temb0, temb1, temb2, tb;
   DevBuf blend_mask, blend_src;
+  DevBuf rowext;      // [2][B] last unmasked frame + 1 per batch entry at full / half rate (padded-frame skipping)
   DevBuf nvalid;      // [2][B] unmasked frames per batch entry at full / half rate (valid-frame GroupNorm mode)
   int tb_steps = 0;
   std::vector<Op> ops;

@@ -106,6 +106,15 @@ void maybe_window(GemmParams& gp, const OT* ptr, int cols, int rows, long long a
   gp.win = win_mode();
   gp.win_min = mn;
 }
+// Row tiles / key tiles / K blocks that lie entirely in the padding of a ragged batch are skipped in the transformer
+// blocks (SRN_SKIP_PADDED=0: compute them like the reference does).
+inline bool skip_padded() {
+  static const bool on = [] {
+    const char* e = getenv("SRN_SKIP_PADDED");
+    return !(e != nullptr && e[0] == '0');
+  }();
+  return on;
+}
 // Shift-free softmax when every score is provably within +-64 (gemm_mainloop.cuh, EPI_ROWMAX prologue); SRN_NOSHIFT=0:
 // always run the row-max pass.
 inline bool noshift_enabled() {
@@ -233,6 +242,13 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     op.kind = OP_GEMM;
     op.name = tag + "." + nm;
     op.level = level;
+    // Padded-frame skipping (gemm.cuh: row_extent).  Every GEMM of the transformer block but ff_out: its output is the
+    // next convolution's (already masked) operand, so it writes its zeros itself.
+    const std::string n(nm);
+    if (skip_padded() && B <= 256 && n != "ff_out") {
+      op.gp.row_extent = pl.rowext.template as<int>() + (size_t)level * B;
+      op.gp.ext_keys = (n == "rowmax" || n == "expscores") ? 1 : (n == "pv" ? 2 : 0);
+    }
     pl.ops.push_back(op);
   };
   {  // fused Q|K|V projection; V is written transposed (V^T [B][2048][Sp]) so that P.V sees a K-major operand
@@ -497,6 +513,7 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
   pl.spk_bias.alloc((size_t)nres * B * C * 4);
   pl.blend_mask.alloc((size_t)B * T);
   pl.nvalid.alloc((size_t)2 * B * sizeof(int));
+  pl.rowext.alloc((size_t)2 * B * sizeof(int));
   pl.blend_src.alloc((size_t)B * cfg_.out_channels * T * 4);
 
   OT* xin = pl.xin.template as<OT>();

@@ -298,6 +298,8 @@ void Engine<OT>::prepass(Plan<OT>& pl, const std::vector<float>& ts, const std::
     launch_k(count_valid_kernel, dim3(B), dim3(256), st, mask, pl.T, pl.Tp, B, pl.nvalid.template as<int>());
     ++launches;
   }
+  launch_k(row_extent_kernel, dim3(B), dim3(256), st, mask, pl.T, pl.Tp, B, pl.rowext.template as<int>());
+  ++launches;
   const int sd = cfg_.spk_embed_dim;
   for (int r = 0; r < nres; ++r) {
     launch_k(gemv_kernel, dim3(512 / 8, B), dim3(256), st, resnets_[r].ws_w, resnets_[r].ws_b,

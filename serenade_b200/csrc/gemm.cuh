@@ -127,6 +127,13 @@ struct GemmParams {
   // EPI_ROWMAX evaluates the test per (batch, head) entry (gemm_mainloop.cuh), writes noshift[z] and skips the tiles of
   // entries whose |score| is provably <= 64; EPI_EXP runs those entries with shift 0 (and clears the maxima for the
   // next attention block).
+  // Padded-frame skipping (transformer-block GEMMs of ragged batches).  row_extent[b] = last unmasked frame of batch
+  // entry b + 1 (at this level's rate), or null.  Row tiles that start at or beyond it are skipped by all three warp
+  // roles: their outputs are only ever consumed at padded frames, which every consumer masks.  ext_keys = 1 (Q K^T
+  // passes): the N tiles are keys of the same entry and are skipped likewise; ext_keys = 2 (P~ V): the K loop and the
+  // row-sum slices stop at the extent, so no skipped (stale) P~ / V^T / statistics entry is ever read.
+  const int* row_extent;
+  int ext_keys;
   float* qk_norm2;
   int* noshift;
   int nz_norm;      // number of (batch, head) entries of qk_norm2

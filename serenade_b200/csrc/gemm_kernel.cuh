@@ -121,8 +121,10 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
       stager_put<float, 32>(st, lane, v);
       stager_flush<float>(st, lane, p, nc, row0, batch, !SRN_DIRECT_STORE);
     } else {
+      // (a select, not a product: with padded-frame skipping the rows of padded frames may hold stale data upstream,
+      //  and 0 * NaN would carry a NaN of an earlier call into the next convolution's operand)
 #pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] *= mk;
+      for (int i = 0; i < 32; ++i) v[i] = mk != 0.f ? v[i] : 0.f;
       round_op(v);
       stager_put<OT, 32>(st, lane, v);
       stager_flush<OT>(st, lane, p, nc + 32 - kOtCols, row0, batch);

@@ -151,6 +151,28 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     if constexpr (EPI == EPI_ROWMAX && !AS) return p.qk_norm2 != nullptr && s_ns[z - p.z0] != 0;     // (null beyond 1024 entries)
     else return false;
   };
+  // Padded-frame skipping: extents of the batch entries of this launch (host side guarantees <= 256 of them, no AS)
+  __shared__ int s_ext[256];
+  const bool use_ext = !AS && p.row_extent != nullptr;
+  if (use_ext) {
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+      const int bb = p.z0 / p.HB + i;
+      s_ext[i] = bb * p.HB < p.z0 + p.nz ? p.row_extent[bb] : 0;
+    }
+    __syncthreads();
+  }
+  const int b_first = p.z0 / p.HB;
+  auto tile_ext = [&](int z) -> int { return use_ext ? s_ext[z / p.HB - b_first] : 0x7fffffff; };
+  // (rem = tile index inside the entry, N fastest)
+  auto skip_pad = [&](int ext, int rem) -> bool {
+    if (!use_ext) return false;
+    if ((rem / ntn_u) * 256 >= ext) return true;                                  // the pair's 256 rows are all padding
+    return p.ext_keys == 1 && ((rem % ntn_u) * (MC ? 2 : 1)) * BN >= ext;          // ... or all its keys are
+  };
+  auto tile_nkb = [&](int ext) -> int {       // P~ V: K blocks up to the extent
+    if (use_ext && p.ext_keys == 2) { const int n = (ext + BK - 1) / BK; return n < p.nkb ? n : p.nkb; }
+    return p.nkb;
+  };
 
   if (warp == 0) {
     if (elect_one()) {
@@ -224,6 +246,9 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         const int z = tile / tiles_mn + p.z0;
         if (skip_tile(z)) continue;
         const int rem = tile % tiles_mn;
+        const int ext = tile_ext(z);
+        if (skip_pad(ext, rem)) continue;
+        const int nkb_t = tile_nkb(ext);
         const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
         const int n0 = ((rem % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN;     // may lie beyond N for the odd last unit (all zero)
         const int b = z / p.HB;
@@ -232,7 +257,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         const int b_batch = p.b_batch_mode == 0 ? 0 : (p.b_batch_mode == 1 ? b : z);
         const int b_row = n0 + (int)rank * (BN / 2) + h * p.b_hrow;
         int seg = 0, j = 0;
-        for (int kb = 0; kb < p.nkb; ++kb) {
+        for (int kb = 0; kb < nkb_t; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * CFG::kStageBytes;
           uint8_t* sb = sa + CFG::kABytes;
@@ -332,11 +357,14 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       } else      // (plain path)
       for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
         if (skip_tile(tile / tiles_mn + p.z0)) { --it; continue; }
+        const int ext = tile_ext(tile / tiles_mn + p.z0);
+        if (skip_pad(ext, tile % tiles_mn)) { --it; continue; }
+        const int nkb_t = tile_nkb(ext);
         const uint32_t as = it & 1;
         mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t tacc = tmem_base + as * BN;
-        for (int kb = 0; kb < p.nkb; ++kb) {
+        for (int kb = 0; kb < nkb_t; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           if (it == 0 && kb == 0) SRN_STAMP(2);
@@ -375,11 +403,11 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     // dependent L2 round trips (16 slice maxima four at a time, then the key mask) in front of every tile.
     float pre_s[16];          // slice statistics 0..15 of this lane's row
     uint8_t pre_k[NCH / 2];   // key-mask bytes of this lane's key in each of the warp's chunks (0 beyond N)
-    auto stat_issue = [&](int zz, int rr, bool ok, int j0, float (&s)[16]) {
+    auto stat_issue = [&](int zz, int rr, bool ok, int j0, int cnt, float (&s)[16]) {
       const float* sp = (EPI == EPI_EXP ? p.stat_max : p.stat_sum) + (long long)zz * p.stat_n * p.stat_ld + rr;
 #pragma unroll
       for (int u = 0; u < 16; ++u)
-        s[u] = (ok && j0 + u < p.stat_n) ? sp[(long long)(j0 + u) * p.stat_ld] : (EPI == EPI_EXP ? -INFINITY : 0.f);
+        s[u] = (ok && j0 + u < cnt) ? sp[(long long)(j0 + u) * p.stat_ld] : (EPI == EPI_EXP ? -INFINITY : 0.f);
     };
     auto key_issue = [&](int bb, int key0, uint8_t (&k)[NCH / 2]) {
 #pragma unroll
@@ -394,6 +422,10 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       if (skip_tile(z)) { --it; continue; }
       const bool noshift = EPI == EPI_EXP && p.noshift != nullptr && s_ns[z - p.z0] != 0;
       const int rem = tile % tiles_mn;
+      const int ext = tile_ext(z);
+      if (skip_pad(ext, rem)) { --it; continue; }
+      // statistics slices of this entry that were written / may be read: up to the extent
+      const int stat_n_t = (use_ext && p.ext_keys != 0) ? min(p.stat_n, (ext + 63) >> 6) : p.stat_n;
       const int mt = (rem / ntn_u) * 2 + (int)rank;     // 128-row tile index inside the batch entry
       const int m0 = mt * 128;
       const int n0 = ((rem % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN;
@@ -427,8 +459,8 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         // slices 0..15 of this row were requested while the previous tile's chunks were processed (pre_s); only the
         // first tile of a CTA and rows with more than 16 slices wait for loads here, 16 in flight at a time
         float a = EPI == EPI_EXP ? -INFINITY : 0.f;
-        for (int j0 = 0; j0 < ((EPI == EPI_EXP && noshift) ? 0 : p.stat_n); j0 += 16) {
-          if (j0 > 0 || !SRN_EPI_PREFETCH || pre_tile != tile) stat_issue(z, row, row_ok, j0, pre_s);
+        for (int j0 = 0; j0 < ((EPI == EPI_EXP && noshift) ? 0 : stat_n_t); j0 += 16) {
+          if (j0 > 0 || !SRN_EPI_PREFETCH || pre_tile != tile) stat_issue(z, row, row_ok, j0, stat_n_t, pre_s);
 #pragma unroll
           for (int u = 0; u < 16; ++u) a = EPI == EPI_EXP ? fmaxf(a, pre_s[u]) : a + pre_s[u];
         }
@@ -500,7 +532,9 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           pre_tile = tn;        // (a skipped tile's values are simply never used)
           if constexpr (EPI != EPI_ROWMAX) {
             const int rown = ((remn / ntn_u) * 2 + (int)rank) * 128 + q * 32 + lane;
-            if (!(EPI == EPI_EXP && p.noshift != nullptr && s_ns[zn - p.z0] != 0)) stat_issue(zn, rown, rown < p.M, 0, pre_s);
+            const int extn = tile_ext(zn);
+            const int cntn = (use_ext && p.ext_keys != 0) ? min(p.stat_n, (extn + 63) >> 6) : p.stat_n;
+            if (!(EPI == EPI_EXP && p.noshift != nullptr && s_ns[zn - p.z0] != 0)) stat_issue(zn, rown, rown < p.M, 0, cntn, pre_s);
           }
           if constexpr (EPI != EPI_PV)
             key_issue(zn / p.HB, ((remn % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN + c_first * 32, pre_k);

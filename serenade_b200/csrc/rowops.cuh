@@ -161,6 +161,36 @@ __global__ void __launch_bounds__(256) count_valid_kernel(const uint8_t* __restr
 }
 
 // ------------------------------------------------------------------------------------------------
+// Padded-frame skipping: out[b] = last unmasked frame of batch entry b + 1 at full rate, out[B + b] the same at half
+// rate (frames 0, 2, 4, ...; 0 = no valid frame).  Works for any mask, not only length prefixes.  One block per entry.
+__global__ void __launch_bounds__(256) row_extent_kernel(const uint8_t* __restrict__ mask, int T, int mask_bstride,
+                                                         int B, int* __restrict__ out) {
+  __shared__ int red[2][8];
+  pdl_launch_dependents();
+  pdl_wait();
+  const int b = blockIdx.x;
+  int full = 0, half = 0;
+  for (int t = threadIdx.x; t < T; t += 256) {
+    if (mask[(long long)b * mask_bstride + t] != 0) {
+      full = max(full, t + 1);
+      if ((t & 1) == 0) half = max(half, (t >> 1) + 1);
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    full = max(full, __shfl_xor_sync(0xffffffffu, full, o));
+    half = max(half, __shfl_xor_sync(0xffffffffu, half, o));
+  }
+  if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = full; red[1][threadIdx.x >> 5] = half; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int f = 0, h = 0;
+    for (int i = 0; i < 8; ++i) { f = max(f, red[0][i]); h = max(h, red[1][i]); }
+    out[b] = f;
+    out[B + b] = h;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Reduce the conv epilogue's per-tile partial sums to (mean, rstd) for the 8 groups of batch b.
 // part: [B][mtiles][8][2].  Result in smem stats[16] = {mean_g, rstd_g}.  Call with >= 256 threads.
 __device__ __forceinline__ void gn_reduce_stats(const float* __restrict__ part, int b, int mtiles, int T,

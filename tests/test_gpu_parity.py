@@ -128,6 +128,51 @@ def test_large_logits_take_the_shifted_softmax(jitter_sd, dev, precision, tol):
     assert e < tol
 
 
+RAGGED = [600, 280, 90]       # full rate: row tiles at 512 (clip 2) and 256, 512 (clip 3) are all padding; half rate: clip 3's tile at 256
+
+
+@pytest.mark.parametrize("precision,step_tol,final_tol", [("tf32", TF32_STEP_TOL, TF32_STEP_TOL),
+                                                          ("bf16", BF16_STEP_TOL, BF16_FINAL_TOL)])
+def test_ragged_batch_with_skipped_padding_tiles(jitter_sd, dev, precision, step_tol, final_tol):
+    """Padded-frame skipping (gemm.cuh: row_extent): row tiles, key tiles and K blocks that lie entirely in a clip's
+    padding are not computed in the transformer blocks.  The reference computes them and masks afterwards
+    (decoder.py:384-467), so the results on the full padded tensor must still agree."""
+    import serenade_b200 as S
+    from oracle import cfm_oracle as O
+    cfm = _make_cfm(jitter_sd, precision)
+    b = S.make_batch(RAGGED, n_steps=2, seed=44)
+    t = torch.tensor(0.29)
+    v = cfm.estimator(b.z.to(dev), b.mask.to(dev), b.mu.to(dev), t, b.spks.to(dev)).cpu()
+    x = cfm.solve_euler(b.z.to(dev), b.t_span.to(dev), b.mu.to(dev), b.mask.to(dev), b.spks.to(dev)).cpu()
+    with torch.inference_mode():
+        v_ref = O.estimator_forward(jitter_sd, b.z, b.mask, b.mu, t, b.spks)
+        x_ref = O.solve_euler(jitter_sd, b.z, b.t_span, b.mu, b.mask, b.spks)
+    ev, ex = rel_l2(v, v_ref), rel_l2(x, x_ref)
+    _report(f"ragged_skip_{precision}.txt", f"lengths {RAGGED} ({precision}): per-step rel_l2={ev:.3e} final rel_l2={ex:.3e}")
+    assert ev < step_tol and ex < final_tol
+    pad = ~b.mask.expand_as(x)
+    assert float(v[pad].abs().sum()) == 0.0 and torch.equal(x[pad], b.z[pad])
+
+
+def test_skipped_tiles_never_leak_stale_data(jitter_sd, dev):
+    """What the skipped tiles leave in the work buffers comes from EARLIER calls.  A solve of a ragged batch must give
+    bit-identical results on a fresh engine and on one whose buffers a full-length batch with NaN inputs has just
+    gone through (same B and T, so the same plan and buffers)."""
+    import serenade_b200 as S
+    b = S.make_batch(RAGGED, n_steps=2, seed=44)
+    args = [b.z.to(dev), b.t_span.to(dev), b.mu.to(dev), b.mask.to(dev), b.spks.to(dev)]
+    fresh = _make_cfm(jitter_sd).solve_euler(*args).cpu()
+    used = _make_cfm(jitter_sd)
+    full = S.make_batch([RAGGED[0]] * len(RAGGED), n_steps=2, seed=45)
+    z_bad = full.z.clone()
+    z_bad[1:] = float("nan")
+    poisoned = used.solve_euler(z_bad.to(dev), full.t_span.to(dev), full.mu.to(dev), full.mask.to(dev), full.spks.to(dev))
+    assert not torch.isfinite(poisoned[1:]).all()
+    again = used.solve_euler(*args).cpu()
+    assert torch.isfinite(again).all()
+    assert torch.equal(again, fresh)
+
+
 def test_solver_matches_oracle_mixed_lengths(cfm_jitter, jitter_sd, dev):
     import serenade_b200 as S
     from oracle import cfm_oracle as O
