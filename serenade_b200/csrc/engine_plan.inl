@@ -179,6 +179,10 @@ void Engine<OT>::add_resnet(Plan<OT>& pl, int ridx, int level, const OT* src0, i
     gp.out_bstride = hs;
     gp.ldo = 512;
     gp.gn_part = gn ? pl.gnpart.template as<float>() : nullptr;
+    if (skip_padded() && B <= 256) {      // padded-frame skipping: fully padded row tiles are all bias (gemm.cuh: ext_halo)
+      gp.row_extent = pl.rowext.template as<int>() + (size_t)level * B;
+      gp.ext_halo = taps == 3 ? 1 : 0;
+    }
     set_D<float>(gp, out, 512, L.T, hs, 512, B);
     op.grid = dim3(512 / op.bn, L.mtiles, B);
     op.tap = Tap{nullptr, out, 0, L.T, 512, 512, hs, B, 0};

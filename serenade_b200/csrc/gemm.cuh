@@ -134,6 +134,9 @@ struct GemmParams {
   // row-sum slices stop at the extent, so no skipped (stale) P~ / V^T / statistics entry is ever read.
   const int* row_extent;
   int ext_keys;
+  int ext_halo;     // convolutions: a row tile is skipped only if it starts >= extent + ext_halo (1 for 3 taps: the row next
+                    // to the last valid frame still sees it); a skipped tile's output is the bias, and its GroupNorm
+                    // partial sums are written from the bias (the reference's statistics span the padded frames)
   float* qk_norm2;
   int* noshift;
   int nz_norm;      // number of (batch, head) entries of qk_norm2

@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   // (rem = tile index inside the entry, N fastest)
   auto skip_pad = [&](int ext, int rem) -> bool {
     if (!use_ext) return false;
-    if ((rem / ntn_u) * 256 >= ext) return true;                                  // the pair's 256 rows are all padding
+    if ((rem / ntn_u) * 256 >= ext + p.ext_halo) return true;                     // the pair's 256 rows are all padding
     return p.ext_keys == 1 && ((rem % ntn_u) * (MC ? 2 : 1)) * BN >= ext;          // ... or all its keys are
   };
   auto tile_nkb = [&](int ext) -> int {       // P~ V: K blocks up to the extent
@@ -219,6 +219,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         for (int tile = t_begin; tile < t_end; tile += t_step) {
           const int z = tile / tiles_mn + p.z0;
           const int rem = tile % tiles_mn;
+          if (skip_pad(tile_ext(z), rem)) continue;
           const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
           const int n0 = (rem % ntn_u) * BN;
           const int b = z / p.HB;
@@ -330,6 +331,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         const int kcb = p.seg[0].nblk;
         const bool boff = (p.win & 2) != 0;
         for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
+          if (skip_pad(tile_ext(tile / tiles_mn + p.z0), tile % tiles_mn)) { --it; continue; }
           const uint32_t as = it & 1;
           mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
           tc_fence_after();
@@ -423,7 +425,29 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       const bool noshift = EPI == EPI_EXP && p.noshift != nullptr && s_ns[z - p.z0] != 0;
       const int rem = tile % tiles_mn;
       const int ext = tile_ext(z);
-      if (skip_pad(ext, rem)) { --it; continue; }
+      if (skip_pad(ext, rem)) {
+        if constexpr (EPI == EPI_STORE_F32) {
+          // a skipped convolution tile is all bias: its GroupNorm partial sums (the reference's statistics include the
+          // padded frames) are rows x sum(bias), rows x sum(bias^2) per 64-channel group; none in valid-frame mode
+          const int t = threadIdx.x - 64;
+          const int n0s = ((rem % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN;
+          if (p.gn_part != nullptr && t < NG * 2 && n0s < p.N) {
+            const int g = t >> 1, w = t & 1;
+            const int mts = (rem / ntn_u) * 2 + (int)rank;
+            int rows = p.M - mts * 128;
+            rows = rows < 0 ? 0 : (rows > 128 ? 128 : rows);
+            if (p.gn_mask != nullptr) rows = 0;
+            float sb = 0.f;
+            for (int c = 0; c < 64; ++c) {
+              const float bv = p.bias != nullptr ? p.bias[n0s + g * 64 + c] : 0.f;
+              sb += w ? bv * bv : bv;
+            }
+            p.gn_part[(((long long)(z / p.HB) * (2 * p.ntm) + mts) * 8 + (n0s >> 6) + g) * 2 + w] = sb * (float)rows;
+          }
+        }
+        --it;
+        continue;
+      }
       // statistics slices of this entry that were written / may be read: up to the extent
       const int stat_n_t = (use_ext && p.ext_keys != 0) ? min(p.stat_n, (ext + 63) >> 6) : p.stat_n;
       const int mt = (rem / ntn_u) * 2 + (int)rank;     // 128-row tile index inside the batch entry

@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(256, 4) gn_apply_kernel(const float* __restric
     float v[8];
     load8(y + off, v);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = (mish_f(v[i] * ga[i] + be[i]) + tb[i]) * m;
+    for (int i = 0; i < 8; ++i) v[i] = m != 0.f ? mish_f(v[i] * ga[i] + be[i]) + tb[i] : 0.f;     // (select: y may be stale at skipped padded tiles)
     store8_op(out + off, v);
   }
   ROW_STAMP(4);
