@@ -14,6 +14,10 @@ static bool pdl_enabled() {
   return on;
 }
 
+// Set before a launch_k call that must NOT start before its predecessor has completed (no programmatic edge): used once
+// per solve, right after row_extent_kernel, so that every later kernel may read the extents before its dependency wait.
+static thread_local bool g_next_launch_serialised = false;
+
 template <typename... KArgs, typename... Args>
 static void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args) {
   cudaLaunchConfig_t cfg;
@@ -25,7 +29,8 @@ static void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t
   attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr.val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = &attr;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cfg.numAttrs = (pdl_enabled() && !g_next_launch_serialised) ? 1 : 0;
+  g_next_launch_serialised = false;
   SRN_CUDA(cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...));
 }
 
@@ -300,6 +305,7 @@ void Engine<OT>::prepass(Plan<OT>& pl, const std::vector<float>& ts, const std::
   }
   launch_k(row_extent_kernel, dim3(B), dim3(256), st, mask, pl.T, pl.Tp, B, pl.rowext.template as<int>());
   ++launches;
+  g_next_launch_serialised = true;      // (the next launch_k below: a full dependency, see gemm_mainloop.cuh: s_ext)
   const int sd = cfg_.spk_embed_dim;
   for (int r = 0; r < nres; ++r) {
     launch_k(gemv_kernel, dim3(512 / 8, B), dim3(256), st, resnets_[r].ws_w, resnets_[r].ws_b,

@@ -104,6 +104,18 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     }
     fence_barrier_init();
   }
+  // Padded-frame skipping: the extents of this launch's batch entries -> shared memory, BEFORE the dependency wait.
+  // That is safe although an earlier kernel of the same stream wrote them: the launch right after row_extent_kernel is
+  // a fully serialised one (engine_run.inl: prepass), so no later kernel can even start before the extents are final.
+  // (made visible to all warps by the cluster barrier below; host side guarantees <= 256 entries)
+  __shared__ int s_ext[256];
+  const bool use_ext = !AS && p.row_extent != nullptr;
+  if (use_ext) {
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+      const int bb = p.z0 / p.HB + i;
+      s_ext[i] = bb * p.HB < p.z0 + p.nz ? __ldcg(p.row_extent + bb) : 0;
+    }
+  }
   if (warp == 2) tmem_alloc_2sm<CFG::kTmemCols>(tmem_slot);
   tc_fence_before();
   cluster_sync_all();
@@ -152,22 +164,37 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     else return false;
   };
   // Padded-frame skipping: extents of the batch entries of this launch (host side guarantees <= 256 of them, no AS)
-  __shared__ int s_ext[256];
-  const bool use_ext = !AS && p.row_extent != nullptr;
-  if (use_ext) {
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
-      const int bb = p.z0 / p.HB + i;
-      s_ext[i] = bb * p.HB < p.z0 + p.nz ? p.row_extent[bb] : 0;
-    }
-    __syncthreads();
-  }
   const int b_first = p.z0 / p.HB;
-  auto tile_ext = [&](int z) -> int { return use_ext ? s_ext[z / p.HB - b_first] : 0x7fffffff; };
-  // (rem = tile index inside the entry, N fastest)
-  auto skip_pad = [&](int ext, int rem) -> bool {
+  // (b = batch entry, mi / ni = row / column tile inside the entry: the callers have them anyway - integer divisions
+  //  by run-time values are ~150-clock dependent chains, and the epilogue warps' per-tile chain is what bounds the
+  //  K = 512 GEMMs)
+  auto tile_ext = [&](int b) -> int { return use_ext ? s_ext[b - b_first] : 0x7fffffff; };
+  auto skip_pad = [&](int ext, int mi, int ni) -> bool {
     if (!use_ext) return false;
-    if ((rem / ntn_u) * 256 >= ext + p.ext_halo) return true;                     // the pair's 256 rows are all padding
-    return p.ext_keys == 1 && ((rem % ntn_u) * (MC ? 2 : 1)) * BN >= ext;          // ... or all its keys are
+    if (mi * 256 >= ext + p.ext_halo) return true;                                // the pair's 256 rows are all padding
+    return p.ext_keys == 1 && (ni * (MC ? 2 : 1)) * BN >= ext;                     // ... or all its keys are
+  };
+  // Tile coordinates kept incrementally (tile -> tile + t_step) for the MMA-issuing lane: three run-time integer
+  // divisions per tile in front of its MMAs cost the mainloop-bound launches ~450 clocks per tile.
+  struct TileCoord {
+    int z, mi, ni, a, c, d, ntn, ntm;
+    __device__ __forceinline__ void init(int tile, int step, int ntn_, int ntm_) {
+      ntn = ntn_; ntm = ntm_;
+      const int tmn = ntn * ntm;
+      z = tile / tmn;
+      const int rem = tile - z * tmn;
+      mi = rem / ntn; ni = rem - mi * ntn;
+      a = step / tmn;
+      const int r1 = step - a * tmn;
+      c = r1 / ntn; d = r1 - c * ntn;
+    }
+    __device__ __forceinline__ void advance() {
+      ni += d;
+      if (ni >= ntn) { ni -= ntn; ++mi; }
+      mi += c;
+      if (mi >= ntm) { mi -= ntm; ++z; }
+      z += a;
+    }
   };
   auto tile_nkb = [&](int ext) -> int {       // P~ V: K blocks up to the extent
     if (use_ext && p.ext_keys == 2) { const int n = (ext + BK - 1) / BK; return n < p.nkb ? n : p.nkb; }
@@ -219,10 +246,11 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         for (int tile = t_begin; tile < t_end; tile += t_step) {
           const int z = tile / tiles_mn + p.z0;
           const int rem = tile % tiles_mn;
-          if (skip_pad(tile_ext(z), rem)) continue;
-          const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
-          const int n0 = (rem % ntn_u) * BN;
+          const int mi = rem / ntn_u, ni = rem - mi * ntn_u;
           const int b = z / p.HB;
+          if (skip_pad(tile_ext(b), mi, ni)) continue;
+          const int m0 = mi * 256 + (int)rank * 128;
+          const int n0 = ni * BN;
           const int h = z - b * p.HB;
           const int a_batch = p.a_zbatch ? z : b;
           const int b_batch = p.b_batch_mode == 0 ? 0 : (p.b_batch_mode == 1 ? b : z);
@@ -247,12 +275,13 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         const int z = tile / tiles_mn + p.z0;
         if (skip_tile(z)) continue;
         const int rem = tile % tiles_mn;
-        const int ext = tile_ext(z);
-        if (skip_pad(ext, rem)) continue;
-        const int nkb_t = tile_nkb(ext);
-        const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
-        const int n0 = ((rem % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN;     // may lie beyond N for the odd last unit (all zero)
+        const int mi = rem / ntn_u, ni = rem - mi * ntn_u;
         const int b = z / p.HB;
+        const int ext = tile_ext(b);
+        if (skip_pad(ext, mi, ni)) continue;
+        const int nkb_t = tile_nkb(ext);
+        const int m0 = mi * 256 + (int)rank * 128;
+        const int n0 = (ni * (MC ? 2 : 1) + (int)pj) * BN;     // may lie beyond N for the odd last unit (all zero)
         const int h = z - b * p.HB;
         const int a_batch = p.a_zbatch ? z : b;
         const int b_batch = p.b_batch_mode == 0 ? 0 : (p.b_batch_mode == 1 ? b : z);
@@ -330,8 +359,14 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         uint32_t wa = 0, wap = 0, wb = 0, wbp = 0;
         const int kcb = p.seg[0].nblk;
         const bool boff = (p.win & 2) != 0;
-        for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
-          if (skip_pad(tile_ext(tile / tiles_mn + p.z0), tile % tiles_mn)) { --it; continue; }
+        TileCoord tc;
+        tc.init(t_begin, t_step, ntn_u, p.ntm);
+        int cur_z = -1, cur_ext = 0x7fffffff;
+        for (int tile = t_begin; tile < t_end; tile += t_step, ++it, tc.advance()) {
+          if (use_ext) {
+            if (tc.z != cur_z) { cur_z = tc.z; cur_ext = tile_ext((tc.z + p.z0) / p.HB); }
+            if (skip_pad(cur_ext, tc.mi, tc.ni)) { --it; continue; }
+          }
           const uint32_t as = it & 1;
           mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
           tc_fence_after();
@@ -356,12 +391,18 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           }
           tc_commit_mask(&tfull_bar[as], (uint16_t)(0x3u << leader));
         }
-      } else      // (plain path)
-      for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
-        if (skip_tile(tile / tiles_mn + p.z0)) { --it; continue; }
-        const int ext = tile_ext(tile / tiles_mn + p.z0);
-        if (skip_pad(ext, tile % tiles_mn)) { --it; continue; }
-        const int nkb_t = tile_nkb(ext);
+      } else {    // (plain path)
+      TileCoord tc;
+      tc.init(t_begin, t_step, ntn_u, p.ntm);
+      int cur_z = -1, cur_ext = 0x7fffffff;
+      for (int tile = t_begin; tile < t_end; tile += t_step, ++it, tc.advance()) {
+        if (skip_tile(tc.z + p.z0)) { --it; continue; }
+        int nkb_t = p.nkb;
+        if (use_ext) {
+          if (tc.z != cur_z) { cur_z = tc.z; cur_ext = tile_ext((tc.z + p.z0) / p.HB); }
+          if (skip_pad(cur_ext, tc.mi, tc.ni)) { --it; continue; }
+          nkb_t = tile_nkb(cur_ext);
+        }
         const uint32_t as = it & 1;
         mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -383,6 +424,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         }
         tc_commit_mask(&tfull_bar[as], (uint16_t)(0x3u << leader));          // both CTAs' epilogues may drain their half
         SRN_STAMP(3);
+      }
       }
     }
   } else {
@@ -424,16 +466,19 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       if (skip_tile(z)) { --it; continue; }
       const bool noshift = EPI == EPI_EXP && p.noshift != nullptr && s_ns[z - p.z0] != 0;
       const int rem = tile % tiles_mn;
-      const int ext = tile_ext(z);
-      if (skip_pad(ext, rem)) {
+      const int mi = rem / ntn_u, ni = rem - mi * ntn_u;
+      const int b = z / p.HB;
+      const int h = z - b * p.HB;
+      const int ext = tile_ext(b);
+      if (skip_pad(ext, mi, ni)) {
         if constexpr (EPI == EPI_STORE_F32) {
           // a skipped convolution tile is all bias: its GroupNorm partial sums (the reference's statistics include the
           // padded frames) are rows x sum(bias), rows x sum(bias^2) per 64-channel group; none in valid-frame mode
           const int t = threadIdx.x - 64;
-          const int n0s = ((rem % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN;
+          const int n0s = (ni * (MC ? 2 : 1) + (int)pj) * BN;
           if (p.gn_part != nullptr && t < NG * 2 && n0s < p.N) {
             const int g = t >> 1, w = t & 1;
-            const int mts = (rem / ntn_u) * 2 + (int)rank;
+            const int mts = mi * 2 + (int)rank;
             int rows = p.M - mts * 128;
             rows = rows < 0 ? 0 : (rows > 128 ? 128 : rows);
             if (p.gn_mask != nullptr) rows = 0;
@@ -442,7 +487,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
               const float bv = p.bias != nullptr ? p.bias[n0s + g * 64 + c] : 0.f;
               sb += w ? bv * bv : bv;
             }
-            p.gn_part[(((long long)(z / p.HB) * (2 * p.ntm) + mts) * 8 + (n0s >> 6) + g) * 2 + w] = sb * (float)rows;
+            p.gn_part[(((long long)b * (2 * p.ntm) + mts) * 8 + (n0s >> 6) + g) * 2 + w] = sb * (float)rows;
           }
         }
         --it;
@@ -450,11 +495,9 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       }
       // statistics slices of this entry that were written / may be read: up to the extent
       const int stat_n_t = (use_ext && p.ext_keys != 0) ? min(p.stat_n, (ext + 63) >> 6) : p.stat_n;
-      const int mt = (rem / ntn_u) * 2 + (int)rank;     // 128-row tile index inside the batch entry
+      const int mt = mi * 2 + (int)rank;     // 128-row tile index inside the batch entry
       const int m0 = mt * 128;
-      const int n0 = ((rem % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN;
-      const int b = z / p.HB;
-      const int h = z - b * p.HB;
+      const int n0 = (ni * (MC ? 2 : 1) + (int)pj) * BN;
       const uint32_t as = it & 1;
       const int row0 = m0 + q * 32;
       const int row = row0 + lane;
@@ -556,7 +599,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           pre_tile = tn;        // (a skipped tile's values are simply never used)
           if constexpr (EPI != EPI_ROWMAX) {
             const int rown = ((remn / ntn_u) * 2 + (int)rank) * 128 + q * 32 + lane;
-            const int extn = tile_ext(zn);
+            const int extn = tile_ext(zn / p.HB);
             const int cntn = (use_ext && p.ext_keys != 0) ? min(p.stat_n, (extn + 63) >> 6) : p.stat_n;
             if (!(EPI == EPI_EXP && p.noshift != nullptr && s_ns[zn - p.z0] != 0)) stat_issue(zn, rown, rown < p.M, 0, cntn, pre_s);
           }
