@@ -120,6 +120,15 @@ int srn_set_use_graph(SrnHandle* h, int32_t enable);
  *     (bin/ssc_decode.py:346-378, batch 1, T = its own length): what a length-bucketed batched decode needs. */
 int srn_set_gn_valid_only(SrnHandle* h, int32_t enable);
 
+/* Run-time options (take effect at the next call; a cached CUDA graph is re-captured when one changes):
+ *   "noshift"  1 (default): attention entries whose scores are provably within +-64 (Cauchy-Schwarz on the Q / K row
+ *              norms) skip the row-max pass and run softmax without a shift; 0: every entry takes the row-max pass.
+ * Unknown names fail. */
+int srn_set_option(SrnHandle* h, const char* name, int32_t value);
+/* Which softmax path the attention blocks of the most recent srn_solve_euler* / srn_estimator_forward* call took:
+ * out[0] = (batch, head, block, step) entries that ran shift-free, out[1] = all entries.  Synchronises the device. */
+int srn_softmax_stats(SrnHandle* h, int64_t* out2);
+
 /* Test hooks: when enabled, every named intermediate of the next forward is kept (as f32, channels-last
  * (B, rows, cols)) and can be fetched by name.  srn_debug_fetch returns the element count via *n_out
  * and copies min(capacity, n) values. */
@@ -128,7 +137,8 @@ int srn_debug_fetch(SrnHandle* h, const char* name, float* host_out, int64_t cap
                     int32_t* rows_out, int32_t* cols_out);
 
 /* Per-op CUDA-event timing of one estimator forward at (B, T) on synthetic contents: writes a JSON array
- * [{"op": name, "kernel": kind, "ms": avg, "flops": algorithmic flops, "bytes": algorithmic bytes}, ...]. */
+ * [{"op": name, "kernel": kind, "ms": avg, "flops": algorithmic flops (no channel padding, nothing for the
+ * row-max pass), "flops_issued": what the tensor cores ran, "bytes": algorithmic bytes}, ...]. */
 int srn_profile_ops(SrnHandle* h, int32_t B, int32_t T, int32_t reps, char* json_out, int64_t capacity);
 
 #ifdef __cplusplus

@@ -18,7 +18,7 @@ EXPORTED_SYMBOLS = [
     "srn_estimator_forward", "srn_solve_euler", "srn_solve_euler_host", "srn_launch_count", "srn_set_use_graph",
     "srn_debug_enable", "srn_debug_fetch", "srn_profile_ops", "srn_content_encode", "srn_style_encode",
     "srn_set_gn_valid_only", "srn_vocoder_set_dilations", "srn_vocoder_hop", "srn_vocoder_decode",
-    "srn_estimator_forward_t", "srn_cfm_loss",
+    "srn_estimator_forward_t", "srn_cfm_loss", "srn_set_option", "srn_softmax_stats",
 ]
 
 PRECISION_BF16 = 0
@@ -61,6 +61,8 @@ def load_library() -> C.CDLL:
     lib.srn_launch_count.argtypes = [vp]
     lib.srn_set_use_graph.argtypes = [vp, i32]
     lib.srn_set_gn_valid_only.argtypes = [vp, i32]
+    lib.srn_set_option.argtypes = [vp, C.c_char_p, i32]
+    lib.srn_softmax_stats.argtypes = [vp, C.POINTER(i64)]
     lib.srn_vocoder_set_dilations.argtypes = [vp, C.POINTER(C.c_int32), i32]
     lib.srn_vocoder_hop.argtypes = [vp, C.POINTER(C.c_int32)]
     lib.srn_vocoder_decode.argtypes = [vp, f32p, f32p, f32p, i32, i32, f32p, vp]

@@ -57,10 +57,21 @@ CUtensorMap make_tmap_3d(const void* base, int elem_bytes, uint64_t inner, uint6
   }                                                \
   return 0;
 
-static void check_handle(SrnHandle* h) {
-  if (h == nullptr || !h->eng) srn::fail("null SrnHandle");
-  SRN_CUDA(cudaSetDevice(h->device));
-}
+// Every entry point runs on the handle's device and leaves the caller's current device as it found it.
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) SRN_CUDA(cudaSetDevice(dev));
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+#define check_handle(h)                                              \
+  if ((h) == nullptr || !(h)->eng) srn::fail("null SrnHandle");      \
+  DeviceGuard srn_device_guard((h)->device)
 
 extern "C" {
 #define SRN_EXPORT __attribute__((visibility("default")))
@@ -91,7 +102,7 @@ SRN_EXPORT int srn_create(const SrnConfig* cfg, SrnHandle** out) {
 SRN_EXPORT int srn_destroy(SrnHandle* h) {
   SRN_API_BEGIN
   if (h != nullptr) {
-    cudaSetDevice(h->device);
+    DeviceGuard guard(h->device);
     delete h;
   }
   SRN_API_END
@@ -225,6 +236,23 @@ SRN_EXPORT int srn_set_gn_valid_only(SrnHandle* h, int32_t enable) {
   SRN_API_BEGIN
   check_handle(h);
   h->eng->gn_valid_only = enable != 0;
+  SRN_API_END
+}
+
+SRN_EXPORT int srn_set_option(SrnHandle* h, const char* name, int32_t value) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (name == nullptr) srn::fail("srn_set_option: null name");
+  if (strcmp(name, "noshift") == 0) h->eng->noshift = value != 0;
+  else srn::fail("srn_set_option: unknown option '%s'", name);
+  SRN_API_END
+}
+
+SRN_EXPORT int srn_softmax_stats(SrnHandle* h, int64_t* out2) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (out2 == nullptr) srn::fail("srn_softmax_stats: null pointer");
+  h->eng->softmax_stats(out2);
   SRN_API_END
 }
 

@@ -9,27 +9,17 @@
 
 namespace srn {
 
-template <typename OT, int BN, int EPI>
+template <typename OT, int BN, int EPI, int EW = 8>
 static void configure_one() {
-  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                GemmCfg<BN>::kSmemBytes));
-  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
-  if constexpr (!std::is_same<OT, float>::value && !SRN_MC &&
-                (EPI == EPI_QKV || EPI == EPI_GEGLU || EPI == EPI_ROWMAX || EPI == EPI_EXP)) {
-    SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  GemmCfg<BN, true>::kSmemBytes));
-    SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, false, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
-  }
-#if SRN_MC
-  if (BN == 256)
-    SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, 256, EPI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  GemmCfg<256>::kSmemBytes));
-#endif
+  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                GemmCfg<BN, EW>::kSmemBytes));
+  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, EW>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
 }
 
 template <typename OT, int BN>
 static void configure_bn() {
   configure_one<OT, BN, EPI_STORE_F32>();
+  configure_one<OT, BN, EPI_STORE_GN>();
   configure_one<OT, BN, EPI_STORE_OT>();
   configure_one<OT, BN, EPI_RESID_F32>();
   configure_one<OT, BN, EPI_RESID_OT>();
@@ -46,8 +36,11 @@ template <typename OT>
 static void configure_kernels() {
   configure_bn<OT, 128>();
   configure_bn<OT, 256>();
-  configure_one<Fp8, 128, EPI_ROWMAX>();
-  configure_one<Fp8, 256, EPI_ROWMAX>();
+  // sixteen epilogue warps (engine_run.inl: launch_gemm_ew)
+  configure_one<OT, 256, EPI_QKV, 16>();
+  configure_one<OT, 256, EPI_ROWMAX, 16>();
+  configure_one<OT, 256, EPI_EXP, 16>();
+  configure_one<OT, 256, EPI_PV, 16>();
 }
 
 std::unique_ptr<EngineBase> make_engine(const SrnConfig& cfg) {

@@ -44,6 +44,8 @@ class EngineBase {
   virtual void vocoder_decode(const float* mel, const float* scale, const float* shift, int B, int T, float* wave,
                               cudaStream_t st) = 0;
   virtual int vocoder_hop() const = 0;
+  virtual void softmax_stats(int64_t* out2) = 0;
+  bool noshift = true;            // srn_set_option("noshift"): shift-free softmax entries allowed
   std::vector<int> voc_dilations = {1, 3, 5};     // HiFiGANResidualBlock dilations (not recoverable from the weights)
   int64_t launches = 0;
   bool use_graph = true;

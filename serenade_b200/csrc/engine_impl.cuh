@@ -64,12 +64,13 @@ struct Op {
   int bn = 128;
   dim3 grid;
   bool is_euler = false;
+  double alg_scale = 1.0;       // algorithmic / issued FLOPs of this op (channel padding; 0 for the row-max pass)
   // row kernels
-  const float* y = nullptr;
+  const void* y = nullptr;      // conv output in operand width (EPI_STORE_GN)
   const float* part = nullptr;
   const float* gamma = nullptr;
   const float* beta = nullptr;
-  const float* res = nullptr;
+  const void* res = nullptr;    // res_conv output, operand width
   const float* ln_g = nullptr;
   const float* ln_b = nullptr;
   float* hres = nullptr;
@@ -78,6 +79,7 @@ struct Op {
   int use_tbias = 0;
   int level = 0;
   Tap tap;
+  Tap tap2;                     // grouped launches: the second output (debug taps)
 };
 
 struct Level {
@@ -93,8 +95,8 @@ struct Plan {
   int B = 0, T = 0, Tp = 0;
   Level lv[2];
   DevBuf xin, y, r, gnpart, a1, hres, ln, qk, vt, smax, ssum, P, ao, gg, hid0, hid1, hc, cv;
-  DevBuf qk8;      // e4m3 copy of Q | K (row-max pass operands)
-  DevBuf qk_norm2, noshift;   // shift-free softmax test: [B * 4][16] squared-norm maxima, [1] flag (EPI_ROWMAX prologue)
+  DevBuf qk_norm2, noshift;   // shift-free softmax test: [B * 4][16] squared-norm maxima, [B * 4] flags (EPI_ROWMAX prologue)
+  DevBuf ns_count;            // [2] int64: attention entries that ran shift-free / all entries, since the call began
   DevBuf x_state, mask, spk_in, mu_in, spk_scale, spk_bias, tsteps, dts, temb0, temb1, temb2, tb;
   DevBuf blend_mask, blend_src;
   DevBuf rowext;      // [2][B] last unmasked frame + 1 per batch entry at full / half rate (padded-frame skipping)
@@ -107,6 +109,8 @@ struct Plan {
   int graph_steps = 0;
   bool graph_blend = false;
   bool graph_gn_valid = false;
+  bool graph_noshift = true;
+  std::vector<float> staged_ts;      // the t_span whose (t, dt) tables are on the device (no re-upload, no host sync)
   int64_t graph_nodes = 0;
   ~Plan() {
     if (graph) cudaGraphExecDestroy(graph);
@@ -142,6 +146,7 @@ class Engine : public EngineBase {
   void vocoder_decode(const float* mel, const float* scale, const float* shift, int B, int T, float* wave,
                       cudaStream_t st) override;
   int vocoder_hop() const override { return voc_.present ? voc_.hop : 0; }
+  void softmax_stats(int64_t* out2) override;
 
  private:
   static constexpr int BK = OpTraits<OT>::kBK;
@@ -217,7 +222,9 @@ class Engine : public EngineBase {
   void pack_decoder(size_t n_est);
   void front_gemm(GemmParams& gp, const OT* W, int N, int K, const float* bias, int M, int nbatch, bool f32_out,
                   void* out, long long out_bstride, int ldo, float slope, cudaStream_t st);
+  static constexpr size_t kMaxPlans = 6;
   std::list<Plan<OT>> plans_;
+  Plan<OT>* last_plan_ = nullptr;   // plan of the most recent estimator / solve call (softmax_stats)
   bool blend_active_ = false;
   int tb_bstride_ = 0;          // 512 while an estimator call with per-clip times runs (estimator_forward_t)
   DevBuf loss_v_, loss_part_, loss_lmask_;

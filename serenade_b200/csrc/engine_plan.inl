@@ -7,9 +7,16 @@ static inline int round_up(int a, int b) { return cdiv(a, b) * b; }
 template <typename OT>
 Plan<OT>& Engine<OT>::get_plan(int B, int T) {
   if (!finalized_) fail("weights not finalized: call srn_finalize_weights first");
-  for (auto& p : plans_)
-    if (p.B == B && p.T == T) return p;
-  if (plans_.size() >= 4) plans_.pop_front();   // bounded cache, oldest first
+  // bounded cache, least recently used first (a hit moves the plan to the back)
+  for (auto it = plans_.begin(); it != plans_.end(); ++it)
+    if (it->B == B && it->T == T) {
+      if (std::next(it) != plans_.end()) plans_.splice(plans_.end(), plans_, it);
+      return plans_.back();
+    }
+  if (plans_.size() >= kMaxPlans) {
+    if (last_plan_ == &plans_.front()) last_plan_ = nullptr;
+    plans_.pop_front();
+  }
   plans_.emplace_back();
   Plan<OT>& pl = plans_.back();
   pl.B = B;
@@ -36,17 +43,9 @@ GemmParams Engine<OT>::base_gemm(const Plan<OT>& pl, int level) const {
 }
 
 namespace {
-// SRN_ROWMAX_FP8=0 keeps the row-max pass in operand precision (A/B switch; default on)
-inline bool rowmax_fp8() {
-  static const bool on = [] {
-    const char* e = getenv("SRN_ROWMAX_FP8");
-    return !(e != nullptr && e[0] == '0');
-  }();
-  return on;
-}
 template <typename OT>
 void set_A(GemmParams& gp, int idx, const OT* ptr, int cols, int rows, long long alloc_rows, int ld, int nbatch) {
-  gp.mapA[idx] = make_tmap_3d(ptr, sizeof(OT), cols, rows, nbatch, ld, (uint64_t)alloc_rows * ld, OpTraits<OT>::kBK, SRN_MC ? 64 : 128);
+  gp.mapA[idx] = make_tmap_3d(ptr, sizeof(OT), cols, rows, nbatch, ld, (uint64_t)alloc_rows * ld, OpTraits<OT>::kBK, 128);
   if (idx == 0) gp.mapA[1] = gp.mapA[0];
 }
 // Call after every add_seg of the op.  TF32 mode: the packed weight rows are [hi | lo] (engine_weights.inl: up_w),
@@ -75,6 +74,41 @@ inline void add_seg(GemmParams& gp, int src, int col0, int shift, int nblk) {
   if (gp.nseg >= 24) fail("too many K segments");
   gp.seg[gp.nseg++] = KSeg{src, col0, shift, nblk};
   gp.nkb += nblk;
+}
+// Tile group 1 (gemm.cuh: GemmParams::grp_*): a second GEMM over the same A tensors in the same launch.  Call begin_group1
+// after set_B_weight of group 0 (the TF32-class mode has doubled its segments by then), then add_seg_g1 per segment, then
+// set_B2_weight.  ntn0 = number of N tiles of group 0.
+inline void begin_group1(GemmParams& gp, int ntn0) {
+  gp.grp_ntn0 = ntn0;
+  gp.grp_seg0 = gp.nseg;
+  gp.grp_nseg = 0;
+  gp.grp_nkb = 0;
+}
+inline void add_seg_g1(GemmParams& gp, int src, int col0, int shift, int nblk) {
+  if (gp.grp_seg0 + gp.grp_nseg >= 24) fail("too many K segments");
+  gp.seg[gp.grp_seg0 + gp.grp_nseg++] = KSeg{src, col0, shift, nblk};
+  gp.grp_nkb += nblk;
+}
+template <typename OT>
+void set_B2_weight(GemmParams& gp, const OT* W, int N, int K, int bn) {
+  if (gp.grp_nkb * OpTraits<OT>::kBK != K) fail("set_B2_weight: K = %d but the A segments cover %d", K, gp.grp_nkb * OpTraits<OT>::kBK);
+  const int Kw = OpTraits<OT>::kTF32 ? 2 * K : K;
+  gp.mapB2 = make_tmap_3d(W, sizeof(OT), Kw, N, 1, Kw, (uint64_t)N * Kw, OpTraits<OT>::kBK, bn / 2);
+  if (OpTraits<OT>::kTF32) {
+    const int n = gp.grp_nseg;
+    if (gp.grp_seg0 + 2 * n > 24) fail("too many K segments");
+    for (int i = 0; i < n; ++i) gp.seg[gp.grp_seg0 + n + i] = gp.seg[gp.grp_seg0 + i];
+    gp.grp_nseg = 2 * n;
+    gp.grp_nkb *= 2;
+  }
+}
+// SRN_GROUPED=0: one launch per GEMM as in round 1 (A/B switch)
+inline bool grouped_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("SRN_GROUPED");
+    return !(e != nullptr && e[0] == '0');
+  }();
+  return on;
 }
 // Window mode (gemm.cuh: GemmParams::win) for a convolution whose K segments are row shifts of ONE operand with the
 // weights packed [tap][channel]: one kWinRows-row A window per K block then serves every tap.  Call after the
@@ -124,17 +158,6 @@ inline bool noshift_enabled() {
   }();
   return on;
 }
-// Attention passes in (batch, head) slices whose P~ stays in the L2: opt-in experiment (SRN_ATTN_SLICES=1).  Measured
-// on one box at C2 (profiles/r01_ab_attn_slices.txt): two slices of 65 MB instead of one 131 MB P~ cost more in the
-// extra launches than the L2 residency returns (exp 2 x 37 vs 65 us, P~ V 2 x 41 vs 67 us, solve 24.2 - 24.6 vs 23.6 ms).
-constexpr size_t kPSliceBytes = 68u << 20;
-inline bool attn_slices() {
-  static const bool on = [] {
-    const char* e = getenv("SRN_ATTN_SLICES");
-    return e != nullptr && e[0] == '1';
-  }();
-  return on;
-}
 // row_tiles = number of 256-row pair tiles; one CTA pair per SM pair (74 on a B200)
 inline int pick_bn(int N, long long row_tiles) {
   const long long nt256 = (N + 255) / 256, nt128 = (N + 127) / 128;
@@ -155,8 +178,10 @@ void Engine<OT>::add_resnet(Plan<OT>& pl, int ridx, int level, const OT* src0, i
   const int B = pl.B;
   const long long hs = (long long)L.R * 512;
   const long long tiles = (long long)L.mtiles * B;
+  // conv (taps = 3 or 1) of the resnet input; `res` != null: the 1x1 res_conv rides along as tile group 1 of the same
+  // launch (same A tensors, centre-tap segments only, its own weights / bias / output)
   auto conv_op = [&](const char* nm, const OT* a0, int ac0, int ald0, const OT* a1, int ac1, const OT* W, int taps,
-                     const float* bias, float* out, bool gn) {
+                     const float* bias, OT* out, bool gn, bool with_res) {
     Op op;
     op.kind = OP_GEMM;
     op.name = tag + "." + nm;
@@ -169,11 +194,11 @@ void Engine<OT>::add_resnet(Plan<OT>& pl, int ridx, int level, const OT* src0, i
       add_seg(gp, 0, 0, shift, ac0 / BK);
       if (a1 != nullptr) add_seg(gp, 1, 0, shift, ac1 / BK);
     }
-    if (a1 == nullptr) maybe_window<OT>(gp, a0, ac0, L.T, L.R, ald0, B);
-    op.bn = pick_bn(512, tiles);
+    if (a1 == nullptr && !with_res) maybe_window<OT>(gp, a0, ac0, L.T, L.R, ald0, B);
+    op.bn = pick_bn(with_res ? 1024 : 512, tiles);
     set_B_weight<OT>(gp, W, 512, taps * (ac0 + ac1), op.bn);
     gp.N = 512;
-    gp.epi = EPI_STORE_F32;
+    gp.epi = EPI_STORE_GN;
     gp.bias = bias;
     gp.out = out;
     gp.out_bstride = hs;
@@ -183,20 +208,38 @@ void Engine<OT>::add_resnet(Plan<OT>& pl, int ridx, int level, const OT* src0, i
       gp.row_extent = pl.rowext.template as<int>() + (size_t)level * B;
       gp.ext_halo = taps == 3 ? 1 : 0;
     }
-    set_D<float>(gp, out, 512, L.T, hs, 512, B);
-    op.grid = dim3(512 / op.bn, L.mtiles, B);
-    op.tap = Tap{nullptr, out, 0, L.T, 512, 512, hs, B, 0};
+    set_D<OT>(gp, out, 512, L.T, hs, 512, B);
+    int ntn = 512 / op.bn;
+    if (with_res) {
+      begin_group1(gp, ntn);
+      add_seg_g1(gp, 0, 0, 0, ac0 / BK);
+      if (a1 != nullptr) add_seg_g1(gp, 1, 0, 0, ac1 / BK);
+      set_B2_weight<OT>(gp, w.wr, 512, ac0 + ac1, op.bn);
+      gp.bias2 = w.br;
+      gp.mapD2 = make_tmap_3d(pl.r.template as<OT>(), sizeof(OT), 512, L.T, B, 512, (uint64_t)hs, 128 / sizeof(OT), 32);
+      ntn *= 2;
+    }
+    op.grid = dim3(ntn, L.mtiles, B);
+    if (a0 == reinterpret_cast<const OT*>(pl.xin.p)) op.alg_scale = (double)cfg_.in_channels / (double)ac0;   // 242 of the 256 packed channels
+    op.tap = Tap{nullptr, out, 1, L.T, 512, 512, hs, B, 0};
     op.level = level;
     pl.ops.push_back(op);
     return &pl.ops.back();
   };
-  conv_op("y1", src0, c0, ld0, src1, c1, w.w1, 3, w.b1, pl.y.template as<float>(), true)->tap.name = "y1";
-  conv_op("r", src0, c0, ld0, src1, c1, w.wr, 1, w.br, pl.r.template as<float>(), false)->tap.name = "r";
+  OT* ybuf = pl.y.template as<OT>();
+  if (grouped_enabled()) {
+    Op* o = conv_op("y1", src0, c0, ld0, src1, c1, w.w1, 3, w.b1, ybuf, true, true);
+    o->tap.name = "y1";
+    o->tap2 = Tap{"r", pl.r.p, 1, L.T, 512, 512, hs, B, 0};
+  } else {
+    conv_op("y1", src0, c0, ld0, src1, c1, w.w1, 3, w.b1, ybuf, true, false)->tap.name = "y1";
+    conv_op("r", src0, c0, ld0, src1, c1, w.wr, 1, w.br, pl.r.template as<OT>(), false, false)->tap.name = "r";
+  }
   {
     Op op;
     op.kind = OP_GN_APPLY;
     op.name = tag + ".a1";
-    op.y = pl.y.template as<float>();
+    op.y = pl.y.p;
     op.part = pl.gnpart.template as<float>();
     op.gamma = w.g1;
     op.beta = w.be1;
@@ -207,16 +250,16 @@ void Engine<OT>::add_resnet(Plan<OT>& pl, int ridx, int level, const OT* src0, i
     op.tap = Tap{"a1", pl.a1.p, 1, L.T, 512, 512, hs, B, 0};
     pl.ops.push_back(op);
   }
-  conv_op("y2", pl.a1.template as<OT>(), 512, 512, nullptr, 0, w.w2, 3, w.b2, pl.y.template as<float>(), true)->tap.name = "y2";
+  conv_op("y2", pl.a1.template as<OT>(), 512, 512, nullptr, 0, w.w2, 3, w.b2, ybuf, true, false)->tap.name = "y2";
   {
     Op op;
     op.kind = OP_GN_RES_SPK_LN;
     op.name = tag + ".resnet";
-    op.y = pl.y.template as<float>();
+    op.y = pl.y.p;
     op.part = pl.gnpart.template as<float>();
     op.gamma = w.g2;
     op.beta = w.be2;
-    op.res = pl.r.template as<float>();
+    op.res = pl.r.p;
     op.ln_g = next.ln1g;
     op.ln_b = next.ln1b;
     op.hres = pl.hres.template as<float>();
@@ -236,7 +279,6 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
   const long long tiles = (long long)L.mtiles * B;
   OT* ln = pl.ln.template as<OT>();
   OT* qk = pl.qk.template as<OT>();
-  uint8_t* qk8 = rowmax_fp8() ? pl.qk8.template as<uint8_t>() : nullptr;
   OT* vt = pl.vt.template as<OT>();
   OT* P = pl.P.template as<OT>();
   OT* ao = pl.ao.template as<OT>();
@@ -273,9 +315,6 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.out2_bstride = (long long)2048 * Sp;
     gp.ld2 = Sp;
     set_D<OT>(gp, qk, 4096, S, gp.out_bstride, 4096, B);
-    gp.out8 = qk8;
-    gp.out8_bstride = (long long)L.R * 4096;
-    gp.ld8 = 4096;
     gp.mapD2 = make_tmap_3d(vt, sizeof(OT), S, 2048, B, Sp, (uint64_t)2048 * Sp, 32, 32, false);
     op.grid = dim3(6144 / op.bn, L.mtiles, B);
     op.tap = Tap{"qk", qk, 1, S, 4096, 4096, gp.out_bstride, B, 0};
@@ -289,7 +328,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
   }
 
   // Attention without a score matrix in HBM.  Q K^T runs twice on the tensor cores: pass 1 keeps only per-row
-  // maxima (key-masked), pass 2 recomputes the tile, writes P~ = exp(s - rowmax) in operand precision and partial
+  // maxima (key-masked; skipped entirely for entries that are provably shift-free), pass 2 recomputes the tile, writes P~ = exp(s - rowmax) in operand precision and partial
   // row sums; P~ V then divides by the row sum in its epilogue.  Replaces scores f32 write + read and the softmax
   // kernel (12 B per score) by 2 + 2 B per score; 1/sqrt(d), the key mask and the normalisation follow
   // F.scaled_dot_product_attention with a boolean key mask.
@@ -307,16 +346,6 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.a_hcol = 512;
     add_seg(gp, 0, 0, 0, 512 / BK);
     gp.mapB = make_tmap_3d(qk, sizeof(OT), 4096, S, B, 4096, (uint64_t)L.R * 4096, BK, op.bn / 2);
-    if (pass == 0 && qk8 != nullptr) {
-      // the shift only has to be NEAR the row maximum: e4m3 copies of Q and K, half the operand bytes, twice the MMA rate
-      gp.ab_fp8 = 1;
-      gp.nseg = 0;
-      gp.nkb = 0;
-      gp.mapA[0] = make_tmap_3d(qk8, 1, 4096, S, B, 4096, (uint64_t)L.R * 4096, 128, SRN_MC ? 64 : 128);
-      gp.mapA[1] = gp.mapA[0];
-      add_seg(gp, 0, 0, 0, 512 / 128);
-      gp.mapB = make_tmap_3d(qk8, 1, 4096, S, B, 4096, (uint64_t)L.R * 4096, 128, op.bn / 2);
-    }
     gp.b_col0 = 2048;
     gp.b_hcol = 512;
     gp.b_batch_mode = 1;
@@ -331,6 +360,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
       gp.noshift = pl.noshift.template as<int>();
       gp.qk_norm2 = pl.qk_norm2.template as<float>();
       gp.nz_norm = B * H;
+      gp.ns_count = pl.ns_count.template as<unsigned long long>();
       static const float nmax = getenv("SRN_NOSHIFT_MAX") ? (float)atof(getenv("SRN_NOSHIFT_MAX")) : 64.0f;
       gp.noshift_max = nmax < 64.0f ? nmax : 64.0f;      // (tests lower it to get shifted and shift-free entries in one launch)
     }
@@ -346,6 +376,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.d_zbatch = 1;
     op.grid = dim3(cdiv(S, op.bn), L.mtiles, B * H);
     if (pass == 1) op.tap = Tap{"P", P, 1, S, S, Sp, (long long)S * Sp, B * H, 0};
+    if (pass == 0) op.alg_scale = 0.0;      // (F(L) counts Q K^T once: the exp pass)
     if (pass == 0) push(op, "rowmax");
     else exp_op = op;
   }
@@ -354,7 +385,7 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     op.gp = base_gemm(pl, level);
     GemmParams& gp = op.gp;
     gp.HB = H;
-    gp.mapA[0] = make_tmap_3d(P, sizeof(OT), S, S, (uint64_t)B * H, Sp, (uint64_t)S * Sp, BK, SRN_MC ? 64 : 128);
+    gp.mapA[0] = make_tmap_3d(P, sizeof(OT), S, S, (uint64_t)B * H, Sp, (uint64_t)S * Sp, BK, 128);
     gp.mapA[1] = gp.mapA[0];
     gp.a_zbatch = 1;
     add_seg(gp, 0, 0, 0, cdiv(S, BK));
@@ -375,26 +406,11 @@ void Engine<OT>::add_tfm(Plan<OT>& pl, int tidx, int level, OT* out_hc, const st
     gp.d_hcol = 512;
     op.grid = dim3(512 / op.bn, L.mtiles, B * H);
     op.tap = Tap{"ao", ao, 1, S, 2048, 2048, gp.out_bstride, B, 0};
-    // P~ of the whole (batch, head) range is B H S Sp elements - 131 MB at C2's full rate, 2.3 GB at C5 - more than the
-    // 126 MB L2.  With SRN_ATTN_SLICES=1 both passes run slice by slice over the (batch, head) range, a slice's P~
-    // (<= kPSliceBytes) being consumed by its P~ V launch right after it was written (measured: not a gain, see above).
-    const int BH = B * H;
-    const size_t z_bytes = (size_t)S * Sp * sizeof(OT);
-    int nsl = attn_slices() ? (int)std::min<size_t>((size_t)BH, (z_bytes * BH + kPSliceBytes - 1) / kPSliceBytes) : 1;
-    // ... but never fewer than about four waves of tiles per launch (74 CTA pairs)
-    const long long tiles_z = (long long)cdiv(S, sc_bn) * L.mtiles;
-    while (nsl > 1 && tiles_z * (BH / nsl) < 4 * 74) --nsl;
-    const int zper = cdiv(BH, nsl);
-    for (int z0 = 0; z0 < BH; z0 += zper) {
-      const int nz = std::min(zper, BH - z0);
-      Op e = exp_op, v = op;
-      e.gp.z0 = z0;
-      e.grid.z = nz;
-      v.gp.z0 = z0;
-      v.grid.z = nz;
-      push(e, "expscores");
-      push(v, "pv");
-    }
+    // (P~ of the whole (batch, head) range is B H S Sp elements - 131 MB at C2's full rate, 2.3 GB at C5 - more than the
+    //  126 MB L2; running both passes slice by slice so that a slice's P~ stays in the L2 was measured in round 1 and
+    //  lost to its extra launches: profiles/r01_ab_attn_slices.txt)
+    push(exp_op, "expscores");
+    push(op, "pv");
   }
   {  // h = attn_out W_o^T + b_o + h    (transformer.py:304)
     Op op;
@@ -485,16 +501,16 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
   const size_t rows = (size_t)B * pl.Tp;
   const size_t es = sizeof(OT);
   pl.xin.alloc(rows * 256 * es);
-  pl.y.alloc(rows * C * 4);
-  pl.r.alloc(rows * C * 4);
+  pl.y.alloc(rows * C * es);      // conv outputs that feed a GroupNorm, operand width (EPI_STORE_GN)
+  pl.r.alloc(rows * C * es);
   pl.gnpart.alloc((size_t)B * 2 * pl.lv[0].mtiles * 16 * 4);   // one (sum, sumsq) x 8 groups per 128-row tile
   pl.a1.alloc(rows * C * es);
   pl.hres.alloc(rows * C * 4);
   pl.ln.alloc(rows * C * es);
   pl.qk.alloc(rows * 4096 * es);
-  if (rowmax_fp8()) pl.qk8.alloc(rows * 4096);
   pl.qk_norm2.alloc((size_t)B * H * 16 * 4);
   pl.noshift.alloc((size_t)B * H * 4);
+  pl.ns_count.alloc(16);
   pl.vt.alloc((size_t)B * 2048 * pl.lv[0].Sp * es);
   {  // softmax statistics: one (max, sum) partial per row per 128-column (or 64-column) slice of the score GEMM
     const size_t n128 = 2 * (size_t)cdiv(T, 128);
@@ -614,33 +630,50 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
   add_resnet(pl, ri, 1, cur, 512, 512, hid1, 512, "up0", tfms_[ri]);
   add_tfm(pl, ri, 1, hc, "up0");
   ++ri;
-  for (int par = 0; par < 2; ++par) {
+  // ConvTranspose1d(4, 2, 1): out[2m] = W1 x[m] + W3 x[m-1], out[2m+1] = W2 x[m] + W0 x[m+1].  The two output parities
+  // are two GEMMs over the same operand (K = 2 x 512 each) that write the interleaved full-rate tensor viewed as
+  // [B][T2][1024]; they run as the two tile groups of ONE launch (SRN_GROUPED=0: two launches).
+  {
     const Level& L = pl.lv[1];
-    Op op;
-    op.kind = OP_GEMM;
-    op.name = par == 0 ? "up0.out_even" : "up0.out";
-    op.level = 1;
-    op.gp = base_gemm(pl, 1);
-    GemmParams& gp = op.gp;
-    set_A<OT>(gp, 0, hc, 512, T2, T2, 512, B);
-    add_seg(gp, 0, 0, par == 0 ? -1 : 0, 512 / BK);
-    add_seg(gp, 0, 0, par == 0 ? 0 : 1, 512 / BK);
-    op.bn = pick_bn(512, tiles1);
-    set_B_weight<OT>(gp, par == 0 ? up_conv_[0].w : up_conv_[0].w_odd, 512, 1024, op.bn);
-    gp.N = 512;
-    gp.epi = EPI_STORE_OT;
-    gp.bias = up_conv_[0].b;
-    gp.out = cv + par * 512;              // frame 2m + par of the full-rate tensor viewed as [B][T2][1024]
-    gp.out_bstride = (long long)T2 * 1024;
-    gp.ldo = 1024;
-    gp.rowmask = mask;
-    gp.mask_bstride = pl.Tp;
-    gp.mask_step = 2;
-    gp.mask_off = par;
-    set_D<OT>(gp, cv + par * 512, 512, T2, gp.out_bstride, 1024, B);
-    op.grid = dim3(512 / op.bn, L.mtiles, B);
-    if (par == 1) op.tap = Tap{"out", cv, 1, T, 512, 512, (long long)pl.Tp * 512, B, 0};
-    pl.ops.push_back(op);
+    const bool grouped = grouped_enabled();
+    for (int par = 0; par < (grouped ? 1 : 2); ++par) {
+      Op op;
+      op.kind = OP_GEMM;
+      op.name = (grouped || par == 1) ? "up0.out" : "up0.out_even";
+      op.level = 1;
+      op.gp = base_gemm(pl, 1);
+      GemmParams& gp = op.gp;
+      set_A<OT>(gp, 0, hc, 512, T2, T2, 512, B);
+      add_seg(gp, 0, 0, par == 0 ? -1 : 0, 512 / BK);
+      add_seg(gp, 0, 0, par == 0 ? 0 : 1, 512 / BK);
+      op.bn = pick_bn(grouped ? 1024 : 512, tiles1);
+      set_B_weight<OT>(gp, par == 0 ? up_conv_[0].w : up_conv_[0].w_odd, 512, 1024, op.bn);
+      gp.N = 512;
+      gp.epi = EPI_STORE_OT;
+      gp.bias = up_conv_[0].b;
+      gp.out = cv + par * 512;              // frame 2m + par of the full-rate tensor viewed as [B][T2][1024]
+      gp.out_bstride = (long long)T2 * 1024;
+      gp.ldo = 1024;
+      gp.rowmask = mask;
+      gp.mask_bstride = pl.Tp;
+      gp.mask_step = 2;
+      gp.mask_off = par;
+      set_D<OT>(gp, cv + par * 512, 512, T2, gp.out_bstride, 1024, B);
+      int ntn = 512 / op.bn;
+      if (grouped) {      // group 1 = the odd output frames
+        begin_group1(gp, ntn);
+        add_seg_g1(gp, 0, 0, 0, 512 / BK);
+        add_seg_g1(gp, 0, 0, 1, 512 / BK);
+        set_B2_weight<OT>(gp, up_conv_[0].w_odd, 512, 1024, op.bn);
+        gp.bias2 = up_conv_[0].b;
+        gp.mask_off2 = 1;
+        gp.mapD2 = make_tmap_3d(cv + 512, sizeof(OT), 512, T2, B, 1024, (uint64_t)gp.out_bstride, 128 / sizeof(OT), 32);
+        ntn *= 2;
+      }
+      op.grid = dim3(ntn, L.mtiles, B);
+      if (grouped || par == 1) op.tap = Tap{"out", cv, 1, T, 512, 512, (long long)pl.Tp * 512, B, 0};
+      pl.ops.push_back(op);
+    }
   }
   // ---- up 1 (full rate): cat([h[:, :, :T], hid0]) -> resnet + transformer, Conv1d k3
   add_resnet(pl, ri, 0, cv, 512, 512, hid0, 512, "up1", tfms_[ri]);
@@ -661,13 +694,13 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
     op.bn = pick_bn(512, tiles0);
     set_B_weight<OT>(gp, final_conv_.w, 512, 1536, op.bn);
     gp.N = 512;
-    gp.epi = EPI_STORE_F32;
+    gp.epi = EPI_STORE_GN;
     gp.bias = final_conv_.b;
     gp.out = pl.y.p;
     gp.out_bstride = (long long)pl.Tp * 512;
     gp.ldo = 512;
     gp.gn_part = pl.gnpart.template as<float>();
-    set_D<float>(gp, pl.y.template as<float>(), 512, T, gp.out_bstride, 512, B);
+    set_D<OT>(gp, pl.y.template as<OT>(), 512, T, gp.out_bstride, 512, B);
     op.grid = dim3(512 / op.bn, L.mtiles, B);
     pl.ops.push_back(op);
   }
@@ -675,7 +708,7 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
     Op op;
     op.kind = OP_GN_APPLY;
     op.name = "final_block";
-    op.y = pl.y.template as<float>();
+    op.y = pl.y.p;
     op.part = pl.gnpart.template as<float>();
     op.gamma = final_g_;
     op.beta = final_be_;

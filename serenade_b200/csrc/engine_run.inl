@@ -34,33 +34,25 @@ static void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t
   SRN_CUDA(cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...));
 }
 
-// A-stationary layout (gemm_mainloop.cuh): K fits the A slots, one K segment, at least two N tiles per row block.
-// Built, bit-identical, measured on one box (profiles/r01_ab_astationary.txt) and NOT adopted: with half the operand
-// bytes per tile the K = 512 GEMMs got no faster with the epilogue switched off (QKV 60.8 vs 56.9 us, Q K^T 57.3 vs
-// 46.6 us) - the operand feed is not what bounds them - so it is opt-in (SRN_ASTAT=1) for further experiments.
-static bool astat_enabled() {
-  static const bool on = [] {
-    const char* e = getenv("SRN_ASTAT");
-    return e != nullptr && e[0] == '1';
+// Sixteen epilogue warps (gemm_kernel.cuh: GemmCfg) for the epilogue-bound K = 512 GEMMs on 256-column tiles.
+// SRN_EW16 is a bit mask for A/B runs: 1 = QKV, 2 = exp pass, 4 = P~ V, 8 = row-max pass (default: QKV + exp).
+static int ew16_mask() {
+  static const int m = [] {
+    const char* e = getenv("SRN_EW16");
+    return e != nullptr ? atoi(e) : 3;
   }();
-  return on;
-}
-template <typename OT, int BN>
-static bool astat_ok(const GemmParams& gp, dim3 grid) {
-  if (std::is_same<OT, float>::value || !astat_enabled()) return false;
-  if (gp.nseg != 1 || gp.win != 0 || (gp.dbg_mode & 3) != 0 || grid.x < 2 || gp.nkb > 8) return false;
-  return (kAsOpBytes - gp.nkb * GemmCfg<BN, true>::kABytes) / GemmCfg<BN, true>::kBBytes >= 3;
+  return m;
 }
 
-template <typename OT, int BN, int EPI, bool AS = false>
+template <typename OT, int BN, int EPI, int EW = 8>
 static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t st) {
   gp.ntn = (int)grid.x;
   gp.ntm = (int)grid.y;
   gp.nz = (int)grid.z;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof cfg);
-  cfg.blockDim = dim3(GemmCfg<BN, AS>::kThreads);
-  cfg.dynamicSmemBytes = GemmCfg<BN, AS>::kSmemBytes;
+  cfg.blockDim = dim3(GemmCfg<BN, EW>::kThreads);
+  cfg.dynamicSmemBytes = GemmCfg<BN, EW>::kSmemBytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -71,41 +63,18 @@ static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
-#if SRN_MC
-  if (BN == 256) {
-    // clusters of two CTA pairs on adjacent N tiles, A multicast between them (gemm_mainloop.cuh)
-    static const int max_clusters = [&] {
-      cudaLaunchConfig_t q = cfg;
-      q.gridDim = dim3(4 * 64);
-      cudaLaunchAttribute a4 = attr[0];
-      a4.val.clusterDim.x = 4;
-      q.attrs = &a4;
-      q.numAttrs = 1;
-      int n = 0;
-      SRN_CUDA(cudaOccupancyMaxActiveClusters(&n, gemm_kernel<OT, 256, EPI, true>, &q));
-      if (getenv("SRN_VERBOSE")) fprintf(stderr, "[srn] 4-CTA clusters resident: %d\n", n);
-      return n;
-    }();
-    const long long units = (long long)((grid.x + 1) / 2) * grid.y * grid.z;
-    const unsigned ncl = (unsigned)std::min<long long>(units, max_clusters);
-    attr[0].val.clusterDim.x = 4;
-    cfg.gridDim = dim3(4 * ncl);
-    SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, 256, EPI, true>, gp));
-    return;
-  }
-#endif
   const long long tiles = (long long)grid.x * grid.y * grid.z;                 // 256 x BN tiles, one per CTA pair
   const unsigned pairs = (unsigned)std::min<long long>(tiles, num_sms / 2);    // persistent: one pair per SM pair
   cfg.gridDim = dim3(2 * pairs);
-  SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, BN, EPI, false, AS>, gp));
+  SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, BN, EPI, EW>, gp));
 }
 
-// the epilogues that have an A-stationary instantiation (2-byte / 1-byte operands only)
+// the epilogues that have a sixteen-warp instantiation (256-column tiles only)
 template <typename OT, int BN, int EPI>
-static void launch_gemm_as(const GemmParams& gp, dim3 grid, int num_sms, cudaStream_t st) {
-  if constexpr (!std::is_same<OT, float>::value && !SRN_MC) {
-    if (astat_ok<OT, BN>(gp, grid)) {
-      launch_gemm_impl<OT, BN, EPI, true>(gp, grid, num_sms, st);
+static void launch_gemm_ew(const GemmParams& gp, dim3 grid, int num_sms, cudaStream_t st, int bit) {
+  if constexpr (BN == 256) {
+    if (ew16_mask() & bit) {
+      launch_gemm_impl<OT, BN, EPI, 16>(gp, grid, num_sms, st);
       return;
     }
   }
@@ -116,15 +85,16 @@ template <typename OT, int BN>
 static void launch_gemm_bn(const GemmParams& gp, dim3 grid, int num_sms, cudaStream_t st) {
   switch (gp.epi) {
     case EPI_STORE_F32: launch_gemm_impl<OT, BN, EPI_STORE_F32>(gp, grid, num_sms, st); break;
+    case EPI_STORE_GN: launch_gemm_impl<OT, BN, EPI_STORE_GN>(gp, grid, num_sms, st); break;
     case EPI_STORE_OT: launch_gemm_impl<OT, BN, EPI_STORE_OT>(gp, grid, num_sms, st); break;
     case EPI_RESID_F32: launch_gemm_impl<OT, BN, EPI_RESID_F32>(gp, grid, num_sms, st); break;
     case EPI_RESID_OT: launch_gemm_impl<OT, BN, EPI_RESID_OT>(gp, grid, num_sms, st); break;
-    case EPI_GEGLU: launch_gemm_as<OT, BN, EPI_GEGLU>(gp, grid, num_sms, st); break;
-    case EPI_QKV: launch_gemm_as<OT, BN, EPI_QKV>(gp, grid, num_sms, st); break;
+    case EPI_GEGLU: launch_gemm_impl<OT, BN, EPI_GEGLU>(gp, grid, num_sms, st); break;
+    case EPI_QKV: launch_gemm_ew<OT, BN, EPI_QKV>(gp, grid, num_sms, st, 1); break;
     case EPI_EULER: launch_gemm_impl<OT, BN, EPI_EULER>(gp, grid, num_sms, st); break;
-    case EPI_ROWMAX: launch_gemm_as<OT, BN, EPI_ROWMAX>(gp, grid, num_sms, st); break;
-    case EPI_EXP: launch_gemm_as<OT, BN, EPI_EXP>(gp, grid, num_sms, st); break;
-    case EPI_PV: launch_gemm_impl<OT, BN, EPI_PV>(gp, grid, num_sms, st); break;
+    case EPI_ROWMAX: launch_gemm_ew<OT, BN, EPI_ROWMAX>(gp, grid, num_sms, st, 8); break;
+    case EPI_EXP: launch_gemm_ew<OT, BN, EPI_EXP>(gp, grid, num_sms, st, 2); break;
+    case EPI_PV: launch_gemm_ew<OT, BN, EPI_PV>(gp, grid, num_sms, st, 4); break;
     case EPI_RESID_ACT: launch_gemm_impl<OT, BN, EPI_RESID_ACT>(gp, grid, num_sms, st); break;
     default: fail("unknown GEMM epilogue %d", gp.epi);
   }
@@ -134,11 +104,9 @@ template <typename OT>
 void Engine<OT>::launch_gemm(const GemmParams& gp, int bn, dim3 grid, cudaStream_t st) {
   if (gp.nkb < 1 || gp.nseg < 1) fail("gemm with empty K");
   if (gp.epi == EPI_RESID_F32 && gp.resid != gp.out) fail("EPI_RESID_F32 updates its residual in place (TMA reduce-add)");
-  if (gp.ab_fp8) {
-    if (gp.epi != EPI_ROWMAX) fail("e4m3 operands are only used by the row-max pass");
-    if (bn == 256) launch_gemm_as<Fp8, 256, EPI_ROWMAX>(gp, grid, num_sms_, st);
-    else launch_gemm_as<Fp8, 128, EPI_ROWMAX>(gp, grid, num_sms_, st);
-  } else if (bn == 256) launch_gemm_bn<OT, 256>(gp, grid, num_sms_, st);
+  if (gp.grp_ntn0 > 0 && (gp.win != 0 || gp.grp_nkb < 1 || (gp.epi != EPI_STORE_GN && gp.epi != EPI_STORE_OT)))
+    fail("tile groups: plain operand path, store epilogues only");
+  if (bn == 256) launch_gemm_bn<OT, 256>(gp, grid, num_sms_, st);
   else launch_gemm_bn<OT, 128>(gp, grid, num_sms_, st);
   ++launches;
 }
@@ -200,6 +168,11 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
           gp.blend_src = pl.blend_src.template as<float>();
         }
         launch_gemm(gp, op.bn, op.grid, st);
+      } else if (!noshift && (op.gp.noshift != nullptr || op.gp.qk_norm2 != nullptr)) {
+        GemmParams gp = op.gp;      // srn_set_option("noshift", 0): no norms collected, every entry takes the row-max pass
+        gp.noshift = nullptr;
+        gp.qk_norm2 = nullptr;
+        launch_gemm(gp, op.bn, op.grid, st);
       } else if (op.gp.gn_part != nullptr && gn_valid_only) {
         GemmParams gp = op.gp;
         gp.gn_mask = mask;
@@ -223,7 +196,7 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
       const float* tb = op.use_tbias ? pl.tb.template as<float>() + ((size_t)op.resnet_idx * pl.tb_steps + step) * 512
                                      : nullptr;
       dim3 grid(cdiv(L.T, rpb), B);
-      launch_k(gn_apply_kernel<OT>, grid, dim3(256), st, op.y, op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma,
+      launch_k(gn_apply_kernel<OT>, grid, dim3(256), st, static_cast<const OT*>(op.y), op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma,
                op.beta, tb, mask, pl.Tp, L.mask_step, static_cast<OT*>(op.out), rpb, nvalid, tb_bstride_);
       ++launches;
     } break;
@@ -235,8 +208,8 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
       dim3 grid(cdiv(L.T, rpb), B);
       const float* sc = pl.spk_scale.template as<float>() + (size_t)op.resnet_idx * B * 512;
       const float* sb = pl.spk_bias.template as<float>() + (size_t)op.resnet_idx * B * 512;
-      launch_k(gn_res_spk_ln<OT>, grid, dim3(256), st, op.y, op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma,
-               op.beta, op.res, mask, pl.Tp, L.mask_step, sc, sb, op.ln_g, op.ln_b, op.hres, static_cast<OT*>(op.out), rpb,
+      launch_k(gn_res_spk_ln<OT>, grid, dim3(256), st, static_cast<const OT*>(op.y), op.part, 2 * L.mtiles, L.T, (long long)L.R * 512, op.gamma,
+               op.beta, static_cast<const OT*>(op.res), mask, pl.Tp, L.mask_step, sc, sb, op.ln_g, op.ln_b, op.hres, static_cast<OT*>(op.out), rpb,
                nvalid);
       ++launches;
     } break;
@@ -252,6 +225,13 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
     const size_t dot = op.name.rfind('.');
     const std::string key = (dot == std::string::npos ? std::string() : op.name.substr(0, dot + 1)) + op.tap.name;
     Tap t = op.tap;
+    t.name = key.c_str();
+    capture_tap(pl, t, st);
+  }
+  if (debug && op.tap2.name != nullptr) {
+    const size_t dot = op.name.rfind('.');
+    const std::string key = (dot == std::string::npos ? std::string() : op.name.substr(0, dot + 1)) + op.tap2.name;
+    Tap t = op.tap2;
     t.name = key.c_str();
     capture_tap(pl, t, st);
   }
@@ -303,6 +283,7 @@ void Engine<OT>::prepass(Plan<OT>& pl, const std::vector<float>& ts, const std::
     launch_k(count_valid_kernel, dim3(B), dim3(256), st, mask, pl.T, pl.Tp, B, pl.nvalid.template as<int>());
     ++launches;
   }
+  SRN_CUDA(cudaMemsetAsync(pl.ns_count.p, 0, 16, st));
   launch_k(row_extent_kernel, dim3(B), dim3(256), st, mask, pl.T, pl.Tp, B, pl.rowext.template as<int>());
   ++launches;
   g_next_launch_serialised = true;      // (the next launch_k below: a full dependency, see gemm_mainloop.cuh: s_ext)
@@ -355,6 +336,8 @@ template <typename OT>
 void Engine<OT>::estimator_forward(const float* x, const float* mu, const uint8_t* mask, const float* spk, float t,
                                    int B, int T, float* v_out, cudaStream_t st) {
   Plan<OT>& pl = get_plan(B, T);
+  last_plan_ = &pl;
+  pl.staged_ts.clear();
   ensure_step_buffers(pl, 1, cfg_.in_channels, (int)resnets_.size());
   stage_inputs(pl, x, mu, mask, spk, cudaMemcpyDeviceToDevice, st);
   const float zero = 0.f;
@@ -373,6 +356,8 @@ template <typename OT>
 void Engine<OT>::estimator_forward_t(const float* x, const float* mu, const uint8_t* mask, const float* spk,
                                      const float* t_host, int B, int T, float* v_out, cudaStream_t st) {
   Plan<OT>& pl = get_plan(B, T);
+  last_plan_ = &pl;
+  pl.staged_ts.clear();
   ensure_step_buffers(pl, B, cfg_.in_channels, (int)resnets_.size());
   stage_inputs(pl, x, mu, mask, spk, cudaMemcpyDeviceToDevice, st);
   const std::vector<float> ts(t_host, t_host + B), zeros(B, 0.f);
@@ -399,6 +384,7 @@ void Engine<OT>::cfm_loss(const float* x1, const float* z, const float* t_host, 
                           const float* spk, const uint8_t* mask_l, int B, int T, float sigma_min, float* y_out,
                           float* loss_out, cudaStream_t st) {
   Plan<OT>& pl = get_plan(B, T);
+  pl.staged_ts.clear();
   const int C = cfg_.out_channels;
   const long long n = (long long)B * C * T;
   const float oms = (float)(1.0 - (double)sigma_min);
@@ -434,14 +420,23 @@ void Engine<OT>::solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bo
       if (s < n_steps) dt = t_span[s + 1] - t;
     }
   }
+  last_plan_ = &pl;
+  const size_t tb_before = pl.tb_steps;
   ensure_step_buffers(pl, n_steps, cfg_.in_channels, (int)resnets_.size());
-  SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, ts.data(), (size_t)n_steps * 4, cudaMemcpyHostToDevice, st));
-  SRN_CUDA(cudaMemcpyAsync(pl.dts.p, dts.data(), (size_t)n_steps * 4, cudaMemcpyHostToDevice, st));
-  SRN_CUDA(cudaStreamSynchronize(st));   // ts / dts are host temporaries
-  check_abort();                         // (reports a timeout of an earlier asynchronous solve)
+  // The (t, dt) tables stay on the device between calls: a decode loop passes the same t_span every time, and then
+  // nothing is uploaded and the call never blocks the host (the copies below need a sync: ts / dts are temporaries).
+  const std::vector<float> span(t_span, t_span + n_steps + 1);
+  if (tb_before != (size_t)pl.tb_steps || pl.staged_ts != span) {
+    SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, ts.data(), (size_t)n_steps * 4, cudaMemcpyHostToDevice, st));
+    SRN_CUDA(cudaMemcpyAsync(pl.dts.p, dts.data(), (size_t)n_steps * 4, cudaMemcpyHostToDevice, st));
+    SRN_CUDA(cudaStreamSynchronize(st));
+    check_abort();                       // (reports a timeout of an earlier asynchronous solve)
+    pl.staged_ts = span;
+  }
   blend_active_ = blend;
   if (use_graph && !debug) {
-    if (pl.graph == nullptr || pl.graph_steps != n_steps || pl.graph_blend != blend || pl.graph_gn_valid != gn_valid_only) {
+    if (pl.graph == nullptr || pl.graph_steps != n_steps || pl.graph_blend != blend || pl.graph_gn_valid != gn_valid_only ||
+        pl.graph_noshift != noshift) {
       if (pl.graph) {
         cudaGraphExecDestroy(pl.graph);
         pl.graph = nullptr;
@@ -468,6 +463,7 @@ void Engine<OT>::solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bo
       pl.graph_steps = n_steps;
       pl.graph_blend = blend;
       pl.graph_gn_valid = gn_valid_only;
+      pl.graph_noshift = noshift;
     }
     SRN_CUDA(cudaGraphLaunch(pl.graph, st));
     launches += pl.graph_nodes;
@@ -475,6 +471,17 @@ void Engine<OT>::solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bo
     prepass(pl, ts, dts, st);
     for (int s = 0; s < n_steps; ++s) run_forward(pl, s, nullptr, true, st);
   }
+}
+
+template <typename OT>
+void Engine<OT>::softmax_stats(int64_t* out2) {
+  out2[0] = out2[1] = 0;
+  if (last_plan_ == nullptr) return;
+  unsigned long long h[2] = {0, 0};
+  SRN_CUDA(cudaDeviceSynchronize());
+  SRN_CUDA(cudaMemcpy(h, last_plan_->ns_count.p, sizeof h, cudaMemcpyDeviceToHost));
+  out2[0] = (int64_t)h[0];
+  out2[1] = (int64_t)h[1];
 }
 
 template <typename OT>
@@ -508,8 +515,8 @@ void Engine<OT>::solve_euler_host(const float* z, const float* mu, const uint8_t
 namespace srn {
 
 // Per-op timing of one estimator forward (CUDA events around `reps` back-to-back launches of each op).
-// Algorithmic work: GEMM flops = 2 * valid rows * N * K (K as issued, incl. zero padding of C_in 242 -> 256);
-// row-kernel bytes = the tensors they must read and write once.
+// GEMM flops: algorithmic and as issued, see below; row-kernel bytes = the tensors they must read and
+// write once.
 #if SRN_TRACE
 // One traced launch of a GEMM op: medians over CTAs of the phase lengths in SM clocks (stderr).
 // stamps: 0 kernel entry, 1 after griddepcontrol.wait, 2 first operand stage landed (leader), 3 last MMA committed
@@ -633,12 +640,8 @@ std::string Engine<OT>::profile_ops(int B, int T, int reps) {
   const size_t es = sizeof(OT);
   for (size_t i = 0; i < pl.ops.size(); ++i) {
     Op& op = pl.ops[i];
-    static const int dbg_mode = getenv("SRN_DBG_MODE") ? atoi(getenv("SRN_DBG_MODE")) : 0;
-    const int saved_mode = op.gp.dbg_mode;
-    op.gp.dbg_mode = dbg_mode;
     SRN_CUDA(cudaEventRecord(e0, st));
     for (int r = 0; r < reps; ++r) launch_op(pl, op, 0, nullptr, true, st);
-    op.gp.dbg_mode = saved_mode;
     SRN_CUDA(cudaEventRecord(e1, st));
     SRN_CUDA(cudaEventSynchronize(e1));
     float ms = 0.f;
@@ -648,22 +651,27 @@ std::string Engine<OT>::profile_ops(int B, int T, int reps) {
     if ((op.kind == OP_GN_RES_SPK_LN || op.kind == OP_GN_APPLY) && getenv("SRN_TRACE") != nullptr) trace_row_op(pl, op, st);
 #endif
     const Level& L = pl.lv[op.level];
-    double flops = 0, bytes = 0;
+    double flops = 0, bytes = 0, issued = 0;
     const char* kind = "";
     const double rows = (double)B * L.T;
     switch (op.kind) {
       case OP_GEMM:
         kind = op.bn == 256 ? "gemm_bn256" : "gemm_bn128";
-        flops = 2.0 * (double)op.gp.M * op.gp.N * ((double)op.gp.nkb * (op.gp.ab_fp8 ? 128 : BK)) * (double)op.grid.z;
+        // issued: every K block the tensor cores run (incl. the 242 -> 256 channel padding, the hi + lo weight passes of
+        // the TF32-class mode and the row-max pass); algorithmic: SURVEY 8d's F(L) share of this op - no padding, one
+        // pass over the weights, nothing for the row-max pass (softmax is one Q K^T in F)
+        issued = 2.0 * (double)op.gp.M * op.gp.N * ((double)(op.gp.nkb + (op.gp.grp_ntn0 > 0 ? op.gp.grp_nkb : 0)) * BK) *
+                 (double)op.grid.z;
+        flops = issued * op.alg_scale * ((OpTraits<OT>::kTF32 && op.gp.b_batch_mode == 0) ? 0.5 : 1.0);
         break;
       case OP_PACKX: kind = "pack_cf_to_cl"; bytes = (double)B * cfg_.out_channels * T * (4 + es); break;
-      case OP_GN_APPLY: kind = "gn_apply"; bytes = rows * 512 * (4 + es); break;
-      case OP_GN_RES_SPK_LN: kind = "gn_res_spk_ln"; bytes = rows * 512 * (4 + 4 + 4 + es); break;
+      case OP_GN_APPLY: kind = "gn_apply"; bytes = rows * 512 * (es + es); break;
+      case OP_GN_RES_SPK_LN: kind = "gn_res_spk_ln"; bytes = rows * 512 * (es + es + 4 + es); break;
       case OP_LAYERNORM: kind = "layernorm"; bytes = rows * 512 * (4 + es); break;
     }
     char buf[512];
-    snprintf(buf, sizeof buf, "%s{\"op\": \"%s\", \"kernel\": \"%s\", \"ms\": %.6f, \"flops\": %.6e, \"bytes\": %.6e}",
-             i ? ", " : "", op.name.c_str(), kind, ms / reps, flops, bytes);
+    snprintf(buf, sizeof buf, "%s{\"op\": \"%s\", \"kernel\": \"%s\", \"ms\": %.6f, \"flops\": %.6e, \"flops_issued\": %.6e, \"bytes\": %.6e}",
+             i ? ", " : "", op.name.c_str(), kind, ms / reps, flops, issued, bytes);
     js += buf;
   }
   js += "]";

@@ -2,23 +2,19 @@
 //
 //   D[z][m][n] = sum_k A[z][m + shift(k)][col(k)] * B[z][n][k]        (both operands K-major)
 //
-// A is described by up to six K "segments" (tap shift, source tensor, column base), which is how the
+// A is described by up to 24 K "segments" (tap shift, source tensor, column base), which is how the
 // masked Conv1d k3 / stride-2 / ConvTranspose1d / 1x1 / channel-concat forms of the estimator all map
 // onto one kernel: TMA fetches the shifted activation rows directly from the channels-last tensor and
 // zero-fills rows outside [0, T) (the conv padding), so no im2col buffer ever exists.
 //
-// Roles (192 threads): warp 0 = TMA producer, warp 1 = tcgen05.mma issuer, warps 2..5 = epilogue
-// (TMEM -> registers -> fused epilogue -> global).  Accumulators live in TMEM (128 lanes x BN columns).
+// Roles (64 + 32 EW threads per CTA, CTA pairs): warp 0 = TMA producer, warp 1 = tcgen05.mma issuer (leader CTA),
+// warps 2.. = EW epilogue warps (8, or 16 for the epilogue-bound K = 512 GEMMs): TMEM -> registers -> fused
+// epilogue -> swizzled smem box -> TMA store.  Accumulators live in TMEM (128 lanes x 2 stages x BN columns).
 #pragma once
 #include <cuda_bf16.h>
 
 #include "ptx.cuh"
 
-// Build-time experiment (python -m serenade_b200.build --variant mc -DSRN_MC=1): BN = 256 GEMMs run as clusters of two
-// CTA pairs with the A operand multicast between them (gemm_mainloop.cuh).
-#ifndef SRN_MC
-#define SRN_MC 0
-#endif
 // -DSRN_TRACE=1: gemm_kernel stamps clock64 at its phase boundaries into GemmParams::trace (8 slots per CTA).
 #ifndef SRN_TRACE
 #define SRN_TRACE 0
@@ -27,7 +23,7 @@
 namespace srn {
 
 enum EpiMode : int {
-  EPI_STORE_F32 = 0,   // out f32 = acc*alpha + bias [, GroupNorm partial sums]
+  EPI_STORE_F32 = 0,   // out f32 = acc*alpha + bias
   EPI_STORE_OT = 1,    // out OT  = (acc + bias) [* rowmask]
   EPI_RESID_F32 = 2,   // out f32 = acc + bias + resid           (in place allowed)
   EPI_RESID_OT = 3,    // out OT  = (acc + bias + resid) [* rowmask]
@@ -39,6 +35,8 @@ enum EpiMode : int {
   EPI_EXP = 8,         // out OT = exp(acc*alpha - rowmax) (0 at masked keys), stat_sum[...] = partial row sums (f32)
   EPI_PV = 9,          // out OT = acc / rowsum
   EPI_RESID_ACT = 10,  // x f32 (mapD) = [resid (mapR) +] acc + bias; second output (mapD2) OT = leaky_relu(x, act_slope)
+  EPI_STORE_GN = 11,   // out OT (bf16, or unrounded f32 in the TF32-class mode) = acc + bias, GroupNorm partial sums
+                       // (sum, sum of squares per 64-channel group and 128-row tile) taken from the f32 accumulators
 };
 
 constexpr int kWinRows = 192;      // rows of an A window (window mode): 128 + the largest shift span
@@ -54,13 +52,13 @@ struct GemmParams {
   CUtensorMap mapA[2];
   CUtensorMap mapB;
   CUtensorMap mapD;    // output tile store: box = 32 rows x 128 bytes, SWIZZLE_128B (all epilogues but EULER)
-  CUtensorMap mapD2;   // EPI_QKV: V^T store, box = 32 (d rows) x 32 (s, contiguous), no swizzle
+  CUtensorMap mapD2;   // EPI_QKV: V^T store, box = 32 (d rows) x 32 (s, contiguous), no swizzle; tile group 1: its output
+  CUtensorMap mapB2;   // tile group 1: its B operand
   CUtensorMap mapR;      // EPI_RESID_OT (2-byte operands): the f32 residual as 32 x 32 boxes, like an f32 mapD
   KSeg seg[24];
   int nseg;
   int nkb;          // total K blocks
   int ntn, ntm, nz; // tile grid: N tiles, M tiles, batch entries (persistent CTAs loop over ntn*ntm*nz tiles)
-  int z0;           // first batch entry of this launch (the attention passes may run a slice of the (batch, head) range)
   int M;            // valid rows per batch entry
   int N;            // valid output columns
   int HB;           // inner batch (heads): blockIdx.z = b * HB + h
@@ -86,10 +84,6 @@ struct GemmParams {
   long long resid_bstride;
   int ldr;
   float* gn_part;   // [B][m_tiles][8][2] partial (sum, sum of squares) per 64-channel group, or null
-  uint8_t* out8;            // EPI_QKV: e4m3 copy of the Q | K columns for the row-max pass [B][rows][ld8], or null
-  long long out8_bstride;
-  int ld8;
-  int ab_fp8;               // host side: launch the Fp8-operand instantiation (EPI_ROWMAX only)
   const uint8_t* gn_mask;   // non-null: only rows with gn_mask[b * mask_bstride + row * mask_step] != 0 enter gn_part
   // EPI_QKV
   int split_n;
@@ -114,8 +108,13 @@ struct GemmParams {
   // Cuts the L2 -> SM operand traffic of a k-tap conv by up to k.  mapA[0] must have kWinRows-row boxes.
   int win;          // 0 = off; 1 = on; 3 = on, descriptors carry the matrix base offset ((addr >> 7) & 7)
   int win_min;      // smallest row shift of the segments (max - min <= kWinRows - 128)
-  int dbg_mode;     // profiling experiments only (SRN_DBG_MODE, srn_profile_ops): bit 0 = no TMA loads, bit 1 = no MMAs,
-                    // bit 2 = no epilogue (results are garbage)
+  // Tile groups: ONE launch for two GEMMs that read the same A tensors (a resnet's k3 conv + its 1x1 res_conv; the two
+  // output parities of the transposed conv).  N tiles [0, grp_ntn0) are group 0 (segments [0, nseg), mapB, mapD, bias,
+  // mask_off), N tiles [grp_ntn0, ntn) group 1 (segments [grp_seg0, grp_seg0 + grp_nseg), mapB2, mapD2, bias2,
+  // mask_off2); both have N columns.  grp_ntn0 = 0: no groups.  GroupNorm partial sums: group 0 only.
+  int grp_ntn0, grp_seg0, grp_nseg, grp_nkb;
+  const float* bias2;
+  int mask_off2;
   // EPI_ROWMAX / EPI_EXP / EPI_PV: per-row softmax statistics, one entry per 64-key slice:
   // stat[(z * stat_n + j) * stat_ld + row], j < stat_n = ceil(keys / 64)
   float* stat_max;
@@ -139,6 +138,7 @@ struct GemmParams {
                     // partial sums are written from the bias (the reference's statistics span the padded frames)
   float* qk_norm2;
   int* noshift;
+  unsigned long long* ns_count;   // EPI_ROWMAX: [0] += shift-free entries, [1] += entries (statistics only), or null
   int nz_norm;      // number of (batch, head) entries of qk_norm2
   float noshift_max; // the bound below which an entry runs shift-free (64; SRN_NOSHIFT_MAX overrides it for tests)
   const uint8_t* keymask;   // (B, keys): key k of batch b takes part iff keymask[b*keymask_bstride + k*keymask_step] != 0
@@ -162,18 +162,6 @@ struct OpTraits<float> {
   static constexpr uint32_t kFmt = 2;
   static constexpr int kBK = 32;
 };
-// FP8 (e4m3) operands: used for ONE thing, the row-max pass of the attention (EPI_ROWMAX).  softmax is invariant to
-// the per-row shift, so the shift only has to be close to the true maximum (no overflow of exp(s - shift), no
-// underflow of the whole row): an e4m3 copy of Q and K gives it at half the operand bytes and twice the MMA rate.
-struct Fp8 { uint8_t v; };
-template <>
-struct OpTraits<Fp8> {
-  static constexpr bool kTF32 = false;
-  static constexpr int kKind = 2;      // kind::f8f6f4, A and B e4m3
-  static constexpr uint32_t kFmt = 0;
-  static constexpr int kBK = 128;
-};
-
 __device__ __forceinline__ float warp_sum_f(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -14,7 +14,7 @@ struct Stager {
   uint32_t base;     // shared address of this warp's 8 KB, 1024-byte aligned
   uint32_t buf;      // which box is being filled
   uint32_t fill;     // bytes of the current 128-byte row already written
-  uint32_t one;      // 1: a single 4 KB box (A-stationary layout) - every fill waits for the previous store's reads
+  uint32_t one;      // 1: a single 4 KB box (16 epilogue warps) - every fill waits for the previous store's reads
   __device__ __forceinline__ uint32_t box() const { return base + buf * 4096; }
 };
 
@@ -57,36 +57,13 @@ __device__ __forceinline__ void stager_put(Stager& s, int lane, const float (&v)
 
 // When the 128-byte rows are complete: store the box.  col = first output column (elements) of the box,
 // row0 = first row, batch = batch coordinate.
-//   default: make the writes visible to the async proxy and issue one TMA bulk store of the 32 x 128 B box;
-//   SRN_DIRECT_STORE: read the box back transposed (conflict-free) and write it with 16-byte st.global, four
-//   full 128-byte lines per warp instruction, rows >= M and columns >= the tensor's extent predicated off.
-#ifndef SRN_DIRECT_STORE
-#define SRN_DIRECT_STORE 0
-#endif
+// The writes are made visible to the async proxy and one lane issues the TMA bulk store of the 32 x 128 B box (a direct
+// st.global epilogue was measured in round 1 and is 2 % slower: the bytes, not the store path, are what costs).
 template <typename OutT>
 __device__ __forceinline__ void stager_flush(Stager& s, int lane, const GemmParams& p, int col, int row0, int batch,
                                              bool reduce_add = false, const CUtensorMap* map = nullptr) {
   if (s.fill < 128) return;
   if (map == nullptr) map = &p.mapD;
-#if SRN_DIRECT_STORE
-  __syncwarp();
-  constexpr int kPiece = 16 / (int)sizeof(OutT);
-  const int pc = lane & 7;
-  const int colp = col + pc * kPiece;
-  const bool col_ok = colp < ((p.out_cols + kPiece - 1) / kPiece) * kPiece;
-  OutT* g = static_cast<OutT*>(p.out) + (long long)batch * (p.d_zbatch ? p.out_hstride : p.out_bstride) + colp;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int r = (lane >> 3) + 4 * j;
-    uint32_t a, b, c, d;
-    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
-                 : "=r"(a), "=r"(b), "=r"(c), "=r"(d)
-                 : "r"(s.box() + r * 128 + ((pc ^ (r & 7)) << 4)));
-    if (col_ok && row0 + r < p.M)
-      *reinterpret_cast<uint4*>(g + (long long)(row0 + r) * p.ldo) = make_uint4(a, b, c, d);
-  }
-  __syncwarp();
-#else
   fence_proxy_async();
   __syncwarp();
   if (lane == 0) {
@@ -105,7 +82,6 @@ __device__ __forceinline__ void stager_flush(Stager& s, int lane, const GemmPara
     }
     tma_store_commit();
   }
-#endif
   if (!s.one) s.buf ^= 1;
   s.fill = 0;
 }

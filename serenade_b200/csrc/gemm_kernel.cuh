@@ -3,11 +3,11 @@
 // CTA pairs (cluster of 2, tcgen05 cta_group::2) loop over 256 x BN output tiles: each CTA of the pair loads its
 // own 128 rows of A and its own half of the B rows by TMA, the leader CTA issues UMMA M=256 for both, and each
 // CTA's TMEM receives the accumulator rows of its own 128 A rows (halves B traffic per CTA; the single-CTA
-// version was bound by L2->SM bandwidth).  320 threads per CTA:
+// version was bound by L2->SM bandwidth).  Per CTA:
 //   warp 0      TMA producer      (smem ring of STAGES x {A 128x128B, B (BN/2)x128B}, SWIZZLE_128B)
 //   warp 1      tcgen05.mma issuer (leader CTA, one elected lane), two TMEM accumulator stages
-//   warps 2..9  epilogue: TMEM -> registers -> fused epilogue -> swizzled smem box -> TMA store, overlapped
-//               with the next tile's main loop through the tmem_full / tmem_empty barriers
+//   warps 2..   epilogue (8 or 16 warps): TMEM -> registers -> fused epilogue -> swizzled smem box -> TMA store,
+//               overlapped with the next tile's main loop through the tmem_full / tmem_empty barriers
 // The epilogue mode is a template parameter: ncu showed the epilogue warps latency-bound on ~520 instructions
 // per 32-column chunk when the mode was a runtime switch with per-element predicates.
 #pragma once
@@ -16,65 +16,49 @@
 
 namespace srn {
 
-// AS = A-stationary layout (gemm_mainloop.cuh): the whole K extent of this CTA's 128 A rows stays in shared memory
-// while the pair sweeps the N tiles of that row block (K <= 8 blocks), B streams through a ring; the epilogue warps
-// get ONE staging box each instead of two to make room.
-constexpr int kAsOpBytes = 176 * 1024;    // A slots (8 x 16 KB at most) + B ring
-template <int BN, bool AS = false>
+// EW = number of epilogue warps (8 or 16).  Sixteen (four per scheduler, each draining 64 accumulator columns of its
+// lane quarter) is for the K = 512 GEMMs whose epilogue, not the tensor pipe, bounds the tile loop: with two warps per
+// scheduler the per-chunk dependency chain (TMEM load -> convert -> stage -> store) has nothing to hide behind.  The
+// sixteen-warp form has ONE staging box per warp (same 64 KB in total) and fits 112 registers per thread.
+template <int BN, int EW = 8>
 struct GemmCfg {
+  static_assert(EW == 8 || (EW == 16 && BN == 256), "8 epilogue warps, or 16 on 256-column tiles");
   static constexpr int kStages = BN == 256 ? 4 : 5;
   static constexpr int kABytes = 128 * 128;            // this CTA's 128 rows of the pair's 256-row A tile
   static constexpr int kBBytes = (BN / 2) * 128;       // this CTA's half of the B tile's BN rows
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kOpBytes = AS ? kAsOpBytes : kStages * kStageBytes;
-  static constexpr int kStgWarp = AS ? 4096 : 8192;           // staging bytes per epilogue warp
-  static constexpr int kStgOff = kOpBytes;                    // epilogue staging: 8 warps x kStgWarp
-  static constexpr int kBarOff = kStgOff + 8 * kStgWarp;      // barriers + tmem slot (256 B)
+  static constexpr int kOpBytes = kStages * kStageBytes;
+  static constexpr int kSlices = EW / 4;                      // column slices of a tile (one epilogue warp per lane quarter each)
+  static constexpr int kChunksPerWarp = (BN / 32) / kSlices;  // 32-column chunks per epilogue warp and tile
+  static constexpr int kStgWarp = EW == 8 ? 8192 : 4096;      // staging bytes per epilogue warp (two boxes / one box)
+  static constexpr int kStgOff = kOpBytes;                    // epilogue staging: EW warps x kStgWarp = 64 KB
+  static constexpr int kBarOff = kStgOff + EW * kStgWarp;     // barriers + tmem slot (256 B)
   static constexpr int kRedOff = kBarOff + 256;               // GroupNorm partial reduction scratch (256 B)
-  static constexpr int kBiasOff = kRedOff + 256;              // per epilogue warp: its bias slice (8 x 512 B)
-  static constexpr int kWinBarOff = kBiasOff + 8 * 512;       // window mode / A-stationary mode: their own barriers (256 B)
+  static constexpr int kBiasOff = kRedOff + 256;              // per epilogue warp: its bias slice (4 x BN floats in all)
+  static constexpr int kWinBarOff = kBiasOff + 8 * 512;       // window mode: its own barriers (256 B)
   static constexpr int kSmemBytes = kWinBarOff + 256 + 1024;  // + alignment slack
   // window mode re-partitions the operand stages: two A windows, the rest is a ring of B stages
   static constexpr int kWinABytes = kWinRows * 128;
   static constexpr int kWinBStages = (kStages * kStageBytes - 2 * kWinABytes) / kBBytes;
   static_assert(kWinBStages >= 3 && 4 + 2 * kWinBStages <= 32, "window-mode barriers fit their 256 bytes");
-  static constexpr int kThreads = 320;
+  static constexpr int kThreads = 64 + 32 * EW;
   static constexpr int kTmemCols = 2 * BN;
   static_assert(kStgOff % 1024 == 0, "staging boxes must be 1024-byte aligned for SWIZZLE_128B");
   static_assert(kSmemBytes <= 227 * 1024, "shared memory per CTA");
 };
 
-// Build-time experiment (-DSRN_EXP2_FMA=1): every other exponential of the EPI_EXP epilogue on the FMA pipes.
-// Measured on one box: 301 us vs 288 us per call for the six expscores launches - the MUFU is not what bounds that
-// epilogue - so it is off.
-#ifndef SRN_EXP2_FMA
-#define SRN_EXP2_FMA 0
-#endif
 #ifndef SRN_KEY_FASTPATH
 #define SRN_KEY_FASTPATH 1
 #endif
-// 2^x without the special-function unit: round-to-nearest split x = n + f through the 1.5 * 2^23 trick (n lands in the
-// low mantissa bits of t), degree-4 near-minimax polynomial for 2^f on [-0.5, 0.5] (max relative error 3.6e-6 in f32
-// evaluation), exponent added as an integer.  x is clamped to >= -125 (result 2^-125 instead of 0: irrelevant next to a
-// row whose largest term is about 1) and must stay below 127 (the shift is within a few units of the row maximum).
-__device__ __forceinline__ float exp2_fma(float x) {
-  x = fmaxf(x, -125.0f);
-  const float t = x + 12582912.0f;
-  const float f = x - (t - 12582912.0f);
-  float pz = fmaf(0.00966636836528778f, f, 0.055921975523233414f);
-  pz = fmaf(pz, f, 0.2402234971523285f);
-  pz = fmaf(pz, f, 0.6931210160255432f);
-  pz = fmaf(pz, f, 1.0f);
-  return __int_as_float(__float_as_int(pz) + (__float_as_int(t) << 23));
-}
 
 // One 32-column chunk of one accumulator row (bias / alpha already applied to v).
 // Softmax modes: `racc` is this thread's running row max (ROWMAX) or row sum (EXP), `rowc` the row constant
 // (EXP: rowmax * log2 e, PV: 1 / rowsum), `keybits` bit i = key column nc + i takes part.
 template <typename OT, int EPI>
-__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[32], Stager& st, int lane, int b, int h,
-                                               int z, int row, int row0, int nc, bool row_ok, float mk, float& gs,
-                                               float& gss, float& racc, float rowc, uint32_t keybits, bool gn_ok) {
+__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const CUtensorMap* dmap, float (&v)[32], Stager& st,
+                                               int lane, int b, int h, int z, int row, int row0, int nc, bool row_ok,
+                                               float mk, float& gs, float& gss, float& racc, float rowc,
+                                               uint32_t keybits, bool gn_ok) {
   const int batch = p.d_zbatch ? z : b;
   constexpr int kOtCols = 128 / (int)sizeof(OT);     // output columns per 128-byte staging row
   // fp32-stored operand tensors are consumed as TF32: round to nearest here (the tensor core truncates)
@@ -89,13 +73,20 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     }
   };
   if constexpr (EPI == EPI_STORE_F32) {
-    if (p.gn_part != nullptr && gn_ok) {
+    stager_acquire(st, lane);
+    stager_put<float, 32>(st, lane, v);
+    stager_flush<float>(st, lane, p, nc + h * p.d_hcol, row0, batch);
+  } else if constexpr (EPI == EPI_STORE_GN) {
+    // conv output that feeds a GroupNorm: statistics from the f32 accumulators (gn_ok: this row and tile group enter
+    // them), the tensor itself in operand width - half the bytes here and in the row kernel that applies the norm; it
+    // is not a GEMM operand, so the TF32-class mode keeps it unrounded f32
+    if (gn_ok) {
 #pragma unroll
       for (int i = 0; i < 32; ++i) { gs += v[i]; gss = fmaf(v[i], v[i], gss); }
     }
     stager_acquire(st, lane);
-    stager_put<float, 32>(st, lane, v);
-    stager_flush<float>(st, lane, p, nc + h * p.d_hcol, row0, batch);
+    stager_put<OT, 32>(st, lane, v);
+    stager_flush<OT>(st, lane, p, nc + 32 - kOtCols, row0, batch, false, dmap);
   } else if constexpr (EPI == EPI_STORE_OT) {
     if (p.act_slope != 1.0f) {
 #pragma unroll
@@ -106,9 +97,9 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     round_op(v);
     stager_acquire(st, lane);
     stager_put<OT, 32>(st, lane, v);
-    stager_flush<OT>(st, lane, p, nc + 32 - kOtCols + h * p.d_hcol, row0, batch);
+    stager_flush<OT>(st, lane, p, nc + 32 - kOtCols + h * p.d_hcol, row0, batch, false, dmap);
   } else if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_RESID_OT) {     // RESID_OT: residual already added by the caller
-    if constexpr (EPI == EPI_RESID_OT && sizeof(OT) == 2 && !SRN_DIRECT_STORE) {
+    if constexpr (EPI == EPI_RESID_OT && sizeof(OT) == 2) {
       // one output box only (the warp's other box receives the residual, gemm_mainloop.cuh: kResidTma)
       if (st.fill == 0) {
         if (lane == 0) tma_store_wait_read<0>();
@@ -119,7 +110,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     }
     if constexpr (EPI == EPI_RESID_F32) {      // out and residual are the same f32 tensor: TMA reduce-add in place
       stager_put<float, 32>(st, lane, v);
-      stager_flush<float>(st, lane, p, nc, row0, batch, !SRN_DIRECT_STORE);
+      stager_flush<float>(st, lane, p, nc, row0, batch, true);
     } else {
       // (a select, not a product: with padded-frame skipping the rows of padded frames may hold stale data upstream,
       //  and 0 * NaN would carry a NaN of an earlier call into the next convolution's operand)
@@ -128,7 +119,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
       round_op(v);
       stager_put<OT, 32>(st, lane, v);
       stager_flush<OT>(st, lane, p, nc + 32 - kOtCols, row0, batch);
-      if constexpr (sizeof(OT) == 2 && !SRN_DIRECT_STORE) st.buf = 0;
+      if constexpr (sizeof(OT) == 2) st.buf = 0;
     }
   } else if constexpr (EPI == EPI_RESID_ACT) {
     // v is the updated f32 stream (the caller added the residual and stored it from the residual box): emit its
@@ -165,23 +156,6 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
 #pragma unroll
       for (int i = 0; i < 32; ++i) gs = fmaf(v[i], v[i], gs);
     }
-    if (nc < p.split_n && p.out8 != nullptr && row_ok) {
-      // e4m3 copy of Q | K for the row-max pass, 32 bytes per lane and chunk straight to global memory (staging it
-      // through a TMA box was measured and is slower: it needs the chunk loop unrolled and a third box)
-      uint32_t w[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        uint16_t lo, hi;
-        asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(lo) : "f"(v[4 * i + 1]), "f"(v[4 * i + 0]));
-        asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(hi) : "f"(v[4 * i + 3]), "f"(v[4 * i + 2]));
-        w[i] = (uint32_t)lo | ((uint32_t)hi << 16);
-      }
-      // one 256-bit store per lane (STG.256, sm_100): a whole 32-byte sector at once instead of two half-sector writes
-      uint8_t* g8 = p.out8 + (long long)batch * p.out8_bstride + (long long)row * p.ld8 + nc;
-      asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(g8), "r"(w[0]), "r"(w[1]), "r"(w[2]),
-                   "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
-                   : "memory");
-    }
     if (nc < p.split_n) {
       stager_acquire(st, lane);
       stager_put<OT, 32>(st, lane, v);
@@ -208,7 +182,8 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
     // proven within +-64), it only keeps the garbage rows of PADDED query frames finite in the shift-free case (their
     // norms do not enter the test, so that a clip's decision does not depend on the padding its batch gives it)
     constexpr float kExpArgMax = 92.332482f;
-    // (32768 exponentials per CTA and tile = 2048 clocks of MUFU.EX2; see SRN_EXP2_FMA above)
+    // (32768 exponentials per CTA and tile = 2048 clocks of MUFU.EX2; moving every other one to the FMA pipes was
+    //  measured and is no faster: the MUFU is not what bounds this epilogue)
     const float sc = p.alpha * 1.4426950408889634f;
     if (SRN_KEY_FASTPATH && keybits == 0xffffffffu) {
       // all 32 keys take part (every chunk but a row's last ones and padded batches): no per-element select, and the
@@ -233,8 +208,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&v)[3
         for (int k = 0; k < 4; ++k) {
           float e;
           const float x = fminf(fmaf(v[i + k], sc, -rowc), kExpArgMax);
-          if (SRN_EXP2_FMA && (k & 1)) e = exp2_fma(x);
-          else asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x));
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x));
           v[i + k] = ((keybits >> (i + k)) & 1u) ? e : 0.f;
         }
         s0 += v[i]; s1 += v[i + 1]; s2 += v[i + 2]; s3 += v[i + 3];

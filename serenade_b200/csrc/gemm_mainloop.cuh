@@ -1,17 +1,14 @@
 // The __global__ kernel: role dispatch, TMA/MMA pipelines, epilogue tile loop.  Included by gemm_kernel.cuh.
+//
+// Variants that were built, measured on the B200 and NOT kept (round 1; the numbers are in DESIGN.md 3.4 and under
+// profiles/r01_ab_*.txt, the code is in the git history before this file's round-2 rewrite): A-operand multicast over
+// four-CTA clusters (only 132 of 148 SMs can hold 4-CTA clusters: no gain), an A-stationary tile order for the K = 512
+// GEMMs (half the operand bytes, yet slower), attention passes in (batch, head) slices, exp2 on the FMA pipes, direct
+// st.global epilogue stores.
 #pragma once
 
 namespace srn {
 
-// MC = A-operand multicast: clusters of FOUR CTAs = two CTA pairs that work on the same 256 output rows and on
-// adjacent N tiles.  The CTAs with the same rank inside their pair need the same 128 rows of A: each loads 64 of them
-// and multicasts to both (cp.async.bulk.tensor ... .cta_group::2 ... .multicast::cluster; the bytes complete on the
-// full barrier of the destination's own pair leader), which removes a quarter of the operand traffic of every k-block
-// (the SM<->L2 fabric, not the tensor pipe, bounds this kernel: DESIGN.md 3.1).  A stage is free when BOTH pairs have
-// consumed it (empty barriers count two commits, multicast to all four CTAs).
-#ifndef SRN_ONEBOX
-#define SRN_ONEBOX 0      // experiment: single staging box per epilogue warp in the default layout too
-#endif
 #ifndef SRN_EPI_PREFETCH
 #define SRN_EPI_PREFETCH 1
 #endif
@@ -21,21 +18,18 @@ namespace srn {
 #define SRN_STAMP(k) do { } while (0)
 #endif
 
-// AS = A-stationary (K <= 8 blocks, one K segment, several N tiles per row block; QKV / GEGLU / Q K^T): every K = 512
-// GEMM of the step sat at the SM<->L2 wall (clock64 trace: 7.0 - 8.3 k clocks per 256 x 256 tile against 4.1 k of MMA
-// time, 256 KB of operands per CTA and tile).  Here a pair owns a CONTIGUOUS range of tiles, N fastest; the A rows of
-// a row block are loaded once into K-block slots that stay put while B streams through a ring (half the operand bytes
-// per tile).  Slot kb is refilled for the next row block as soon as the last N tile's MMAs on it have committed.
-template <typename OT, int BN, int EPI, bool MC, bool AS = false>
-__global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
+template <typename OT, int BN, int EPI, int EW = 8>
+__global__ void __launch_bounds__(64 + 32 * EW, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
   using TR = OpTraits<OT>;
-  using CFG = GemmCfg<BN, AS>;
-  static_assert(!AS || (!MC && (EPI == EPI_QKV || EPI == EPI_GEGLU || EPI == EPI_ROWMAX || EPI == EPI_EXP)),
-                "A-stationary layout: single-box epilogues only");
+  using CFG = GemmCfg<BN, EW>;
   constexpr int STAGES = CFG::kStages;
   constexpr int BK = TR::kBK;
-  constexpr int NCH = BN / 32;          // 32-column chunks per tile
-  constexpr int NG = BN / 64;           // GroupNorm groups per tile
+  constexpr int NCH = BN / 32;                  // 32-column chunks per tile
+  constexpr int CPW = CFG::kChunksPerWarp;      // ... per epilogue warp
+  constexpr int NG = BN / 64;                   // GroupNorm groups per tile
+  // epilogues that need the warp's second staging box for the residual keep eight warps
+  static_assert(EW == 8 || !(EPI == EPI_RESID_OT || EPI == EPI_RESID_ACT || EPI == EPI_EULER || EPI == EPI_GEGLU),
+                "sixteen epilogue warps: one staging box per warp, two chunks per 128-byte staging row");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -53,29 +47,14 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  constexpr int CL = MC ? 4 : 2;                 // CTAs per cluster
-  const int ntn_u = MC ? (p.ntn + 1) / 2 : p.ntn;   // work units along N: single tiles, or pairs of adjacent tiles
-  const int tiles_mn = ntn_u * p.ntm;
-  const int total_tiles = tiles_mn * p.nz;       // units of work per cluster
-  const uint32_t crank = cluster_ctarank();
-  const uint32_t rank = crank & 1u;              // rank inside the CTA pair, 0 = leader (issues the MMAs)
-  const uint32_t pj = MC ? (crank >> 1) : 0u;    // which pair of the cluster: N tile 2 u + pj
-  const uint32_t leader = crank & ~1u;           // cluster rank of this pair's leader
-  const int pair0 = blockIdx.x / CL;
-  const int npairs = gridDim.x / CL;
-  // tiles of this pair: pair0, pair0 + npairs, ... (default) or one contiguous range (AS)
-  int t_begin = pair0, t_end = total_tiles, t_step = npairs;
-  if constexpr (AS) {
-    const int tq = total_tiles / npairs, tr = total_tiles - tq * npairs;
-    t_begin = pair0 * tq + (pair0 < tr ? pair0 : tr);
-    t_end = t_begin + tq + (pair0 < tr ? 1 : 0);
-    t_step = 1;
-  }
-  uint64_t* as_a_full = wa_full;            // AS: [8] A K-block slots (shares the window-mode barrier block)
-  uint64_t* as_a_empty = as_a_full + 8;
-  uint64_t* as_b_full = as_a_empty + 8;     // [<= 8] B ring
-  uint64_t* as_b_empty = as_b_full + 8;
-  const int as_nb = AS ? min(8, (CFG::kOpBytes - p.nkb * CFG::kABytes) / CFG::kBBytes) : 0;
+  const int tiles_mn = p.ntn * p.ntm;
+  const int total_tiles = tiles_mn * p.nz;       // units of work per CTA pair
+  const uint32_t rank = cluster_ctarank() & 1u;  // rank inside the CTA pair, 0 = leader (issues the MMAs)
+  constexpr uint32_t leader = 0;
+  const int pair0 = blockIdx.x / 2;
+  const int npairs = gridDim.x / 2;
+  // tiles of this pair: pair0, pair0 + npairs, ...
+  const int t_begin = pair0, t_end = total_tiles, t_step = npairs;
 
   pdl_launch_dependents();
   if (threadIdx.x == 0) SRN_STAMP(0);
@@ -85,20 +64,19 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
     tma_prefetch_desc(&p.mapB);
     tma_prefetch_desc(&p.mapD);
     if (EPI == EPI_RESID_OT && sizeof(OT) == 2) tma_prefetch_desc(&p.mapR);
+    if (p.grp_ntn0 > 0) { tma_prefetch_desc(&p.mapB2); tma_prefetch_desc(&p.mapD2); }
   }
   if (warp == 1 && elect_one()) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], MC ? 2 : 1);
+      mbar_init(&empty_bar[s], 1);
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 16);    // one arrival per epilogue warp of both CTAs (leader's copy is used)
+      mbar_init(&tempty_bar[s], 2 * EW);    // one arrival per epilogue warp of both CTAs (leader's copy is used)
     }
     for (int s = 0; s < 8; ++s) mbar_init(&resid_bar[s], 1);
-    if constexpr (AS) {
-      for (int s = 0; s < 32; ++s) mbar_init(&as_a_full[s], 1);
-    } else if (p.win) {
+    if (p.win) {
       for (int s = 0; s < 2; ++s) { mbar_init(&wa_full[s], 1); mbar_init(&wa_empty[s], 1); }
       for (int s = 0; s < CFG::kWinBStages; ++s) { mbar_init(&wb_full[s], 1); mbar_init(&wb_empty[s], 1); }
     }
@@ -109,12 +87,9 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   // a fully serialised one (engine_run.inl: prepass), so no later kernel can even start before the extents are final.
   // (made visible to all warps by the cluster barrier below; host side guarantees <= 256 entries)
   __shared__ int s_ext[256];
-  const bool use_ext = !AS && p.row_extent != nullptr;
+  const bool use_ext = p.row_extent != nullptr;
   if (use_ext) {
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
-      const int bb = p.z0 / p.HB + i;
-      s_ext[i] = bb * p.HB < p.z0 + p.nz ? __ldcg(p.row_extent + bb) : 0;
-    }
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) s_ext[i] = i * p.HB < p.nz ? __ldcg(p.row_extent + i) : 0;
   }
   if (warp == 2) tmem_alloc_2sm<CFG::kTmemCols>(tmem_slot);
   tc_fence_before();
@@ -124,7 +99,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
   pdl_wait();     // everything above overlapped with the previous kernel's tail
   if (threadIdx.x == 0) SRN_STAMP(1);
   // Shift-free softmax, decided per (batch, head) entry z (so a clip's result never depends on what else is in the
-  // batch): s_ns[z - z0] != 0 means every score of that entry is provably within +-64 - its row-max tiles are skipped
+  // batch): s_ns[z] != 0 means every score of that entry is provably within +-64 - its row-max tiles are skipped
   // and its exp tiles run with shift 0.
   __shared__ uint8_t s_ns[(EPI == EPI_ROWMAX || EPI == EPI_EXP) ? 1024 : 4];
   if constexpr (EPI == EPI_ROWMAX) {
@@ -146,33 +121,35 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         ok = bound <= p.noshift_max ? 1 : 0;                    // (NaN / Inf fail the test)
         if (blockIdx.x == 0) p.noshift[z] = ok;                 // for the exp pass
       }
+      if (blockIdx.x == 0 && p.ns_count != nullptr) {           // (statistics for srn_softmax_stats)
+        if (ok) atomicAdd(p.ns_count, 1ull);
+        atomicAdd(p.ns_count + 1, 1ull);
+      }
       s_ns[z] = ok;
     }
     __syncthreads();
   }
   if constexpr (EPI == EPI_EXP) {
     for (int z = threadIdx.x; z < p.nz && z < 1024; z += blockDim.x)
-      s_ns[z] = p.noshift != nullptr ? (uint8_t)(*reinterpret_cast<const volatile int*>(p.noshift + p.z0 + z)) : (uint8_t)0;
-    if (p.qk_norm2 != nullptr && blockIdx.x == 0 && p.z0 == 0)     // the row-max pass has read the maxima: clear them
+      s_ns[z] = p.noshift != nullptr ? (uint8_t)(*reinterpret_cast<const volatile int*>(p.noshift + z)) : (uint8_t)0;
+    if (p.qk_norm2 != nullptr && blockIdx.x == 0)     // the row-max pass has read the maxima: clear them
       for (int i = threadIdx.x; i < p.nz_norm * 16; i += blockDim.x) p.qk_norm2[i] = 0.f;
     __syncthreads();
   }
-  // (row-max pass: tiles of shift-free entries are skipped by all three roles; not in the A-stationary experiment,
-  //  whose slot bookkeeping assumes every tile is visited - there the pass simply runs)
+  // (row-max pass: tiles of shift-free entries are skipped by all three roles)
   auto skip_tile = [&](int z) -> bool {
-    if constexpr (EPI == EPI_ROWMAX && !AS) return p.qk_norm2 != nullptr && s_ns[z - p.z0] != 0;     // (null beyond 1024 entries)
+    if constexpr (EPI == EPI_ROWMAX) return p.qk_norm2 != nullptr && s_ns[z] != 0;     // (null beyond 1024 entries)
     else return false;
   };
-  // Padded-frame skipping: extents of the batch entries of this launch (host side guarantees <= 256 of them, no AS)
-  const int b_first = p.z0 / p.HB;
+  // Padded-frame skipping: extents of the batch entries of this launch (host side guarantees <= 256 of them)
   // (b = batch entry, mi / ni = row / column tile inside the entry: the callers have them anyway - integer divisions
   //  by run-time values are ~150-clock dependent chains, and the epilogue warps' per-tile chain is what bounds the
   //  K = 512 GEMMs)
-  auto tile_ext = [&](int b) -> int { return use_ext ? s_ext[b - b_first] : 0x7fffffff; };
+  auto tile_ext = [&](int b) -> int { return use_ext ? s_ext[b] : 0x7fffffff; };
   auto skip_pad = [&](int ext, int mi, int ni) -> bool {
     if (!use_ext) return false;
-    if (mi * 256 >= ext + p.ext_halo) return true;                                // the pair's 256 rows are all padding
-    return p.ext_keys == 1 && (ni * (MC ? 2 : 1)) * BN >= ext;                     // ... or all its keys are
+    if (mi * 256 >= ext + p.ext_halo) return true;        // the pair's 256 rows are all padding
+    return p.ext_keys == 1 && ni * BN >= ext;              // ... or all its keys are
   };
   // Tile coordinates kept incrementally (tile -> tile + t_step) for the MMA-issuing lane: three run-time integer
   // divisions per tile in front of its MMAs cost the mainloop-bound launches ~450 clocks per tile.
@@ -196,57 +173,25 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       z += a;
     }
   };
-  auto tile_nkb = [&](int ext) -> int {       // P~ V: K blocks up to the extent
-    if (use_ext && p.ext_keys == 2) { const int n = (ext + BK - 1) / BK; return n < p.nkb ? n : p.nkb; }
+  auto tile_nkb = [&](int ext, bool g1) -> int {
+    if (g1) return p.grp_nkb;
+    if (use_ext && p.ext_keys == 2) { const int n = (ext + BK - 1) / BK; return n < p.nkb ? n : p.nkb; }   // P~ V: K blocks up to the extent
     return p.nkb;
   };
+  auto in_group1 = [&](int ni) -> bool { return p.grp_ntn0 > 0 && ni >= p.grp_ntn0; };
 
   if (warp == 0) {
     if (elect_one()) {
       // ------------------------------------------------------------ TMA producer
       uint32_t stage = 0, phase = 0;
-      if constexpr (AS) {
-        uint32_t bs = 0, bph = 0, agen = 0;
-        int cur = -1;
-        const KSeg sg = p.seg[0];
-        uint8_t* sb0 = smem + p.nkb * CFG::kABytes;
-        for (int tile = t_begin; tile < t_end; ++tile) {
-          const int z = tile / tiles_mn + p.z0;
-          const int rem = tile % tiles_mn;
-          const int m0 = (rem / ntn_u) * 256 + (int)rank * 128;
-          const int n0 = (rem % ntn_u) * BN;
-          const int b = z / p.HB;
-          const int h = z - b * p.HB;
-          const int a_batch = p.a_zbatch ? z : b;
-          const int b_batch = p.b_batch_mode == 0 ? 0 : (p.b_batch_mode == 1 ? b : z);
-          const int b_row = n0 + (int)rank * (BN / 2) + h * p.b_hrow;
-          const int akey = tile / ntn_u;
-          const bool newa = akey != cur;
-          cur = akey;
-          for (int kb = 0; kb < p.nkb; ++kb) {
-            if (newa) {      // (slot kb was released by the previous row block's last tile)
-              mbar_wait(&as_a_empty[kb], (agen & 1) ^ 1);
-              if (rank == 0) mbar_expect_tx(&as_a_full[kb], 2 * CFG::kABytes);
-              tma_load_3d_2sm(smem + kb * CFG::kABytes, &p.mapA[sg.src], map_to_cta(&as_a_full[kb], leader),
-                              sg.col0 + kb * BK + h * p.a_hcol, m0 + sg.shift, a_batch);
-            }
-            mbar_wait(&as_b_empty[bs], bph ^ 1);
-            if (rank == 0) mbar_expect_tx(&as_b_full[bs], 2 * CFG::kBBytes);
-            tma_load_3d_2sm(sb0 + bs * CFG::kBBytes, &p.mapB, map_to_cta(&as_b_full[bs], leader),
-                            p.b_col0 + kb * BK + h * p.b_hcol, b_row, b_batch);
-            if (++bs == (uint32_t)as_nb) { bs = 0; bph ^= 1; }
-          }
-          if (newa) ++agen;
-        }
-      } else
-      if (!MC && p.win) {
+      if (p.win) {
         // window mode: per K block one A window (all the segments' rows) + one B box per segment
         uint32_t wa = 0, wap = 0, wb = 0, wbp = 0;
         const int kcb = p.seg[0].nblk;
         for (int tile = t_begin; tile < t_end; tile += t_step) {
-          const int z = tile / tiles_mn + p.z0;
+          const int z = tile / tiles_mn;
           const int rem = tile % tiles_mn;
-          const int mi = rem / ntn_u, ni = rem - mi * ntn_u;
+          const int mi = rem / p.ntn, ni = rem - mi * p.ntn;
           const int b = z / p.HB;
           if (skip_pad(tile_ext(b), mi, ni)) continue;
           const int m0 = mi * 256 + (int)rank * 128;
@@ -270,50 +215,38 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
             }
           }
         }
-      } else      // (the per-segment boxes of the plain path follow as the else branch)
-      for (int tile = t_begin; tile < t_end; tile += t_step) {
-        const int z = tile / tiles_mn + p.z0;
-        if (skip_tile(z)) continue;
-        const int rem = tile % tiles_mn;
-        const int mi = rem / ntn_u, ni = rem - mi * ntn_u;
-        const int b = z / p.HB;
-        const int ext = tile_ext(b);
-        if (skip_pad(ext, mi, ni)) continue;
-        const int nkb_t = tile_nkb(ext);
-        const int m0 = mi * 256 + (int)rank * 128;
-        const int n0 = (ni * (MC ? 2 : 1) + (int)pj) * BN;     // may lie beyond N for the odd last unit (all zero)
-        const int h = z - b * p.HB;
-        const int a_batch = p.a_zbatch ? z : b;
-        const int b_batch = p.b_batch_mode == 0 ? 0 : (p.b_batch_mode == 1 ? b : z);
-        const int b_row = n0 + (int)rank * (BN / 2) + h * p.b_hrow;
-        int seg = 0, j = 0;
-        for (int kb = 0; kb < nkb_t; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* sa = smem + stage * CFG::kStageBytes;
-          uint8_t* sb = sa + CFG::kABytes;
-          // both CTAs' bytes complete on the pair LEADER's full barrier; only the leader arms it (for both)
-          const uint32_t fb = map_to_cta(&full_bar[stage], leader);
-          const KSeg sg = p.seg[seg];
-          if (p.dbg_mode & 1) {          // profiling experiment: no operand traffic (results are garbage)
-            if (rank == 0) mbar_arrive(&full_bar[stage]);
-          } else {
+      } else {      // (the per-segment boxes of the plain path)
+        for (int tile = t_begin; tile < t_end; tile += t_step) {
+          const int z = tile / tiles_mn;
+          if (skip_tile(z)) continue;
+          const int rem = tile % tiles_mn;
+          const int mi = rem / p.ntn, ni = rem - mi * p.ntn;
+          const int b = z / p.HB;
+          const int ext = tile_ext(b);
+          if (skip_pad(ext, mi, ni)) continue;
+          const bool g1 = in_group1(ni);
+          const int nkb_t = tile_nkb(ext, g1);
+          const int m0 = mi * 256 + (int)rank * 128;
+          const int n0 = (g1 ? ni - p.grp_ntn0 : ni) * BN;     // row of this tile group's B operand
+          const CUtensorMap* mB = g1 ? &p.mapB2 : &p.mapB;
+          const int h = z - b * p.HB;
+          const int a_batch = p.a_zbatch ? z : b;
+          const int b_batch = p.b_batch_mode == 0 ? 0 : (p.b_batch_mode == 1 ? b : z);
+          const int b_row = n0 + (int)rank * (BN / 2) + h * p.b_hrow;
+          int seg = g1 ? p.grp_seg0 : 0, j = 0;
+          for (int kb = 0; kb < nkb_t; ++kb) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            uint8_t* sa = smem + stage * CFG::kStageBytes;
+            uint8_t* sb = sa + CFG::kABytes;
+            // both CTAs' bytes complete on the pair LEADER's full barrier; only the leader arms it (for both)
+            const uint32_t fb = map_to_cta(&full_bar[stage], leader);
+            const KSeg sg = p.seg[seg];
             if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * CFG::kStageBytes);
-            if constexpr (MC) {
-              // my half (64 rows) of this pair-rank's 128 A rows, to me and to the same-rank CTA of the other pair
-              tma_load_3d_2sm_mc(sa + pj * (CFG::kABytes / 2), &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol,
-                                 m0 + (int)pj * 64 + sg.shift, a_batch, (uint16_t)((1u << rank) | (1u << (rank + 2))));
-            } else {
-              tma_load_3d_2sm(sa, &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol, m0 + sg.shift, a_batch);
-#if SRN_MC
-              // builds with the multicast kernels encode every A map with 64-row boxes
-              tma_load_3d_2sm(sa + CFG::kABytes / 2, &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol,
-                              m0 + 64 + sg.shift, a_batch);
-#endif
-            }
-            tma_load_3d_2sm(sb, &p.mapB, fb, p.b_col0 + kb * BK + h * p.b_hcol, b_row, b_batch);
+            tma_load_3d_2sm(sa, &p.mapA[sg.src], fb, sg.col0 + j * BK + h * p.a_hcol, m0 + sg.shift, a_batch);
+            tma_load_3d_2sm(sb, mB, fb, p.b_col0 + kb * BK + h * p.b_hcol, b_row, b_batch);
+            if (++j == sg.nblk) { j = 0; ++seg; }
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
-          if (++j == sg.nblk) { j = 0; ++seg; }
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -323,48 +256,16 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       constexpr uint32_t idesc = make_idesc(TR::kFmt, 256, BN);
       uint32_t stage = 0, phase = 0;
       uint32_t it = 0;
-      if constexpr (AS) {
-        uint32_t bs = 0, bph = 0, agen = 0;
-        int cur = -1;
-        const uint32_t sa0 = smem_u32(smem);
-        const uint32_t sb0 = sa0 + (uint32_t)(p.nkb * CFG::kABytes);
-        for (int tile = t_begin; tile < t_end; ++tile, ++it) {
-          const int akey = tile / ntn_u;
-          const bool newa = akey != cur;
-          cur = akey;
-          const bool lasta = tile + 1 == t_end || (tile + 1) / ntn_u != akey;
-          const uint32_t as = it & 1;
-          mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
-          tc_fence_after();
-          const uint32_t tacc = tmem_base + as * BN;
-          for (int kb = 0; kb < p.nkb; ++kb) {
-            if (newa) mbar_wait(&as_a_full[kb], agen & 1);
-            mbar_wait(&as_b_full[bs], bph);
-            tc_fence_after();
-            if (it == 0 && kb == 0) SRN_STAMP(2);
-            const uint64_t da = make_kmajor_sw128_desc(sa0 + (uint32_t)(kb * CFG::kABytes));
-            const uint64_t db = make_kmajor_sw128_desc(sb0 + bs * (uint32_t)CFG::kBBytes);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) umma_pair<TR::kKind>(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-            tc_commit_mask(&as_b_empty[bs], 0x3);
-            if (lasta) tc_commit_mask(&as_a_empty[kb], 0x3);     // the next row block may overwrite this slot
-            if (++bs == (uint32_t)as_nb) { bs = 0; bph ^= 1; }
-          }
-          tc_commit_mask(&tfull_bar[as], (uint16_t)(0x3u << leader));
-          SRN_STAMP(3);
-          if (newa) ++agen;
-        }
-      } else
-      if (!MC && p.win) {
+      TileCoord tc;
+      tc.init(t_begin, t_step, p.ntn, p.ntm);
+      int cur_z = -1, cur_ext = 0x7fffffff;
+      if (p.win) {
         uint32_t wa = 0, wap = 0, wb = 0, wbp = 0;
         const int kcb = p.seg[0].nblk;
         const bool boff = (p.win & 2) != 0;
-        TileCoord tc;
-        tc.init(t_begin, t_step, ntn_u, p.ntm);
-        int cur_z = -1, cur_ext = 0x7fffffff;
         for (int tile = t_begin; tile < t_end; tile += t_step, ++it, tc.advance()) {
           if (use_ext) {
-            if (tc.z != cur_z) { cur_z = tc.z; cur_ext = tile_ext((tc.z + p.z0) / p.HB); }
+            if (tc.z != cur_z) { cur_z = tc.z; cur_ext = tile_ext(tc.z / p.HB); }
             if (skip_pad(cur_ext, tc.mi, tc.ni)) { --it; continue; }
           }
           const uint32_t as = it & 1;
@@ -389,94 +290,93 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
             tc_commit_mask(&wa_empty[wa], 0x3);
             if (++wa == 2) { wa = 0; wap ^= 1; }
           }
-          tc_commit_mask(&tfull_bar[as], (uint16_t)(0x3u << leader));
+          tc_commit_mask(&tfull_bar[as], 0x3);
         }
       } else {    // (plain path)
-      TileCoord tc;
-      tc.init(t_begin, t_step, ntn_u, p.ntm);
-      int cur_z = -1, cur_ext = 0x7fffffff;
-      for (int tile = t_begin; tile < t_end; tile += t_step, ++it, tc.advance()) {
-        if (skip_tile(tc.z + p.z0)) { --it; continue; }
-        int nkb_t = p.nkb;
-        if (use_ext) {
-          if (tc.z != cur_z) { cur_z = tc.z; cur_ext = tile_ext((tc.z + p.z0) / p.HB); }
-          if (skip_pad(cur_ext, tc.mi, tc.ni)) { --it; continue; }
-          nkb_t = tile_nkb(cur_ext);
-        }
-        const uint32_t as = it & 1;
-        mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
-        tc_fence_after();
-        const uint32_t tacc = tmem_base + as * BN;
-        for (int kb = 0; kb < nkb_t; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
+        for (int tile = t_begin; tile < t_end; tile += t_step, ++it, tc.advance()) {
+          if (skip_tile(tc.z)) { --it; continue; }
+          if (use_ext) {
+            if (tc.z != cur_z) { cur_z = tc.z; cur_ext = tile_ext(tc.z / p.HB); }
+            if (skip_pad(cur_ext, tc.mi, tc.ni)) { --it; continue; }
+          }
+          const int nkb_t = tile_nkb(cur_ext, in_group1(tc.ni));
+          const uint32_t as = it & 1;
+          mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
           tc_fence_after();
-          if (it == 0 && kb == 0) SRN_STAMP(2);
-          const uint32_t sa = smem_u32(smem + stage * CFG::kStageBytes);
-          const uint64_t da = make_kmajor_sw128_desc(sa);
-          const uint64_t db = make_kmajor_sw128_desc(sa + CFG::kABytes);
-          if (!(p.dbg_mode & 2)) {       // (dbg_mode & 2: profiling experiment without MMAs)
+          const uint32_t tacc = tmem_base + as * BN;
+          for (int kb = 0; kb < nkb_t; ++kb) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            if (it == 0 && kb == 0) SRN_STAMP(2);
+            const uint32_t sa = smem_u32(smem + stage * CFG::kStageBytes);
+            const uint64_t da = make_kmajor_sw128_desc(sa);
+            const uint64_t db = make_kmajor_sw128_desc(sa + CFG::kABytes);
 #pragma unroll
             for (int k = 0; k < 4; ++k)   // 4 x 32 bytes of K per 128-byte swizzled row
               umma_pair<TR::kKind>(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            tc_commit_mask(&empty_bar[stage], 0x3);     // frees the stage in both CTAs
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
-          tc_commit_mask(&empty_bar[stage], MC ? 0xF : 0x3);     // frees the stage in both CTAs (MC: one of the two arrivals, in all four)
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          tc_commit_mask(&tfull_bar[as], 0x3);          // both CTAs' epilogues may drain their half
+          SRN_STAMP(3);
         }
-        tc_commit_mask(&tfull_bar[as], (uint16_t)(0x3u << leader));          // both CTAs' epilogues may drain their half
-        SRN_STAMP(3);
-      }
       }
     }
   } else {
-    // -------------------------------------------------------------- epilogue (8 warps)
+    // -------------------------------------------------------------- epilogue (EW warps)
     const int q = warp & 3;                 // TMEM lane quarter this warp may access (warp id % 4)
-    const int sub = (warp - 2) >> 2;        // which half of the tile's columns
+    const int sub = (warp - 2) >> 2;        // which slice of the tile's columns (EW / 4 slices)
     Stager st;
     st.base = smem_u32(smem + CFG::kStgOff + (warp - 2) * CFG::kStgWarp);
     st.buf = 0;
     st.fill = 0;
-    st.one = (AS || SRN_ONEBOX) ? 1u : 0u;
+    st.one = EW == 16 ? 1u : 0u;
     uint32_t rphase = 0;      // parity of this warp's residual barrier (kResidTma)
-    const bool has_bias = p.bias != nullptr;
     const bool has_alpha = p.alpha != 1.0f;
-    float* bias_s = reinterpret_cast<float*>(smem + CFG::kBiasOff) + (warp - 2) * 128;   // this warp's bias slice
+    float* bias_s = reinterpret_cast<float*>(smem + CFG::kBiasOff) + (warp - 2) * (CPW * 32);   // this warp's bias slice
     const uint32_t tepi_addr = map_to_cta(&tempty_bar[0], leader);
     uint32_t it = 0;
     // Per-row / per-key side inputs of the softmax epilogues, requested one tile ahead (SRN_EPI_PREFETCH): the clock64
     // trace showed expscores at 9.9 k clocks per tile with a 4.6 k chunk loop - the rest was the serial chain of
     // dependent L2 round trips (16 slice maxima four at a time, then the key mask) in front of every tile.
     float pre_s[16];          // slice statistics 0..15 of this lane's row
-    uint8_t pre_k[NCH / 2];   // key-mask bytes of this lane's key in each of the warp's chunks (0 beyond N)
+    uint8_t pre_k[CPW];       // key-mask bytes of this lane's key in each of the warp's chunks (0 beyond N)
     auto stat_issue = [&](int zz, int rr, bool ok, int j0, int cnt, float (&s)[16]) {
       const float* sp = (EPI == EPI_EXP ? p.stat_max : p.stat_sum) + (long long)zz * p.stat_n * p.stat_ld + rr;
 #pragma unroll
       for (int u = 0; u < 16; ++u)
         s[u] = (ok && j0 + u < cnt) ? sp[(long long)(j0 + u) * p.stat_ld] : (EPI == EPI_EXP ? -INFINITY : 0.f);
     };
-    auto key_issue = [&](int bb, int key0, uint8_t (&k)[NCH / 2]) {
+    auto key_issue = [&](int bb, int key0, uint8_t (&k)[CPW]) {
 #pragma unroll
-      for (int cc = 0; cc < NCH / 2; ++cc) {
+      for (int cc = 0; cc < CPW; ++cc) {
         const int key = key0 + cc * 32 + lane;
         k[cc] = key < p.N ? p.keymask[(long long)bb * p.keymask_bstride + (long long)key * p.keymask_step] : (uint8_t)0;
       }
     };
     int pre_tile = -1;        // the tile pre_s / pre_k were requested for
     for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
-      const int z = tile / tiles_mn + p.z0;
+      const int z = tile / tiles_mn;
       if (skip_tile(z)) { --it; continue; }
-      const bool noshift = EPI == EPI_EXP && p.noshift != nullptr && s_ns[z - p.z0] != 0;
+      const bool noshift = EPI == EPI_EXP && p.noshift != nullptr && s_ns[z] != 0;
       const int rem = tile % tiles_mn;
-      const int mi = rem / ntn_u, ni = rem - mi * ntn_u;
+      const int mi = rem / p.ntn, ni = rem - mi * p.ntn;
       const int b = z / p.HB;
       const int h = z - b * p.HB;
       const int ext = tile_ext(b);
+      // tile group (gemm.cuh): group 1 has its own output tensor, bias and mask offset, and no GroupNorm statistics
+      const bool g1 = in_group1(ni);
+      const int n0 = (g1 ? ni - p.grp_ntn0 : ni) * BN;
+      const float* bias = g1 ? p.bias2 : p.bias;
+      const CUtensorMap* dmap = g1 ? &p.mapD2 : &p.mapD;
+      const bool has_bias = bias != nullptr;
+      const bool gn_on = EPI == EPI_STORE_GN && p.gn_part != nullptr && !g1;
       if (skip_pad(ext, mi, ni)) {
-        if constexpr (EPI == EPI_STORE_F32) {
+        if constexpr (EPI == EPI_STORE_GN) {
           // a skipped convolution tile is all bias: its GroupNorm partial sums (the reference's statistics include the
           // padded frames) are rows x sum(bias), rows x sum(bias^2) per 64-channel group; none in valid-frame mode
           const int t = threadIdx.x - 64;
-          const int n0s = (ni * (MC ? 2 : 1) + (int)pj) * BN;
-          if (p.gn_part != nullptr && t < NG * 2 && n0s < p.N) {
+          if (gn_on && t < NG * 2 && n0 < p.N) {
             const int g = t >> 1, w = t & 1;
             const int mts = mi * 2 + (int)rank;
             int rows = p.M - mts * 128;
@@ -484,10 +384,10 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
             if (p.gn_mask != nullptr) rows = 0;
             float sb = 0.f;
             for (int c = 0; c < 64; ++c) {
-              const float bv = p.bias != nullptr ? p.bias[n0s + g * 64 + c] : 0.f;
+              const float bv = has_bias ? bias[n0 + g * 64 + c] : 0.f;
               sb += w ? bv * bv : bv;
             }
-            p.gn_part[(((long long)b * (2 * p.ntm) + mts) * 8 + (n0s >> 6) + g) * 2 + w] = sb * (float)rows;
+            p.gn_part[(((long long)b * (2 * p.ntm) + mts) * 8 + (n0 >> 6) + g) * 2 + w] = sb * (float)rows;
           }
         }
         --it;
@@ -497,28 +397,27 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       const int stat_n_t = (use_ext && p.ext_keys != 0) ? min(p.stat_n, (ext + 63) >> 6) : p.stat_n;
       const int mt = mi * 2 + (int)rank;     // 128-row tile index inside the batch entry
       const int m0 = mt * 128;
-      const int n0 = (ni * (MC ? 2 : 1) + (int)pj) * BN;
       const uint32_t as = it & 1;
       const int row0 = m0 + q * 32;
       const int row = row0 + lane;
       const bool row_ok = row < p.M;
       float mk = 1.0f;
       if (p.rowmask != nullptr && row_ok)
-        mk = p.rowmask[(long long)b * p.mask_bstride + (long long)row * p.mask_step + p.mask_off] ? 1.0f : 0.0f;
-      bool gn_ok = row_ok;      // does this row enter the GroupNorm statistics (valid-frame mode: unmasked rows only)
-      if constexpr (EPI == EPI_STORE_F32) {
-        if (p.gn_mask != nullptr && row_ok)
+        mk = p.rowmask[(long long)b * p.mask_bstride + (long long)row * p.mask_step + (g1 ? p.mask_off2 : p.mask_off)] ? 1.0f : 0.0f;
+      bool gn_ok = row_ok && gn_on;      // does this row enter the GroupNorm statistics (valid-frame mode: unmasked rows only)
+      if constexpr (EPI == EPI_STORE_GN) {
+        if (p.gn_mask != nullptr && gn_ok)
           gn_ok = p.gn_mask[(long long)b * p.mask_bstride + (long long)row * p.mask_step] != 0;
       }
       float* red = gn_red + as * (4 * NG * 2);
-      const int c_first = sub * (NCH / 2);
+      const int c_first = sub * CPW;
       int nvalid = (p.N - (n0 + c_first * 32) + 31) / 32;     // chunks of this warp that start inside N
-      nvalid = nvalid < 0 ? 0 : (nvalid > NCH / 2 ? NCH / 2 : nvalid);
+      nvalid = nvalid < 0 ? 0 : (nvalid > CPW ? CPW : nvalid);
       // 2-byte outputs fill one 128-byte staging row per TWO chunks: never stop on a half-filled box (N = keys
       // need not be a multiple of 64 for EPI_EXP; columns >= N hold exact zeros and are clipped by the store)
       if constexpr (sizeof(OT) == 2 && EPI == EPI_EXP) nvalid = (nvalid + 1) & ~1;
       const uint32_t trow = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN + c_first * 32);
-      // ---- everything that does not depend on the accumulator is fetched BEFORE waiting for it: with two epilogue
+      // ---- everything that does not depend on the accumulator is fetched BEFORE waiting for it: with few epilogue
       // warps per scheduler any global-load latency left inside the chunk loop is fully exposed (ncu: long_sb)
       float gs = 0.f, gss = 0.f;
       float racc = EPI == EPI_ROWMAX ? -INFINITY : 0.f, rowc = 0.f;
@@ -536,18 +435,18 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           else rowc = a > 0.f ? 1.0f / a : 0.f;
         }
       }
-      uint32_t keybits[NCH / 2];
+      uint32_t keybits[CPW];
       if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
         if (!SRN_EPI_PREFETCH || pre_tile != tile) key_issue(b, n0 + c_first * 32, pre_k);
 #pragma unroll
-        for (int cc = 0; cc < NCH / 2; ++cc) keybits[cc] = __ballot_sync(0xffffffffu, pre_k[cc] != 0);
+        for (int cc = 0; cc < CPW; ++cc) keybits[cc] = __ballot_sync(0xffffffffu, pre_k[cc] != 0);
       }
       if (has_bias) {       // this warp's bias slice -> smem (read back as broadcasts, one vector per 4 columns)
         const int col = n0 + c_first * 32 + lane * 4;
         float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (lane < NCH * 4 && col < p.N) bv = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+        if (lane < CPW * 8 && col < p.N) bv = __ldg(reinterpret_cast<const float4*>(bias + col));
         __syncwarp();       // the previous tile's reads of this slice are done
-        if (lane < NCH * 4) *reinterpret_cast<float4*>(bias_s + lane * 4) = bv;
+        if (lane < CPW * 8) *reinterpret_cast<float4*>(bias_s + lane * 4) = bv;
         __syncwarp();
       }
       // (EPI_RESID_F32 adds its residual in the L2 with a TMA reduce-add store: nothing to load)
@@ -557,9 +456,9 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
       // chunk ahead (kResidTma); the other precisions keep the register path.
       // EPI_RESID_ACT: the same residual box, but the sum goes back INTO the box and is stored from there as the f32
       // stream (mapD) while its activated 2-byte copy leaves through the warp's other box (mapD2).
-      constexpr bool kAct = EPI == EPI_RESID_ACT && !SRN_DIRECT_STORE;
-      constexpr bool kResidTma = ((EPI == EPI_RESID_OT && sizeof(OT) == 2) || kAct) && !SRN_DIRECT_STORE;
-      constexpr bool kResid = (EPI == EPI_RESID_OT && !kResidTma) || (EPI == EPI_RESID_F32 && SRN_DIRECT_STORE);
+      constexpr bool kAct = EPI == EPI_RESID_ACT;
+      constexpr bool kResidTma = (EPI == EPI_RESID_OT && sizeof(OT) == 2) || kAct;
+      constexpr bool kResid = EPI == EPI_RESID_OT && !kResidTma;
       float4 r4[kResid ? 8 : 1];
       const float4* rs = nullptr;
       if constexpr (kResid) {
@@ -570,16 +469,15 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         }
       }
       const bool has_res = !kAct || p.resid != nullptr;      // EPI_RESID_ACT without a residual: store + activated copy
+      uint8_t* const rbox_ptr = smem + CFG::kStgOff + (warp - 2) * CFG::kStgWarp + 4096;      // (kResidTma: EW = 8, two boxes)
       if constexpr (kResidTma) {
         __syncwarp();      // the previous tile's reads of the residual box are done
         if (lane == 0 && nvalid > 0 && has_res) {
           if constexpr (kAct) tma_store_wait_read<0>();      // ... and so is the store of its last chunk
           mbar_expect_tx(&resid_bar[warp - 2], 4096);
-          tma_load_3d(reinterpret_cast<void*>(smem + CFG::kStgOff + (warp - 2) * 8192 + 4096), &p.mapR, &resid_bar[warp - 2],
-                      n0 + c_first * 32, row0, b);
+          tma_load_3d(reinterpret_cast<void*>(rbox_ptr), &p.mapR, &resid_bar[warp - 2], n0 + c_first * 32, row0, b);
         }
       }
-      if (p.dbg_mode & 4) nvalid = 0;    // profiling experiment without the epilogue
       mbar_wait(&tfull_bar[as], (it >> 1) & 1);
       tc_fence_after();
       if (threadIdx.x == 64) { if (it == 0) SRN_STAMP(4); SRN_STAMP(5); }
@@ -594,17 +492,16 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         // the next tile's side inputs: in flight during this tile's chunks
         const int tn = tile + t_step;
         if (tn < t_end) {
-          const int zn = tn / tiles_mn + p.z0;
+          const int zn = tn / tiles_mn;
           const int remn = tn % tiles_mn;
           pre_tile = tn;        // (a skipped tile's values are simply never used)
           if constexpr (EPI != EPI_ROWMAX) {
-            const int rown = ((remn / ntn_u) * 2 + (int)rank) * 128 + q * 32 + lane;
+            const int rown = ((remn / p.ntn) * 2 + (int)rank) * 128 + q * 32 + lane;
             const int extn = tile_ext(zn / p.HB);
             const int cntn = (use_ext && p.ext_keys != 0) ? min(p.stat_n, (extn + 63) >> 6) : p.stat_n;
-            if (!(EPI == EPI_EXP && p.noshift != nullptr && s_ns[zn - p.z0] != 0)) stat_issue(zn, rown, rown < p.M, 0, cntn, pre_s);
+            if (!(EPI == EPI_EXP && p.noshift != nullptr && s_ns[zn] != 0)) stat_issue(zn, rown, rown < p.M, 0, cntn, pre_s);
           }
-          if constexpr (EPI != EPI_PV)
-            key_issue(zn / p.HB, ((remn % ntn_u) * (MC ? 2 : 1) + (int)pj) * BN + c_first * 32, pre_k);
+          if constexpr (EPI != EPI_PV) key_issue(zn / p.HB, (remn % p.ntn) * BN + c_first * 32, pre_k);
         }
       }
 #pragma unroll 1
@@ -669,8 +566,7 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
             __syncwarp();      // every lane has its row: the box may receive the next chunk
             if (lane == 0 && cc + 1 < nvalid) {
               mbar_expect_tx(&resid_bar[warp - 2], 4096);
-              tma_load_3d(reinterpret_cast<void*>(smem + CFG::kStgOff + (warp - 2) * 8192 + 4096), &p.mapR,
-                          &resid_bar[warp - 2], nc + 32, row0, b);
+              tma_load_3d(reinterpret_cast<void*>(rbox_ptr), &p.mapR, &resid_bar[warp - 2], nc + 32, row0, b);
             }
           }
         }
@@ -695,15 +591,14 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
         uint32_t kbits = 0;
         if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
 #pragma unroll
-          for (int j = 0; j < NCH / 2; ++j) kbits = j == cc ? keybits[j] : kbits;    // keeps keybits[] in registers
+          for (int j = 0; j < CPW; ++j) kbits = j == cc ? keybits[j] : kbits;    // keeps keybits[] in registers
         }
-        epilogue_chunk<OT, EPI>(p, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss, racc, rowc, kbits, gn_ok);
+        epilogue_chunk<OT, EPI>(p, dmap, v, st, lane, b, h, z, row, row0, nc, row_ok, mk, gs, gss, racc, rowc, kbits, gn_ok);
         if constexpr (kAct) {
           if (lane == 0 && cc + 1 < nvalid && has_res) {      // the box's store has been read: fetch the next residual chunk
             tma_store_wait_read<0>();
             mbar_expect_tx(&resid_bar[warp - 2], 4096);
-            tma_load_3d(reinterpret_cast<void*>(smem + CFG::kStgOff + (warp - 2) * 8192 + 4096), &p.mapR,
-                        &resid_bar[warp - 2], nc + 32, row0, b);
+            tma_load_3d(reinterpret_cast<void*>(rbox_ptr), &p.mapR, &resid_bar[warp - 2], nc + 32, row0, b);
           }
         }
         if constexpr (EPI == EPI_ROWMAX || EPI == EPI_EXP) {
@@ -732,8 +627,8 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
             gs = 0.f;
           }
         }
-        if constexpr (EPI == EPI_STORE_F32) {
-          if (p.gn_part != nullptr && (c & 1)) {   // a 64-channel group is complete
+        if constexpr (EPI == EPI_STORE_GN) {
+          if (gn_on && (c & 1)) {   // a 64-channel group is complete
             const float s = warp_sum_f(gs), ss = warp_sum_f(gss);
             if (lane == 0) {
               red[(q * NG + (c >> 1)) * 2 + 0] = s;
@@ -743,11 +638,11 @@ __global__ void __launch_bounds__(320, 1) gemm_kernel(const __grid_constant__ Ge
           }
         }
       }
-      if constexpr (EPI == EPI_STORE_F32) {
-        if (p.gn_part != nullptr) {
-          asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps only
+      if constexpr (EPI == EPI_STORE_GN) {
+        if (p.gn_part != nullptr) {     // (uniform over the CTA's epilogue warps: every tile, also group 1's, meets here)
+          asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");   // the epilogue warps only
           const int t = threadIdx.x - 64;
-          if (t < NG * 2) {
+          if (gn_on && t < NG * 2) {
             const int g = t >> 1, w = t & 1;
             const float s = red[(0 * NG + g) * 2 + w] + red[(1 * NG + g) * 2 + w] + red[(2 * NG + g) * 2 + w] +
                             red[(3 * NG + g) * 2 + w];

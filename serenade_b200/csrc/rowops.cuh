@@ -62,6 +62,15 @@ __device__ __forceinline__ void load8(const float* p, float (&v)[8]) {
   const float4 b = reinterpret_cast<const float4*>(p)[1];
   v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
 }
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {      // bf16 -> f32 is a 16-bit shift
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
 __device__ __forceinline__ void store8(float* p, const float (&v)[8]) {
   reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
   reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
@@ -231,7 +240,7 @@ __device__ __forceinline__ void gn_reduce_stats(const float* __restrict__ part, 
 // ------------------------------------------------------------------------------------------------
 // out = (Mish(GN(y)) + tbias) * mask      (tbias may be null).  256 threads = 4 rows x 64 threads x 8 ch.
 template <typename OT>
-__global__ void __launch_bounds__(256, 4) gn_apply_kernel(const float* __restrict__ y, const float* __restrict__ part,
+__global__ void __launch_bounds__(256, 4) gn_apply_kernel(const OT* __restrict__ y, const float* __restrict__ part,
                                                        int mtiles, int T, long long bstride,
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                                        const float* __restrict__ tbias, const uint8_t* __restrict__ mask,
@@ -286,10 +295,10 @@ __global__ void __launch_bounds__(256, 4) gn_apply_kernel(const float* __restric
 // prologue), and the per-channel constants come from shared memory with the GroupNorm affine folded.
 // (forcing 3 or 4 resident blocks per SM through __launch_bounds__ was measured: no faster, 3 spills and is slower)
 template <typename OT>
-__global__ void __launch_bounds__(256, SRN_GNRES_MINBLOCKS) gn_res_spk_ln(const float* __restrict__ y, const float* __restrict__ part,
+__global__ void __launch_bounds__(256, SRN_GNRES_MINBLOCKS) gn_res_spk_ln(const OT* __restrict__ y, const float* __restrict__ part,
                                                      int mtiles, int T, long long bstride,
                                                      const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                     const float* __restrict__ res, const uint8_t* __restrict__ mask,
+                                                     const OT* __restrict__ res, const uint8_t* __restrict__ mask,
                                                      int mask_bstride, int mask_step,
                                                      const float* __restrict__ spk_scale /*[B][512]*/,
                                                      const float* __restrict__ spk_bias, const float* __restrict__ ln_g,
