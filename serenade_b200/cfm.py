@@ -78,10 +78,20 @@ class _Engine:
     def set_gn_valid_only(self, flag: bool) -> None:
         _lib.check(self.lib.srn_set_gn_valid_only(self.h, int(flag)), "srn_set_gn_valid_only")
 
+    def set_option(self, name: str, value: int) -> None:
+        """Run-time options of the C ABI (include/serenade_b200.h: srn_set_option), e.g. ("noshift", 0)."""
+        _lib.check(self.lib.srn_set_option(self.h, name.encode(), int(value)), f"srn_set_option({name})")
+
+    def softmax_stats(self):
+        """(shift-free attention entries, all entries) of the most recent solve / estimator call (synchronises)."""
+        out = (C.c_int64 * 2)()
+        _lib.check(self.lib.srn_softmax_stats(self.h, out), "srn_softmax_stats")
+        return int(out[0]), int(out[1])
+
     def profile_ops(self, B: int, T: int, reps: int = 5):
         """[(op name, kernel, avg ms)] for one estimator forward at (B, T): CUDA-event timing per op."""
         import json
-        buf = C.create_string_buffer(1 << 16)
+        buf = C.create_string_buffer(1 << 17)
         _lib.check(self.lib.srn_profile_ops(self.h, B, T, reps, buf, len(buf)), "srn_profile_ops")
         return json.loads(buf.value.decode())
 
@@ -108,7 +118,20 @@ def _as_mask_u8(mask: torch.Tensor, B: int, T: int, device) -> torch.Tensor:
         m = m[:, 0]
     if tuple(m.shape) != (B, T):
         raise ValueError(f"mask shape {tuple(mask.shape)} does not match batch {B} x {T} frames")
+    # the C ABI reads "non-zero = valid": a bool or uint8 mask already on the device is passed as it is (a bool tensor
+    # is one 0 / 1 byte per element), without the compare + cast kernels
+    if m.device == torch.device(device) and m.is_contiguous():
+        if m.dtype == torch.uint8:
+            return m
+        if m.dtype == torch.bool:
+            return m.view(torch.uint8)
     return (m != 0).to(device=device, dtype=torch.uint8).contiguous()
+
+
+def _tspan_host(t_span: torch.Tensor) -> torch.Tensor:
+    """t_span as a contiguous f32 CPU tensor (the C ABI takes the grid from host memory).  Pass a CPU tensor to keep the
+    call asynchronous: a device tensor (what the reference builds, flow_matching.py:61) costs one blocking D2H read."""
+    return t_span.detach().to("cpu", torch.float32).contiguous()
 
 
 class Decoder(nn.Module):
@@ -283,7 +306,7 @@ class CFM(nn.Module):
     def inference(self, mu, mask, n_timesteps=10, temperature=0.667, spks=None):
         # noise is drawn on the CPU generator then moved, exactly like flow_matching.py:57-60
         z = torch.randn((mu.shape[0], self.out_channels, mu.shape[2])).to(mu.device) * temperature
-        t_span = torch.linspace(0, 1, n_timesteps + 1, device=mu.device)
+        t_span = torch.linspace(0, 1, n_timesteps + 1)       # (host: srn_solve_euler takes the grid from host memory)
         return self.solve_euler(z, t_span=t_span, mu=mu, mask=mask, trg_spks=spks)
 
     @torch.inference_mode()
@@ -298,7 +321,7 @@ class CFM(nn.Module):
         muf = mu.detach().to(device=dev, dtype=torch.float32).contiguous()
         spk = trg_spks.detach().to(device=dev, dtype=torch.float32).contiguous()
         m8 = _as_mask_u8(mask, B, T, dev)
-        ts = t_span.detach().to("cpu", torch.float32).contiguous()
+        ts = _tspan_host(t_span)
         n_steps = ts.numel() - 1
         if n_steps < 1:
             raise ValueError("t_span needs at least two points")

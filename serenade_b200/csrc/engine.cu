@@ -9,11 +9,11 @@
 
 namespace srn {
 
-template <typename OT, int BN, int EPI, int EW = 8>
+template <typename OT, int BN, int EPI>
 static void configure_one() {
-  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                GemmCfg<BN, EW>::kSmemBytes));
-  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI, EW>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
+  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                GemmCfg<BN>::kSmemBytes));
+  SRN_CUDA(cudaFuncSetAttribute(gemm_kernel<OT, BN, EPI>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
 }
 
 template <typename OT, int BN>
@@ -36,11 +36,6 @@ template <typename OT>
 static void configure_kernels() {
   configure_bn<OT, 128>();
   configure_bn<OT, 256>();
-  // sixteen epilogue warps (engine_run.inl: launch_gemm_ew)
-  configure_one<OT, 256, EPI_QKV, 16>();
-  configure_one<OT, 256, EPI_ROWMAX, 16>();
-  configure_one<OT, 256, EPI_EXP, 16>();
-  configure_one<OT, 256, EPI_PV, 16>();
 }
 
 std::unique_ptr<EngineBase> make_engine(const SrnConfig& cfg) {

@@ -34,25 +34,15 @@ static void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t
   SRN_CUDA(cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...));
 }
 
-// Sixteen epilogue warps (gemm_kernel.cuh: GemmCfg) for the epilogue-bound K = 512 GEMMs on 256-column tiles.
-// SRN_EW16 is a bit mask for A/B runs: 1 = QKV, 2 = exp pass, 4 = P~ V, 8 = row-max pass (default: QKV + exp).
-static int ew16_mask() {
-  static const int m = [] {
-    const char* e = getenv("SRN_EW16");
-    return e != nullptr ? atoi(e) : 3;
-  }();
-  return m;
-}
-
-template <typename OT, int BN, int EPI, int EW = 8>
+template <typename OT, int BN, int EPI>
 static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t st) {
   gp.ntn = (int)grid.x;
   gp.ntm = (int)grid.y;
   gp.nz = (int)grid.z;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof cfg);
-  cfg.blockDim = dim3(GemmCfg<BN, EW>::kThreads);
-  cfg.dynamicSmemBytes = GemmCfg<BN, EW>::kSmemBytes;
+  cfg.blockDim = dim3(GemmCfg<BN>::kThreads);
+  cfg.dynamicSmemBytes = GemmCfg<BN>::kSmemBytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -66,19 +56,7 @@ static void launch_gemm_impl(GemmParams gp, dim3 grid, int num_sms, cudaStream_t
   const long long tiles = (long long)grid.x * grid.y * grid.z;                 // 256 x BN tiles, one per CTA pair
   const unsigned pairs = (unsigned)std::min<long long>(tiles, num_sms / 2);    // persistent: one pair per SM pair
   cfg.gridDim = dim3(2 * pairs);
-  SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, BN, EPI, EW>, gp));
-}
-
-// the epilogues that have a sixteen-warp instantiation (256-column tiles only)
-template <typename OT, int BN, int EPI>
-static void launch_gemm_ew(const GemmParams& gp, dim3 grid, int num_sms, cudaStream_t st, int bit) {
-  if constexpr (BN == 256) {
-    if (ew16_mask() & bit) {
-      launch_gemm_impl<OT, BN, EPI, 16>(gp, grid, num_sms, st);
-      return;
-    }
-  }
-  launch_gemm_impl<OT, BN, EPI>(gp, grid, num_sms, st);
+  SRN_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<OT, BN, EPI>, gp));
 }
 
 template <typename OT, int BN>
@@ -90,11 +68,11 @@ static void launch_gemm_bn(const GemmParams& gp, dim3 grid, int num_sms, cudaStr
     case EPI_RESID_F32: launch_gemm_impl<OT, BN, EPI_RESID_F32>(gp, grid, num_sms, st); break;
     case EPI_RESID_OT: launch_gemm_impl<OT, BN, EPI_RESID_OT>(gp, grid, num_sms, st); break;
     case EPI_GEGLU: launch_gemm_impl<OT, BN, EPI_GEGLU>(gp, grid, num_sms, st); break;
-    case EPI_QKV: launch_gemm_ew<OT, BN, EPI_QKV>(gp, grid, num_sms, st, 1); break;
+    case EPI_QKV: launch_gemm_impl<OT, BN, EPI_QKV>(gp, grid, num_sms, st); break;
     case EPI_EULER: launch_gemm_impl<OT, BN, EPI_EULER>(gp, grid, num_sms, st); break;
-    case EPI_ROWMAX: launch_gemm_ew<OT, BN, EPI_ROWMAX>(gp, grid, num_sms, st, 8); break;
-    case EPI_EXP: launch_gemm_ew<OT, BN, EPI_EXP>(gp, grid, num_sms, st, 2); break;
-    case EPI_PV: launch_gemm_ew<OT, BN, EPI_PV>(gp, grid, num_sms, st, 4); break;
+    case EPI_ROWMAX: launch_gemm_impl<OT, BN, EPI_ROWMAX>(gp, grid, num_sms, st); break;
+    case EPI_EXP: launch_gemm_impl<OT, BN, EPI_EXP>(gp, grid, num_sms, st); break;
+    case EPI_PV: launch_gemm_impl<OT, BN, EPI_PV>(gp, grid, num_sms, st); break;
     case EPI_RESID_ACT: launch_gemm_impl<OT, BN, EPI_RESID_ACT>(gp, grid, num_sms, st); break;
     default: fail("unknown GEMM epilogue %d", gp.epi);
   }
@@ -346,6 +324,10 @@ void Engine<OT>::estimator_forward(const float* x, const float* mu, const uint8_
   SRN_CUDA(cudaStreamSynchronize(st));   // &t / &zero are stack temporaries
   blend_active_ = false;
   prepass(pl, std::vector<float>{t}, std::vector<float>{0.f}, st);
+  if (debug) {      // the hoisted time path (decoder.py:48-63, :113-157, :97): time embedding, per-resnet time biases
+    capture_tap(pl, Tap{"time_emb", pl.temb2.p, 0, 1, 2048, 2048, 0, 1, 0}, st);
+    capture_tap(pl, Tap{"time_bias", pl.tb.p, 0, (int)resnets_.size(), 512, pl.tb_steps * 512, 0, 1, 0}, st);
+  }
   run_forward(pl, 0, v_out, false, st);
 }
 

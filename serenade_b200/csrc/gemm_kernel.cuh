@@ -16,13 +16,13 @@
 
 namespace srn {
 
-// EW = number of epilogue warps (8 or 16).  Sixteen (four per scheduler, each draining 64 accumulator columns of its
-// lane quarter) is for the K = 512 GEMMs whose epilogue, not the tensor pipe, bounds the tile loop: with two warps per
-// scheduler the per-chunk dependency chain (TMEM load -> convert -> stage -> store) has nothing to hide behind.  The
-// sixteen-warp form has ONE staging box per warp (same 64 KB in total) and fits 112 registers per thread.
-template <int BN, int EW = 8>
+// Eight epilogue warps, two per lane quarter (each drains half of the tile's columns), two staging boxes per warp.
+// Sixteen warps (four per scheduler, 64 accumulator columns each, one staging box per warp, 96 registers) were built
+// and measured in round 2 for the K = 512 GEMMs whose tile loop is longer than their MMA time: slower everywhere
+// (QKV 368 vs 334 us, exp 261 vs 246 us, P~ V 255 vs 244 us per C2 estimator call; profiles/r02_ab_epilogue_warps.txt).
+template <int BN>
 struct GemmCfg {
-  static_assert(EW == 8 || (EW == 16 && BN == 256), "8 epilogue warps, or 16 on 256-column tiles");
+  static constexpr int EW = 8;
   static constexpr int kStages = BN == 256 ? 4 : 5;
   static constexpr int kABytes = 128 * 128;            // this CTA's 128 rows of the pair's 256-row A tile
   static constexpr int kBBytes = (BN / 2) * 128;       // this CTA's half of the B tile's BN rows
@@ -30,7 +30,7 @@ struct GemmCfg {
   static constexpr int kOpBytes = kStages * kStageBytes;
   static constexpr int kSlices = EW / 4;                      // column slices of a tile (one epilogue warp per lane quarter each)
   static constexpr int kChunksPerWarp = (BN / 32) / kSlices;  // 32-column chunks per epilogue warp and tile
-  static constexpr int kStgWarp = EW == 8 ? 8192 : 4096;      // staging bytes per epilogue warp (two boxes / one box)
+  static constexpr int kStgWarp = 8192;                       // staging bytes per epilogue warp (two 4 KB boxes)
   static constexpr int kStgOff = kOpBytes;                    // epilogue staging: EW warps x kStgWarp = 64 KB
   static constexpr int kBarOff = kStgOff + EW * kStgWarp;     // barriers + tmem slot (256 B)
   static constexpr int kRedOff = kBarOff + 256;               // GroupNorm partial reduction scratch (256 B)

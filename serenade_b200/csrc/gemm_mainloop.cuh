@@ -4,7 +4,7 @@
 // profiles/r01_ab_*.txt, the code is in the git history before this file's round-2 rewrite): A-operand multicast over
 // four-CTA clusters (only 132 of 148 SMs can hold 4-CTA clusters: no gain), an A-stationary tile order for the K = 512
 // GEMMs (half the operand bytes, yet slower), attention passes in (batch, head) slices, exp2 on the FMA pipes, direct
-// st.global epilogue stores.
+// st.global epilogue stores; round 2: sixteen epilogue warps (gemm_kernel.cuh), an e4m3 row-max pass.
 #pragma once
 
 namespace srn {
@@ -18,18 +18,16 @@ namespace srn {
 #define SRN_STAMP(k) do { } while (0)
 #endif
 
-template <typename OT, int BN, int EPI, int EW = 8>
-__global__ void __launch_bounds__(64 + 32 * EW, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
+template <typename OT, int BN, int EPI>
+__global__ void __launch_bounds__(GemmCfg<BN>::kThreads, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
   using TR = OpTraits<OT>;
-  using CFG = GemmCfg<BN, EW>;
+  using CFG = GemmCfg<BN>;
+  constexpr int EW = CFG::EW;                   // epilogue warps
   constexpr int STAGES = CFG::kStages;
   constexpr int BK = TR::kBK;
   constexpr int NCH = BN / 32;                  // 32-column chunks per tile
   constexpr int CPW = CFG::kChunksPerWarp;      // ... per epilogue warp
   constexpr int NG = BN / 64;                   // GroupNorm groups per tile
-  // epilogues that need the warp's second staging box for the residual keep eight warps
-  static_assert(EW == 8 || !(EPI == EPI_RESID_OT || EPI == EPI_RESID_ACT || EPI == EPI_EULER || EPI == EPI_GEGLU),
-                "sixteen epilogue warps: one staging box per warp, two chunks per 128-byte staging row");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -330,7 +328,7 @@ __global__ void __launch_bounds__(64 + 32 * EW, 1) gemm_kernel(const __grid_cons
     st.base = smem_u32(smem + CFG::kStgOff + (warp - 2) * CFG::kStgWarp);
     st.buf = 0;
     st.fill = 0;
-    st.one = EW == 16 ? 1u : 0u;
+    st.one = 0u;
     uint32_t rphase = 0;      // parity of this warp's residual barrier (kResidTma)
     const bool has_alpha = p.alpha != 1.0f;
     float* bias_s = reinterpret_cast<float*>(smem + CFG::kBiasOff) + (warp - 2) * (CPW * 32);   // this warp's bias slice

@@ -37,57 +37,77 @@ def level_mask(batch, rows):
     return m.unsqueeze(-1).float()
 
 
-def fine_reference(sd, batch, t):
-    """Inner tensors of down_blocks.0 (channels-last), computed with torch fp32 from the state dict."""
-    P = "estimator.down_blocks.0"
+def fine_block(sd, prefix, tag, x, mask, temb, spks):
+    """Inner tensors (channels-last) of one resnet + transformer block `prefix` whose input is x (B, C_in, S) at the
+    rate of `mask` (B, 1, S): {tag}.y1/r/a1/y2/resnet/qk/P/ao/h_attn/ln3/gg, in torch fp32 from the state dict."""
+    out = {}
+    xm = x * mask
+    y1 = F.conv1d(xm, sd[prefix + ".0.block1.block.0.weight"], sd[prefix + ".0.block1.block.0.bias"], padding=1)
+    out[tag + ".y1"] = y1.transpose(1, 2)
+    out[tag + ".r"] = F.conv1d(xm, sd[prefix + ".0.res_conv.weight"], sd[prefix + ".0.res_conv.bias"]).transpose(1, 2)
+    h = F.mish(F.group_norm(y1, 8, sd[prefix + ".0.block1.block.1.weight"], sd[prefix + ".0.block1.block.1.bias"])) * mask
+    h = h + F.linear(F.mish(temb), sd[prefix + ".0.mlp.1.weight"], sd[prefix + ".0.mlp.1.bias"]).unsqueeze(-1)
+    out[tag + ".a1"] = (h * mask).transpose(1, 2)
+    y2 = F.conv1d(h * mask, sd[prefix + ".0.block2.block.0.weight"], sd[prefix + ".0.block2.block.0.bias"], padding=1)
+    out[tag + ".y2"] = y2.transpose(1, 2)
+    res = O._resnet(sd, prefix + ".0", x, mask, temb, spks)
+    out[tag + ".resnet"] = res.transpose(1, 2)
+    hs = res.transpose(1, 2)
+    tp = prefix + ".1.0"
+    n1 = F.layer_norm(hs, (512,), sd[tp + ".norm1.weight"], sd[tp + ".norm1.bias"])
+    q = F.linear(n1, sd[tp + ".attn1.to_q.weight"])
+    k = F.linear(n1, sd[tp + ".attn1.to_k.weight"])
+    v = F.linear(n1, sd[tp + ".attn1.to_v.weight"])
+    out[tag + ".qk"] = torch.cat([q, k], dim=-1)
+    B, S, _ = q.shape
+    qh, kh, vh = (z.view(B, S, 4, 512).transpose(1, 2) for z in (q, k, v))
+    sc = torch.matmul(qh, kh.transpose(-1, -2)) / math.sqrt(512)
+    scm = sc.masked_fill(~mask[:, 0].view(B, 1, 1, S), float("-inf"))
+    pr = torch.softmax(scm, dim=-1)
+    out[tag + ".P"] = pr.reshape(B * 4, S, S)
+    ao = torch.matmul(pr, vh).transpose(1, 2).reshape(B, S, 2048)
+    out[tag + ".ao"] = ao
+    h_attn = F.linear(ao, sd[tp + ".attn1.to_out.0.weight"], sd[tp + ".attn1.to_out.0.bias"]) + hs
+    out[tag + ".h_attn"] = h_attn
+    n3 = F.layer_norm(h_attn, (512,), sd[tp + ".norm3.weight"], sd[tp + ".norm3.bias"])
+    out[tag + ".ln3"] = n3
+    pj = F.linear(n3, sd[tp + ".ff.net.0.proj.weight"], sd[tp + ".ff.net.0.proj.bias"])
+    hh, gg = pj.chunk(2, dim=-1)
+    out[tag + ".gg"] = hh * F.gelu(gg)
+    return out
+
+
+def fine_reference(sd, batch, t, stages=None):
+    """Inner tensors of down_blocks.0 (full rate, 242 input channels) and - given the oracle's block outputs `stages` -
+    of down_blocks.1 (half rate) and up_blocks.1 (the 1024-channel skip-concat resnet), each block fed with the
+    ORACLE's input so that a stage's error is its own; plus the hoisted time path (a4): the time embedding and the six
+    per-resnet time biases."""
     out = {}
     with torch.inference_mode():
         mask = batch.mask
         x = torch.cat([batch.z, batch.mu], dim=1)
-        xm = x * mask
-        out["xin"] = F.pad(xm.transpose(1, 2), (0, 256 - xm.shape[1]))
+        out["xin"] = F.pad((x * mask).transpose(1, 2), (0, 256 - x.shape[1]))
         temb = O._time_embedding(sd, torch.tensor(t), x.shape[1])
-        y1 = F.conv1d(xm, sd[P + ".0.block1.block.0.weight"], sd[P + ".0.block1.block.0.bias"], padding=1)
-        out["down0.y1"] = y1.transpose(1, 2)
-        out["down0.r"] = F.conv1d(xm, sd[P + ".0.res_conv.weight"], sd[P + ".0.res_conv.bias"]).transpose(1, 2)
-        h = F.mish(F.group_norm(y1, 8, sd[P + ".0.block1.block.1.weight"], sd[P + ".0.block1.block.1.bias"])) * mask
-        h = h + F.linear(F.mish(temb), sd[P + ".0.mlp.1.weight"], sd[P + ".0.mlp.1.bias"]).unsqueeze(-1)
-        out["down0.a1"] = (h * mask).transpose(1, 2)
-        y2 = F.conv1d(h * mask, sd[P + ".0.block2.block.0.weight"], sd[P + ".0.block2.block.0.bias"], padding=1)
-        out["down0.y2"] = y2.transpose(1, 2)
-        res = O._resnet(sd, P + ".0", x, mask, temb, batch.spks)
-        out["down0.resnet"] = res.transpose(1, 2)
-        hs = res.transpose(1, 2)
-        tp = P + ".1.0"
-        n1 = F.layer_norm(hs, (512,), sd[tp + ".norm1.weight"], sd[tp + ".norm1.bias"])
-        q = F.linear(n1, sd[tp + ".attn1.to_q.weight"])
-        k = F.linear(n1, sd[tp + ".attn1.to_k.weight"])
-        v = F.linear(n1, sd[tp + ".attn1.to_v.weight"])
-        out["down0.qk"] = torch.cat([q, k], dim=-1)
-        B, S, _ = q.shape
-        qh, kh, vh = (z.view(B, S, 4, 512).transpose(1, 2) for z in (q, k, v))
-        sc = torch.matmul(qh, kh.transpose(-1, -2)) / math.sqrt(512)
-        out["down0.sc"] = sc.reshape(B * 4, S, S)
-        scm = sc.masked_fill(~mask[:, 0].view(B, 1, 1, S), float("-inf"))
-        pr = torch.softmax(scm, dim=-1)
-        out["down0.P"] = pr.reshape(B * 4, S, S)
-        ao = torch.matmul(pr, vh).transpose(1, 2).reshape(B, S, 2048)
-        out["down0.ao"] = ao
-        h_attn = F.linear(ao, sd[tp + ".attn1.to_out.0.weight"], sd[tp + ".attn1.to_out.0.bias"]) + hs
-        out["down0.h_attn"] = h_attn
-        n3 = F.layer_norm(h_attn, (512,), sd[tp + ".norm3.weight"], sd[tp + ".norm3.bias"])
-        out["down0.ln3"] = n3
-        pj = F.linear(n3, sd[tp + ".ff.net.0.proj.weight"], sd[tp + ".ff.net.0.proj.bias"])
-        hh, gg = pj.chunk(2, dim=-1)
-        out["down0.gg"] = hh * F.gelu(gg)
+        out["time_emb"] = temb.unsqueeze(0)
+        names = ["down_blocks.0", "down_blocks.1", "mid_blocks.0", "mid_blocks.1", "up_blocks.0", "up_blocks.1"]
+        out["time_bias"] = torch.cat([F.linear(F.mish(temb), sd[f"estimator.{n}.0.mlp.1.weight"], sd[f"estimator.{n}.0.mlp.1.bias"])
+                                      for n in names], dim=0).unsqueeze(0)
+        out.update(fine_block(sd, "estimator.down_blocks.0", "down0", x, mask, temb, batch.spks))
+        if stages is not None:
+            T = x.shape[-1]
+            m2 = mask[:, :, ::2]
+            out.update(fine_block(sd, "estimator.down_blocks.1", "down1", stages["down0.out"].transpose(1, 2), m2, temb,
+                                  batch.spks))
+            xin = torch.cat([stages["up0.out"].transpose(1, 2)[:, :, :T], stages["down0.tfm"].transpose(1, 2)], dim=1)
+            out.update(fine_block(sd, "estimator.up_blocks.1", "up1", xin, mask, temb, batch.spks))
     return out
 
 
 BLOCK_ORDER = ["down0.resnet", "down0.tfm", "down0.out", "down1.resnet", "down1.tfm", "down1.out",
                "mid0.resnet", "mid0.tfm", "mid1.resnet", "mid1.tfm", "up0.resnet", "up0.tfm", "up0.out",
                "up1.resnet", "up1.tfm", "up1.out", "final_block"]
-FINE_ORDER = ["xin", "down0.y1", "down0.r", "down0.a1", "down0.y2", "down0.resnet", "down0.qk",
-              "down0.P", "down0.ao", "down0.h_attn", "down0.ln3", "down0.gg"]
+_FINE_TAPS = ["y1", "r", "a1", "y2", "resnet", "qk", "P", "ao", "h_attn", "ln3", "gg"]
+FINE_ORDER = ["xin", "time_emb", "time_bias"] + [f"{blk}.{t}" for blk in ("down0", "down1", "up1") for t in _FINE_TAPS]
 # outputs that the CUDA path stores already masked (every consumer masks them anyway)
 MASKED_TAPS = {"tfm", "out"}
 
@@ -101,23 +121,29 @@ def compare(cfm, sd, batch, t, fine=True):
     try:
         v = est(batch.z.to(dev), batch.mask.to(dev), batch.mu.to(dev), torch.tensor(t), batch.spks.to(dev)).cpu()
         rows = []
+        stages = oracle_stages(sd, batch, t)
         if fine:
-            ref = fine_reference(sd, batch, t)
+            ref = fine_reference(sd, batch, t, stages)
             for name in FINE_ORDER:
                 got = eng.debug_fetch(name)
                 want = ref[name]
-                valid = level_mask(batch, want.shape[1]) if name != "down0.P" else None
-                if name == "down0.P":
+                if name in ("time_emb", "time_bias"):
+                    rows.append((name, rel(got, want), "hoisted time path (a4)"))
+                    continue
+                is_p = name.endswith(".P")
+                valid = level_mask(batch, want.shape[1]) if not is_p else None
+                if is_p:
                     # the CUDA path keeps P~ = exp(s - rowmax) unnormalised (the row sum is divided out in the
                     # P~ V epilogue): normalise here; compare valid query rows and valid keys only
                     m = batch.mask[:, 0].float()
+                    if want.shape[1] != m.shape[1]:
+                        m = m[:, ::2]
                     mm = (m.unsqueeze(2) * m.unsqueeze(1)).repeat_interleave(4, dim=0)
                     got = got * mm
                     got = got / got.sum(-1, keepdim=True).clamp_min(1e-30)
                     rows.append((name, rel(got * mm, want * mm), "valid q,k, rows normalised on the host"))
                 else:
                     rows.append((name, rel(got * valid, want * valid), "valid rows"))
-        stages = oracle_stages(sd, batch, t)
         for name in BLOCK_ORDER:
             got = eng.debug_fetch(name)
             want = stages[name]

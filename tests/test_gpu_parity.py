@@ -64,7 +64,7 @@ def test_stagewise_vs_oracle(cfm_jitter, jitter_sd, dev, lengths):
     text = format_report(rows)
     _report(f"stagewise_{'_'.join(map(str, lengths))}.txt", text)
     print(text)
-    bad = [(n, e) for n, e, _ in rows if not (e < 3e-2)]
+    bad = [(n, e) for n, e, _ in rows if not (e < 1.5e-2)]
     assert not bad, f"stages out of tolerance: {bad}\n{text}"
     pad = ~b.mask.expand_as(v)
     assert float(v[pad].abs().sum()) == 0.0          # decoder.py:467
@@ -399,3 +399,77 @@ def test_reloading_weights_takes_effect(jitter_sd, stock_sd, dev):
     x3 = _make_cfm(stock_sd).solve_euler(*args)
     assert not torch.equal(x1, x2)
     assert torch.equal(x2, x3)
+
+
+def test_softmax_path_switch_and_statistics(cfm_jitter, jitter_sd, dev):
+    """srn_set_option("noshift", 0) routes every attention entry through the row-max pass; srn_softmax_stats reports
+    which path the last solve took.  Both paths are the same softmax: results agree to rounding and with the oracle."""
+    import serenade_b200 as S
+    from oracle import cfm_oracle as O
+    b = S.make_batch([150, 97], n_steps=3, seed=31)
+    args = [b.z.to(dev), b.t_span, b.mu.to(dev), b.mask.to(dev), b.spks.to(dev)]
+    eng = cfm_jitter.estimator.engine(dev)
+    x_free = cfm_jitter.solve_euler(*args)
+    free, total = eng.softmax_stats()
+    assert total == 2 * 4 * 6 * 3 and 0 < free <= total, (free, total)      # (clips x heads) x blocks x steps; most run shift-free
+    eng.set_option("noshift", 0)
+    try:
+        x_shift = cfm_jitter.solve_euler(*args)
+        assert eng.softmax_stats() == (0, total)
+    finally:
+        eng.set_option("noshift", 1)
+    assert torch.equal(cfm_jitter.solve_euler(*args), x_free)           # switched back (graph re-captured)
+    with torch.inference_mode():
+        ref = O.solve_euler(jitter_sd, b.z, b.t_span, b.mu, b.mask, b.spks)
+    e1, e2, e12 = rel_l2(x_free.cpu(), ref), rel_l2(x_shift.cpu(), ref), rel_l2(x_free.cpu(), x_shift.cpu())
+    _report("softmax_paths.txt", f"shift-free vs oracle {e1:.3e}, shifted vs oracle {e2:.3e}, shift-free vs shifted {e12:.3e}")
+    assert e1 < BF16_FINAL_TOL and e2 < BF16_FINAL_TOL and e12 < 5e-3
+    with pytest.raises(RuntimeError):
+        eng.set_option("no_such_option", 1)
+
+
+def test_pipelined_sharded_decode_equals_the_plain_loop(cfm_jitter, dev):
+    """sharding.decode_sharded_pipelined (pinned double-buffered staging, copy streams) returns bit for bit what the
+    serial loop returns, for ragged clips and uneven batches, and again on a second pass through the same slots."""
+    import serenade_b200 as S
+    from serenade_b200 import sharding
+    lengths = [120, 64, 97, 120, 33, 80, 71]
+    clips = []
+    for i, L in enumerate(lengths):
+        b = S.make_batch([L], n_steps=2, seed=500 + i)
+        clips.append(dict(mu=b.mu[0], z=b.z[0], spk=b.spks[0]))
+    t_span = torch.linspace(0, 1, 3)
+    plain = sharding.decode_sharded(cfm_jitter.solve_euler, clips, t_span, max_batch=3, device=dev)
+    for _ in range(2):
+        piped = sharding.decode_sharded_pipelined(cfm_jitter, clips, t_span, max_batch=3, device=dev)
+        assert sorted(piped) == sorted(plain) == list(range(len(lengths)))
+        for i in plain:
+            assert piped[i].shape == (80, lengths[i])
+            assert torch.equal(piped[i], plain[i]), i
+    two = {}
+    for r in range(2):
+        two.update(sharding.decode_sharded_pipelined(cfm_jitter, clips, t_span, rank=r, world_size=2, max_batch=3, device=dev))
+    assert sorted(two) == list(range(len(lengths)))
+
+
+@pytest.mark.parametrize("precision,step_tol,final_tol", [("bf16", BF16_STEP_TOL, BF16_FINAL_TOL),
+                                                          ("tf32", TF32_STEP_TOL, TF32_STEP_TOL)])
+def test_golden_vector_in_channels_244(dev, precision, step_tol, final_tol):
+    """SerenadeNew's geometry, CFM(in_channels=244) (reference serenade_new.py:77): 164 conditioning channels, packed to
+    the same 256-column conv operand; golden from the unmodified reference modules."""
+    import serenade_b200 as S
+    spec, v_ref, x_ref = load_golden("new244_mixed")
+    geom = S.synth.DecoderGeometry(in_channels=spec["in_channels"])
+    sd = S.synth.make_state_dict(seed=0, jitter=spec["jitter"], g=geom)
+    cfm = S.CFM(in_channels=244, out_channels=80, spk_embed_dim=256, decoder_channels=(512, 512),
+                decoder_attention_head_dim=512, precision=precision)
+    cfm.load_state_dict(sd, strict=True)
+    b = S.synth.make_batch(spec["lengths"], n_steps=spec["n_steps"], seed=spec["seed"], g=geom)
+    v = cfm.estimator(b.z.to(dev), b.mask.to(dev), b.mu.to(dev), torch.tensor(spec["t"]), b.spks.to(dev)).cpu()
+    x = cfm.solve_euler(b.z.to(dev), b.t_span, b.mu.to(dev), b.mask.to(dev), b.spks.to(dev)).cpu()
+    e_v, e_x = rel_l2(v, v_ref), rel_l2(x, x_ref)
+    _report(f"golden_244_{precision}.txt", f"new244_mixed ({precision}): per-step rel_l2={e_v:.3e} final rel_l2={e_x:.3e}")
+    assert e_v < step_tol and e_x < final_tol
+    pad = ~b.mask.expand_as(v)
+    assert float(v[pad].abs().sum()) == 0.0
+    assert torch.equal(x[pad], b.z[pad])

@@ -25,6 +25,21 @@ def test_oracle_matches_reference_golden(name, jitter_sd, stock_sd):
     assert torch.equal(x[pad], b.z[pad])
 
 
+def test_oracle_matches_reference_golden_in_channels_244():
+    """SerenadeNew's CFM(in_channels=244) (reference serenade_new.py:77): golden from the unmodified reference modules."""
+    spec, v_ref, x_ref = load_golden("new244_mixed")
+    geom = synth.DecoderGeometry(in_channels=spec["in_channels"])
+    sd = synth.make_state_dict(seed=0, jitter=spec["jitter"], g=geom)
+    assert synth.state_dict_checksum(sd) == pytest.approx(spec["weight_checksum"], rel=1e-9)
+    b = synth.make_batch(spec["lengths"], n_steps=spec["n_steps"], seed=spec["seed"], g=geom)
+    assert b.mu.shape[1] == 164
+    with torch.inference_mode():
+        v = O.estimator_forward(sd, b.z, b.mask, b.mu, torch.tensor(spec["t"]), b.spks)
+        x = O.solve_euler(sd, b.z, b.t_span, b.mu, b.mask, b.spks)
+    assert rel_l2(v, v_ref) < 2e-5
+    assert rel_l2(x, x_ref) < 2e-5
+
+
 def test_time_grid_matches_reference_wobble():
     # flow_matching.py:79-91: fp32 running t, dt recomputed as t_span[k+1] - t
     ts, dts = O.time_grid(torch.linspace(0, 1, 11))
