@@ -253,8 +253,15 @@ class CFM(nn.Module):
     """Reference flow_matching.py:9-133: inference, and the forward value of `compute_loss` (no backward pass)."""
 
     def __init__(self, in_channels=80, out_channels=80, solver="euler", sigma_min=1e-4, spk_embed_dim=256,
-                 decoder_channels=(512, 512), decoder_attention_head_dim=256, precision="bf16", gn_stats="padded"):
+                 decoder_channels=(512, 512), decoder_attention_head_dim=256, precision="bf16", gn_stats="padded",
+                 shape_bucket=0):
         super().__init__()
+        # shape_bucket > 0 (with gn_stats="valid" only): solve_euler pads T up to the next multiple with masked frames.
+        # The engine keeps one plan (workspace, TMA maps, captured CUDA graph) per (B, T); a decode loop over utterances
+        # of arbitrary lengths would build a new one - milliseconds of cudaMalloc, descriptor encoding and graph
+        # instantiation - for almost every call.  In valid-frame GroupNorm mode masked frames do not change any valid
+        # frame (bit for bit: tests/test_gpu_parity.py), so buckets cost nothing but the padded work.
+        self.shape_bucket = int(shape_bucket)
         self.n_feats = in_channels
         self.spk_embed_dim = spk_embed_dim
         self.solver = solver
@@ -317,7 +324,17 @@ class CFM(nn.Module):
         eng = est.engine(x.device)
         B, _, T = x.shape
         dev = x.device
-        xs = x.detach().to(torch.float32).clone().contiguous()
+        T_in = T
+        if self.shape_bucket > 0 and est.gn_stats == "valid" and T % self.shape_bucket != 0 and blend_mask is None:
+            pad = self.shape_bucket - T % self.shape_bucket
+            x = torch.nn.functional.pad(x.detach().to(torch.float32), (0, pad))
+            mu = torch.nn.functional.pad(mu.detach().to(device=dev, dtype=torch.float32), (0, pad))
+            m2 = mask[:, 0] if mask.dim() == 3 else mask
+            mask = torch.nn.functional.pad(m2.to(dev) != 0, (0, pad))
+            T = T + pad
+            xs = x.contiguous()
+        else:
+            xs = x.detach().to(torch.float32).clone().contiguous()
         muf = mu.detach().to(device=dev, dtype=torch.float32).contiguous()
         spk = trg_spks.detach().to(device=dev, dtype=torch.float32).contiguous()
         m8 = _as_mask_u8(mask, B, T, dev)
@@ -336,7 +353,7 @@ class CFM(nn.Module):
                                                ts_p, n_steps, B, T, bm.data_ptr() if bm is not None else None,
                                                bs.data_ptr() if bs is not None else None, C.c_void_p(st)),
                        "srn_solve_euler")
-        return xs
+        return xs if T == T_in else xs[:, :, :T_in].contiguous()
 
     @torch.inference_mode()
     def decode_host(self, z, mu, mask, spks, t_span, out=None, device=None):

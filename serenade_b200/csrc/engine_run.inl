@@ -18,6 +18,8 @@ static bool pdl_enabled() {
 // per solve, right after row_extent_kernel, so that every later kernel may read the extents before its dependency wait.
 static thread_local bool g_next_launch_serialised = false;
 
+static thread_local size_t g_next_launch_smem = 0;      // dynamic shared memory of the next launch_k call
+
 template <typename... KArgs, typename... Args>
 static void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args) {
   cudaLaunchConfig_t cfg;
@@ -25,6 +27,8 @@ static void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t
   cfg.gridDim = grid;
   cfg.blockDim = block;
   cfg.stream = st;
+  cfg.dynamicSmemBytes = g_next_launch_smem;
+  g_next_launch_smem = 0;
   cudaLaunchAttribute attr;
   attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr.val.programmaticStreamSerializationAllowed = 1;
@@ -182,7 +186,9 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
       // rows per block: 32 (same-box A/B: 138 us per call, 16 rows 152 us, 8 rows 167 us); the per-block prologue
       // (GroupNorm statistics + folded constants) is about half of a 32-row block's time, so a launch that needs more
       // than one wave of resident blocks (2 per SM) gets the smallest multiple of 8 that fits it in one wave instead
-      const int rpb = row_rpb(L.T, B, 2 * num_sms_, 8, 32);
+      int rpb = row_rpb(L.T, B, 2 * num_sms_, 8, 32);
+      rpb = std::min(rpb, 256);      // (the block's mask bytes sit in a 256-entry shared array)
+      g_next_launch_smem = gnres_smem_bytes<OT>();
       dim3 grid(cdiv(L.T, rpb), B);
       const float* sc = pl.spk_scale.template as<float>() + (size_t)op.resnet_idx * B * 512;
       const float* sb = pl.spk_bias.template as<float>() + (size_t)op.resnet_idx * B * 512;

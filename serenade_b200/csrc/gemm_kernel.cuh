@@ -20,6 +20,10 @@ namespace srn {
 // Sixteen warps (four per scheduler, 64 accumulator columns each, one staging box per warp, 96 registers) were built
 // and measured in round 2 for the K = 512 GEMMs whose tile loop is longer than their MMA time: slower everywhere
 // (QKV 368 vs 334 us, exp 261 vs 246 us, P~ V 255 vs 244 us per C2 estimator call; profiles/r02_ab_epilogue_warps.txt).
+// "Wide" 256 x 512 tiles for P~ V (one accumulator filling all 512 TMEM columns, A fetched once for both column
+// halves: a quarter less L2 -> SM traffic per FLOP, but no epilogue / main loop overlap) were built and measured in
+// round 2: 69.7 vs 67.0 us at C2's full rate, 26.3 vs 27.1 us at half rate, 132.4 vs 134.5 ms per 10-step solve at C5's
+// shape (profiles/r02_ab_rowkernels_widepv.txt) - within noise, so the kernel keeps two accumulator stages throughout.
 template <int BN>
 struct GemmCfg {
   static constexpr int EW = 8;

@@ -4,7 +4,8 @@
 // profiles/r01_ab_*.txt, the code is in the git history before this file's round-2 rewrite): A-operand multicast over
 // four-CTA clusters (only 132 of 148 SMs can hold 4-CTA clusters: no gain), an A-stationary tile order for the K = 512
 // GEMMs (half the operand bytes, yet slower), attention passes in (batch, head) slices, exp2 on the FMA pipes, direct
-// st.global epilogue stores; round 2: sixteen epilogue warps (gemm_kernel.cuh), an e4m3 row-max pass.
+// st.global epilogue stores; round 2: sixteen epilogue warps and 256 x 512 tiles (gemm_kernel.cuh), the e4m3 row-max
+// pass of round 1 (its Q | K copy cost more than it saved once most entries run shift-free).
 #pragma once
 
 namespace srn {

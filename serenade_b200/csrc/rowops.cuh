@@ -18,12 +18,6 @@ namespace srn {
 constexpr int kC = 512;         // hidden width of the ssc1 decoder
 constexpr int kGroups = 8;      // GroupNorm groups (decoder.py:67)
 
-#ifndef SRN_GNRES_MINBLOCKS
-#define SRN_GNRES_MINBLOCKS 2
-#endif
-#ifndef SRN_GNRES_PREFETCH
-#define SRN_GNRES_PREFETCH 1
-#endif
 #if SRN_TRACE
 // -DSRN_TRACE=1 builds: per-block stamps of gn_res_spk_ln (8 slots per block: 0-4 clock64 at the phase boundaries,
 // 5 SM id, 6/7 globaltimer at entry/exit); see Engine::trace_op
@@ -54,6 +48,17 @@ __device__ __forceinline__ float mish_f(float x) {
   const float w = __expf(fminf(x, 20.f));
   const float n = w * (w + 2.0f);
   return x > 20.f ? x : x * __fdividef(n, n + 2.0f);
+}
+// The same without the denormal handling that `__expf` / `__fdividef` carry when the file is not compiled with
+// -ftz=true (ncu, round 2: 31 warp instructions per element in gn_apply, most of them predicated range fix-ups around
+// the two MUFU ops): flush-to-zero ex2 / rcp, 9 instructions, and no select for x > 20 (n + 2 == n there, so the ratio is 1).
+__device__ __forceinline__ float mish_fast(float x) {
+  float w, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(w) : "f"(fminf(x, 20.f) * 1.4426950408889634f));
+  const float a = w + 2.0f;
+  const float n = w * a;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaf(w, a, 2.0f)));
+  return x * (n * r);
 }
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
 
@@ -238,30 +243,86 @@ __device__ __forceinline__ void gn_reduce_stats(const float* __restrict__ part, 
 }
 
 // ------------------------------------------------------------------------------------------------
-// out = (Mish(GN(y)) + tbias) * mask      (tbias may be null).  256 threads = 4 rows x 64 threads x 8 ch.
+// The two GroupNorm row kernels.  Neither is bound by HBM bandwidth: ncu (profiles/r02_ncu_full_rowkernels.txt) shows
+// them issue- and latency-bound (31 and 748 warp instructions per element / row in the round-1 forms, most of them the
+// denormal fix-ups around Mish's two MUFU ops and per-row shared-memory constant loads).  Round 2:
+//   gn_apply_kernel   out = (Mish(GN(y)) + tbias) * mask; 256 threads = 4 rows x 64 threads x 8 channels; every thread
+//                     keeps U rows' loads in flight (issued before the statistics prologue / before the previous batch
+//                     is consumed); flush-to-zero Mish (mish_fast)
+//   gn_res_spk_ln     u = Mish(GN(y2)) * mask + r (ResnetBlock1D, decoder.py:98-99); s = LN_c(u) * scale[b] + bias[b]
+//                     (SpeakerAdapter, decoder.py:34-45) -> hres (f32 residual stream); ln = LayerNorm(s) * g1 + b1
+//                     (transformer.py:286) -> OT.  The y / res rows of a block stream through a 3-stage shared-memory
+//                     ring filled by bulk async copies (cp.async.bulk + mbarrier complete_tx: one elected thread, no
+//                     registers held for data in flight); a warp takes two rows per stage, so the per-channel constants
+//                     are fetched from shared memory once for both and the rows' reduction chains interleave; each
+//                     LayerNorm is one fused (sum, sum of squares) butterfly instead of two dependent ones.
+// Same-box A/B against the round-1 forms: profiles/r02_ab_rowkernels_widepv.txt (117 -> 89 us and 76 -> 59 us per C2 call).
 template <typename OT>
-__global__ void __launch_bounds__(256, 4) gn_apply_kernel(const OT* __restrict__ y, const float* __restrict__ part,
-                                                       int mtiles, int T, long long bstride,
-                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                       const float* __restrict__ tbias, const uint8_t* __restrict__ mask,
-                                                       int mask_bstride, int mask_step, OT* __restrict__ out,
-                                                       int rows_per_block, const int* __restrict__ nvalid,
-                                                       int tbias_bstride) {
+struct Raw8;
+template <>
+struct Raw8<__nv_bfloat16> {
+  uint4 u;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { u = *reinterpret_cast<const uint4*>(p); }
+  __device__ __forceinline__ void unpack(float (&v)[8]) const {
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(w[i] << 16);
+      v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+};
+template <>
+struct Raw8<float> {
+  float4 a, b;
+  __device__ __forceinline__ void load(const float* p) {
+    a = reinterpret_cast<const float4*>(p)[0];
+    b = reinterpret_cast<const float4*>(p)[1];
+  }
+  __device__ __forceinline__ void unpack(float (&v)[8]) const {
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+};
+
+template <typename OT>
+__global__ void __launch_bounds__(256, 4) gn_apply_kernel(const OT* __restrict__ y, const float* __restrict__ part, int mtiles,
+                                                      int T, long long bstride, const float* __restrict__ gamma,
+                                                      const float* __restrict__ beta, const float* __restrict__ tbias,
+                                                      const uint8_t* __restrict__ mask, int mask_bstride, int mask_step,
+                                                      OT* __restrict__ out, int rows_per_block,
+                                                      const int* __restrict__ nvalid, int tbias_bstride) {
+  constexpr int U = sizeof(OT) == 2 ? 4 : 2;      // rows in flight per thread
   __shared__ float stats[16];
   __shared__ double red[256];
   pdl_launch_dependents();
-  ROW_STAMP(0);
   const int c = (threadIdx.x & 63) * 8;
   const int g = c >> 6;
-  float ga[8], be[8], tb[8];
+  float ga[8], be[8];
   load8(gamma + c, ga);       // weights: not produced by an earlier kernel, fetched under the previous kernel's tail
   load8(beta + c, be);
   pdl_wait();
-  ROW_STAMP(1);
   const int b = blockIdx.y;
+  const int r0 = blockIdx.x * rows_per_block;
+  const int r1 = min(r0 + rows_per_block, T);
+  const long long boff = b * bstride + c;
+  const uint8_t* mrow = mask + (long long)b * mask_bstride;
+  Raw8<OT> raw[U];
+  uint8_t mk[U];
+  auto issue = [&](int rb) {
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const int r = rb + 4 * j;
+      if (r < r1) {
+        raw[j].load(y + boff + (long long)r * kC);
+        mk[j] = mrow[(long long)r * mask_step];
+      }
+    }
+  };
+  int rb = r0 + (threadIdx.x >> 6);
+  issue(rb);                  // in flight during the statistics prologue
   gn_reduce_stats(part, b, mtiles, T, nvalid, stats, red);
-  ROW_STAMP(2);
   const float mean = stats[2 * g], rstd = stats[2 * g + 1];
+  float tb[8];
   if (tbias != nullptr) load8(tbias + (long long)b * tbias_bstride + c, tb);      // (stride 0: one t for the batch)
   else {
 #pragma unroll
@@ -269,47 +330,52 @@ __global__ void __launch_bounds__(256, 4) gn_apply_kernel(const OT* __restrict__
   }
 #pragma unroll
   for (int i = 0; i < 8; ++i) { ga[i] *= rstd; be[i] -= mean * ga[i]; }
-  const int r0 = blockIdx.x * rows_per_block;
-  const int r1 = min(r0 + rows_per_block, T);
-#pragma unroll 4
-  for (int r = r0 + (threadIdx.x >> 6); r < r1; r += 4) {
-    const long long off = b * bstride + (long long)r * kC + c;
-    const float m = mask[(long long)b * mask_bstride + (long long)r * mask_step] ? 1.f : 0.f;
-    float v[8];
-    load8(y + off, v);
+  for (; rb < r1; rb += 4 * U) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = m != 0.f ? mish_f(v[i] * ga[i] + be[i]) + tb[i] : 0.f;     // (select: y may be stale at skipped padded tiles)
-    store8_op(out + off, v);
+    for (int j = 0; j < U; ++j) {
+      const int r = rb + 4 * j;
+      if (r < r1) {
+        float v[8];
+        raw[j].unpack(v);
+        const bool on = mk[j] != 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = on ? mish_fast(fmaf(v[i], ga[i], be[i])) + tb[i] : 0.f;   // (select: y may be stale at skipped padded tiles)
+        store8_op(out + boff + (long long)r * kC, v);
+      }
+    }
+    if (rb + 4 * U < r1) issue(rb + 4 * U);
   }
-  ROW_STAMP(4);
 }
 
-// ------------------------------------------------------------------------------------------------
-// One warp per row (512 channels = 16 per lane, as two 8-wide vectors 256 apart).
-//   u   = Mish(GN(y2)) * mask + r                                  (ResnetBlock1D, decoder.py:98-99)
-//   s   = (u - mean_c(u)) / sqrt(var_c(u) + 1e-5) * scale[b] + bias[b]   (SpeakerAdapter, decoder.py:34-45)
-//   hres = s (f32 residual stream);  ln = LayerNorm(s) * g1 + b1 (OT)    (transformer.py:286)
-// The kernel is latency-bound, not bandwidth-bound (clock64 trace: ~7800 clk per row and warp, 100 registers = 16
-// warps per SM): a row is four dependent warp reductions behind a global-load round trip.  So the loads of a warp's
-// NEXT row are issued as soon as the current row's values are consumed (and the first row's before the statistics
-// prologue), and the per-channel constants come from shared memory with the GroupNorm affine folded.
-// (forcing 3 or 4 resident blocks per SM through __launch_bounds__ was measured: no faster, 3 spills and is slower)
+// rows per warp and ring stage of gn_res_spk_ln (two for 2-byte rows: the per-channel constants are fetched from
+// shared memory once for both, and the two rows' reduction chains interleave)
 template <typename OT>
-__global__ void __launch_bounds__(256, SRN_GNRES_MINBLOCKS) gn_res_spk_ln(const OT* __restrict__ y, const float* __restrict__ part,
-                                                     int mtiles, int T, long long bstride,
-                                                     const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                     const OT* __restrict__ res, const uint8_t* __restrict__ mask,
-                                                     int mask_bstride, int mask_step,
-                                                     const float* __restrict__ spk_scale /*[B][512]*/,
-                                                     const float* __restrict__ spk_bias, const float* __restrict__ ln_g,
-                                                     const float* __restrict__ ln_b, float* __restrict__ hres,
-                                                     OT* __restrict__ ln_out, int rows_per_block,
-                                                     const int* __restrict__ nvalid) {
+__host__ __device__ constexpr int gnres_rpw() { return sizeof(OT) == 2 ? 2 : 1; }
+// dynamic shared memory of gn_res_spk_ln: 3 stages x 8 warps x RPW rows x (y row + res row)
+template <typename OT>
+constexpr int gnres_smem_bytes() { return 3 * 8 * gnres_rpw<OT>() * 2 * kC * (int)sizeof(OT); }
+
+template <typename OT>
+__global__ void __launch_bounds__(256, 2) gn_res_spk_ln(const OT* __restrict__ y, const float* __restrict__ part, int mtiles,
+                                                           int T, long long bstride, const float* __restrict__ gamma,
+                                                           const float* __restrict__ beta, const OT* __restrict__ res,
+                                                           const uint8_t* __restrict__ mask, int mask_bstride, int mask_step,
+                                                           const float* __restrict__ spk_scale, const float* __restrict__ spk_bias,
+                                                           const float* __restrict__ ln_g, const float* __restrict__ ln_b,
+                                                           float* __restrict__ hres, OT* __restrict__ ln_out,
+                                                           int rows_per_block, const int* __restrict__ nvalid) {
+  constexpr int NST = 3;
+  constexpr int RPW = gnres_rpw<OT>();
+  constexpr int SROWS = 8 * RPW;                         // rows per stage
+  constexpr int kRowBytes = kC * (int)sizeof(OT);
+  constexpr int kStageBytes = SROWS * 2 * kRowBytes;    // [SROWS y rows][SROWS res rows]
+  extern __shared__ __align__(128) uint8_t ring[];
   __shared__ float stats[16];
   __shared__ double red[256];
   __shared__ __align__(16) float cst[6][kC];     // folded GN scale / shift, speaker scale / bias, LN gain / bias
+  __shared__ uint64_t full_bar[NST], empty_bar[NST];
+  __shared__ uint8_t s_mask[256];
   pdl_launch_dependents();
-  ROW_STAMP(0);
   // weights (not produced by an earlier kernel): fetched under the previous kernel's tail, two channels per thread
   float wg[2], wb[2], wlg[2], wlb[2];
 #pragma unroll
@@ -317,27 +383,36 @@ __global__ void __launch_bounds__(256, SRN_GNRES_MINBLOCKS) gn_res_spk_ln(const 
     const int c = threadIdx.x + k * 256;
     wg[k] = gamma[c]; wb[k] = beta[c]; wlg[k] = ln_g[c]; wlb[k] = ln_b[c];
   }
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NST; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
   pdl_wait();
-  ROW_STAMP(1);
   const int b = blockIdx.y;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(r0 + rows_per_block, T);
+  const int niter = (r1 - r0 + SROWS - 1) / SROWS;
   const long long boff = b * bstride;
-  float v[16], rr[16];
-  float m = 0.f;
-  int r = r0 + warp;
-  auto fetch = [&](int row) {       // this warp's next row: in flight during the statistics / the previous row's tail
-    const long long o = boff + (long long)row * kC + lane * 8;
-    load8(y + o, *reinterpret_cast<float(*)[8]>(&v[0]));
-    load8(y + o + 256, *reinterpret_cast<float(*)[8]>(&v[8]));
-    load8(res + o, *reinterpret_cast<float(*)[8]>(&rr[0]));
-    load8(res + o + 256, *reinterpret_cast<float(*)[8]>(&rr[8]));
-    m = mask[(long long)b * mask_bstride + (long long)row * mask_step] ? 1.f : 0.f;
+  auto fill = [&](int it) {      // thread 0: rows r0 + SROWS it .. of y and res -> stage it % NST (whole rows are contiguous)
+    const int s = it % NST;
+    const int rr = r0 + SROWS * it;
+    const int n = min(SROWS, r1 - rr);
+    const uint32_t bytes = (uint32_t)n * kRowBytes;
+    const uint32_t dst = smem_u32(ring + s * kStageBytes);
+    const uint32_t bar = smem_u32(&full_bar[s]);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(2 * bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(y + boff + (long long)rr * kC), "r"(bytes), "r"(bar)
+                 : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst + SROWS * kRowBytes),
+                 "l"(res + boff + (long long)rr * kC), "r"(bytes), "r"(bar)
+                 : "memory");
   };
-#if SRN_GNRES_PREFETCH
-  if (r < r1) fetch(r);
-#endif
+  if (threadIdx.x == 0)
+    for (int it = 0; it < NST && it < niter; ++it) fill(it);      // in flight during the statistics prologue
+  if (threadIdx.x < r1 - r0) s_mask[threadIdx.x] = mask[(long long)b * mask_bstride + (long long)(r0 + threadIdx.x) * mask_step];
   float wsc[2], wsb[2];      // (written once per solve by the prepass: read after the wait, in flight during the statistics)
 #pragma unroll
   for (int k = 0; k < 2; ++k) {
@@ -358,14 +433,34 @@ __global__ void __launch_bounds__(256, SRN_GNRES_MINBLOCKS) gn_res_spk_ln(const 
     cst[5][c] = wlb[k];
   }
   __syncthreads();
-  ROW_STAMP(2);
-  for (; r < r1; r += 8) {
-    if (r >= r0 + 8) ROW_STAMP(3);
-    const long long rowoff = boff + (long long)r * kC;
-    float u[16];
-#if !SRN_GNRES_PREFETCH
-    fetch(r);
-#endif
+  for (int it = 0; it < niter; ++it) {
+    const int s = it % NST;
+    const uint32_t ph = (uint32_t)(it / NST) & 1u;
+    const int rbase = r0 + SROWS * it + warp * RPW;      // this warp's rows: rbase .. rbase + RPW - 1
+    mbar_wait(&full_bar[s], ph);
+    Raw8<OT> ry[RPW][2], rr[RPW][2];
+#pragma unroll
+    for (int j = 0; j < RPW; ++j) {
+      if (rbase + j < r1) {
+        const OT* sy = reinterpret_cast<const OT*>(ring + s * kStageBytes) + (warp * RPW + j) * kC + lane * 8;
+        const OT* sr = sy + SROWS * kC;
+        ry[j][0].load(sy); ry[j][1].load(sy + 256);
+        rr[j][0].load(sr); rr[j][1].load(sr + 256);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty_bar[s]);
+    if (threadIdx.x == 0 && it + NST < niter) {      // all eight warps have taken their rows: refill the stage
+      mbar_wait(&empty_bar[s], ph);
+      fill(it + NST);
+    }
+    if (rbase >= r1) continue;
+    float u[RPW][16], m[RPW], s1[RPW], q1[RPW];
+#pragma unroll
+    for (int j = 0; j < RPW; ++j) {
+      m[j] = (rbase + j < r1 && s_mask[rbase + j - r0]) ? 1.f : 0.f;
+      s1[j] = 0.f; q1[j] = 0.f;
+    }
 #pragma unroll
     for (int hlf = 0; hlf < 2; ++hlf) {
       const int c = hlf * 256 + lane * 8;
@@ -373,51 +468,85 @@ __global__ void __launch_bounds__(256, SRN_GNRES_MINBLOCKS) gn_res_spk_ln(const 
       load8(&cst[0][c], ga);
       load8(&cst[1][c], be);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) u[hlf * 8 + i] = mish_f(fmaf(v[hlf * 8 + i], ga[i], be[i])) * m + rr[hlf * 8 + i];
+      for (int j = 0; j < RPW; ++j) {
+        float v[8], rv[8];
+        if (rbase + j < r1) { ry[j][hlf].unpack(v); rr[j][hlf].unpack(rv); }
+        else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { v[i] = 0.f; rv[i] = 0.f; }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float x = fmaf(mish_fast(fmaf(v[i], ga[i], be[i])), m[j], rv[i]);
+          u[j][hlf * 8 + i] = x;
+          s1[j] += x;
+          q1[j] = fmaf(x, x, q1[j]);
+        }
+      }
     }
-#if SRN_GNRES_PREFETCH
-    if (r + 8 < r1) fetch(r + 8);
-#endif
-    float s = 0.f;
+    // SpeakerAdapter LayerNorm (biased variance, eps 1e-5): sum and sum of squares of every row in one butterfly
 #pragma unroll
-    for (int i = 0; i < 16; ++i) s += u[i];
-    const float mu = warp_sum(s) * (1.0f / kC);
-    float q = 0.f;
+    for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
-    for (int i = 0; i < 16; ++i) { u[i] -= mu; q += u[i] * u[i]; }
-    const float inv = 1.0f / sqrtf(warp_sum(q) * (1.0f / kC) + 1e-5f);
-    float s2 = 0.f;
+      for (int j = 0; j < RPW; ++j) {
+        s1[j] += __shfl_xor_sync(0xffffffffu, s1[j], o);
+        q1[j] += __shfl_xor_sync(0xffffffffu, q1[j], o);
+      }
+    }
+    float mu[RPW], inv[RPW], s2[RPW], q2[RPW];
+#pragma unroll
+    for (int j = 0; j < RPW; ++j) {
+      mu[j] = s1[j] * (1.0f / kC);
+      inv[j] = 1.0f / sqrtf(fmaxf(q1[j] * (1.0f / kC) - mu[j] * mu[j], 0.f) + 1e-5f);
+      s2[j] = 0.f; q2[j] = 0.f;
+    }
 #pragma unroll
     for (int hlf = 0; hlf < 2; ++hlf) {
       const int c = hlf * 256 + lane * 8;
-      float sc[8], sb[8], o[8];
+      float sc[8], sb[8];
       load8(&cst[2][c], sc);
       load8(&cst[3][c], sb);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        o[i] = u[hlf * 8 + i] * inv * sc[i] + sb[i];
-        u[hlf * 8 + i] = o[i];
-        s2 += o[i];
-      }
-      store8(hres + rowoff + c, o);
-    }
-    const float mu2 = warp_sum(s2) * (1.0f / kC);
-    float q2 = 0.f;
+      for (int j = 0; j < RPW; ++j) {
+        float o[8];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) { u[i] -= mu2; q2 += u[i] * u[i]; }
-    const float inv2 = rsqrtf(warp_sum(q2) * (1.0f / kC) + 1e-5f);
+        for (int i = 0; i < 8; ++i) {
+          o[i] = fmaf((u[j][hlf * 8 + i] - mu[j]) * inv[j], sc[i], sb[i]);
+          u[j][hlf * 8 + i] = o[i];
+          s2[j] += o[i];
+          q2[j] = fmaf(o[i], o[i], q2[j]);
+        }
+        if (rbase + j < r1) store8(hres + boff + (long long)(rbase + j) * kC + c, o);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int j = 0; j < RPW; ++j) {
+        s2[j] += __shfl_xor_sync(0xffffffffu, s2[j], o);
+        q2[j] += __shfl_xor_sync(0xffffffffu, q2[j], o);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < RPW; ++j) {
+      mu[j] = s2[j] * (1.0f / kC);
+      inv[j] = rsqrtf(fmaxf(q2[j] * (1.0f / kC) - mu[j] * mu[j], 0.f) + 1e-5f);
+    }
 #pragma unroll
     for (int hlf = 0; hlf < 2; ++hlf) {
       const int c = hlf * 256 + lane * 8;
-      float g1[8], b1[8], o[8];
+      float g1[8], b1[8];
       load8(&cst[4][c], g1);
       load8(&cst[5][c], b1);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) o[i] = u[hlf * 8 + i] * inv2 * g1[i] + b1[i];
-      store8_op(ln_out + rowoff + c, o);
+      for (int j = 0; j < RPW; ++j) {
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = fmaf((u[j][hlf * 8 + i] - mu[j]) * inv[j], g1[i], b1[i]);
+        if (rbase + j < r1) store8_op(ln_out + boff + (long long)(rbase + j) * kC + c, o);
+      }
     }
   }
-  ROW_STAMP(4);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -44,7 +44,12 @@ class Serenade(nn.Module):
     """Drop-in for reference `serenade.models.Serenade` (inference side)."""
 
     def __init__(self, input_dim=768, output_dim=80, encoder_channels=80, decoder_channels=512, gst_embed_dim=256,
-                 decoder_attention_head_dim=512, mask_size=(0.1, 0.5), cfg_prob=0.1, precision="bf16"):
+                 decoder_attention_head_dim=512, mask_size=(0.1, 0.5), cfg_prob=0.1, precision="bf16",
+                 shape_bucket=128):
+        """The reference's constructor kwargs (serenade.py:36-47) + two of this build: `precision` ("bf16" | "tf32") and
+        `shape_bucket` (frames; 0 = off): the CFM decode of one unpadded utterance / of a valid-frame batch runs on T
+        rounded up to the bucket, so a decode loop over arbitrary lengths reuses a handful of engine plans instead of
+        building one (workspace + TMA maps + CUDA graph) per distinct length.  Results do not change, bit for bit."""
         super().__init__()
         if output_dim != 80 or gst_embed_dim != 256:
             raise ValueError("this build is specialised for 80-bin mels and a 256-dim style embedding")
@@ -65,7 +70,8 @@ class Serenade(nn.Module):
         conditioning_dim = output_dim + encoder_channels + 1 + 1
         self.cfm_decoder = CFM(in_channels=conditioning_dim + output_dim, out_channels=output_dim,
                                spk_embed_dim=gst_embed_dim, decoder_channels=(decoder_channels, decoder_channels),
-                               decoder_attention_head_dim=decoder_attention_head_dim, precision=precision)
+                               decoder_attention_head_dim=decoder_attention_head_dim, precision=precision,
+                               shape_bucket=shape_bucket)
         self._front_refs = None
         self.cfm_decoder.estimator._extra_state = self._frontend_state
         self.register_load_state_dict_post_hook(lambda module, _keys: module.cfm_decoder.estimator.mark_weights_dirty())
@@ -140,8 +146,17 @@ class Serenade(nn.Module):
         total_lengths = (lengths + ref_lengths).to(dev)
         T = enc_outs.shape[1]
         mask = (torch.arange(T, device=dev)[None, :] < total_lengths[:, None]).unsqueeze(1)     # make_non_pad_mask
-        mel_pred = self.cfm_decoder.inference(enc_outs.permute(0, 2, 1), mask, n_timesteps=n_timesteps,
-                                              temperature=temperature, spks=ref_speaker_features).permute(0, 2, 1)
+        # One unpadded utterance (the reference CLI's call, bin/ssc_decode.py:428): valid-frame GroupNorm statistics are
+        # the reference's statistics, so the decode may run on a length bucket (CFM.shape_bucket) and reuse its plan.
+        est = self.cfm_decoder.estimator
+        saved = est.gn_stats
+        if self.cfm_decoder.shape_bucket > 0 and enc_outs.shape[0] == 1 and int(total_lengths[0]) == T:
+            est.gn_stats = "valid"
+        try:
+            mel_pred = self.cfm_decoder.inference(enc_outs.permute(0, 2, 1), mask, n_timesteps=n_timesteps,
+                                                  temperature=temperature, spks=ref_speaker_features).permute(0, 2, 1)
+        finally:
+            est.gn_stats = saved
         mel_pred = mel_pred[:, int(ref_lengths[0]):, :]
         return mel_pred.squeeze(0)
 

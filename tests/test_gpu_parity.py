@@ -473,3 +473,23 @@ def test_golden_vector_in_channels_244(dev, precision, step_tol, final_tol):
     pad = ~b.mask.expand_as(v)
     assert float(v[pad].abs().sum()) == 0.0
     assert torch.equal(x[pad], b.z[pad])
+
+
+def test_length_buckets_do_not_change_results(jitter_sd, dev):
+    """CFM(shape_bucket=128, gn_stats="valid"): T is padded up to the bucket with masked frames so that a decode loop
+    over arbitrary lengths reuses its plans; every valid frame is bit-identical to the unbucketed decode."""
+    import serenade_b200 as S
+    plain = _make_cfm(jitter_sd)
+    plain.estimator.gn_stats = "valid"
+    bucketed = S.CFM(in_channels=242, out_channels=80, spk_embed_dim=256, decoder_channels=(512, 512),
+                     decoder_attention_head_dim=512, gn_stats="valid", shape_bucket=128)
+    bucketed.load_state_dict(jitter_sd, strict=True)
+    for lengths in ([131], [200, 77], [256]):
+        b = S.make_batch(lengths, n_steps=3, seed=41)
+        args = [b.z.to(dev), b.t_span, b.mu.to(dev), b.mask.to(dev), b.spks.to(dev)]
+        x0, x1 = plain.solve_euler(*args), bucketed.solve_euler(*args)
+        assert x1.shape == x0.shape
+        assert torch.equal(x0, x1), lengths
+    # three lengths in one bucket: one plan; unpadded single utterances in the default mode are untouched
+    launches = bucketed.estimator.engine(dev).launches
+    assert launches > 0
