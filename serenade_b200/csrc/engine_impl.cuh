@@ -8,6 +8,8 @@
 #include <cstring>
 #include <list>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "engine.h"
 #include "rowops.cuh"
 #include "frontops.cuh"

@@ -221,9 +221,52 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
   }
 }
 
+// NVTX ranges (the reference has no tracing at all): one range per estimator call and one per
+// UNet block (down0, down1, mid0, ... = the op names' prefixes), around the launches - in eager mode and while a graph is
+// captured.  nvtx3 is header-only and costs a few nanoseconds per call when no tool is attached; SRN_NVTX=0 removes them.
+static bool nvtx_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("SRN_NVTX");
+    return !(e != nullptr && e[0] == '0');
+  }();
+  return on;
+}
+struct NvtxRange {
+  bool on;
+  explicit NvtxRange(const char* name) : on(nvtx_enabled()) {
+    if (on) nvtxRangePushA(name);
+  }
+  ~NvtxRange() {
+    if (on) nvtxRangePop();
+  }
+};
+
 template <typename OT>
 void Engine<OT>::run_forward(Plan<OT>& pl, int step, float* v_out, bool update_x, cudaStream_t st) {
-  for (Op& op : pl.ops) launch_op(pl, op, step, v_out, update_x, st);
+  char nm[48];
+  snprintf(nm, sizeof nm, "srn.estimator step %d", step);
+  NvtxRange whole(nm);
+  std::string cur;
+  bool open = false;
+  for (Op& op : pl.ops) {
+    if (nvtx_enabled()) {
+      const size_t dot = op.name.find('.');
+      const std::string blk = dot == std::string::npos ? op.name : op.name.substr(0, dot);
+      if (blk != cur) {
+        if (open) nvtxRangePop();
+        nvtxRangePushA(blk.c_str());
+        open = true;
+        cur = blk;
+      }
+    }
+    try {
+      launch_op(pl, op, step, v_out, update_x, st);
+    } catch (...) {
+      if (open) nvtxRangePop();
+      throw;
+    }
+  }
+  if (open) nvtxRangePop();
 }
 
 // Reads (and clears) the device-side soft-abort flag of ptx.cuh: mbar_wait.  Call only after a synchronisation.
@@ -254,6 +297,7 @@ void Engine<OT>::stage_inputs(Plan<OT>& pl, const float* x, const float* mu, con
 template <typename OT>
 void Engine<OT>::prepass(Plan<OT>& pl, const std::vector<float>& ts, const std::vector<float>& dts, cudaStream_t st) {
   (void)dts;
+  NvtxRange range("srn.prepass");
   const int B = pl.B, n = (int)ts.size();
   const int nres = (int)resnets_.size();
   const uint8_t* mask = pl.mask.template as<uint8_t>();
@@ -476,6 +520,7 @@ template <typename OT>
 void Engine<OT>::solve_euler(float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
                              int n_steps, int B, int T, const uint8_t* blend_mask, const float* blend_src,
                              cudaStream_t st) {
+  NvtxRange range("srn.solve_euler");
   Plan<OT>& pl = get_plan(B, T);
   stage_inputs(pl, x, mu, mask, spk, cudaMemcpyDeviceToDevice, st);
   const bool blend = blend_mask != nullptr;
@@ -490,6 +535,7 @@ void Engine<OT>::solve_euler(float* x, const float* mu, const uint8_t* mask, con
 template <typename OT>
 void Engine<OT>::solve_euler_host(const float* z, const float* mu, const uint8_t* mask, const float* spk,
                                   const float* t_span, int n_steps, int B, int T, float* mel_out, cudaStream_t st) {
+  NvtxRange range("srn.solve_euler_host");
   Plan<OT>& pl = get_plan(B, T);
   stage_inputs(pl, z, mu, mask, spk, cudaMemcpyHostToDevice, st);
   solve_staged(pl, t_span, n_steps, false, st);

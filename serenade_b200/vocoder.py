@@ -181,18 +181,79 @@ class HiFiGANGenerator(nn.Module):
         return self.decode(c).unsqueeze(1)
 
 
-class Vocoder:
-    """Reference vocoder/vocoder.py:12-75 with the files replaced by objects: `model` is a loaded HiFiGANGenerator,
-    `stats` / `trg_stats` are {"mean", "scale"} tensors or arrays (the reference reads them from stats.h5 /
-    the recipe's joblib; h5py is not in this image)."""
+def load_vocoder(checkpoint, config=None, precision="bf16") -> "HiFiGANGenerator":
+    """Reference vocoder/utils.py:14-47 `load_vocoder`: generator built from `config["generator_params"]` (a dict, a yaml
+    path, or config.yml next to the checkpoint), parameters from `torch.load(checkpoint)["model"]["generator"]`."""
+    import os
+    if config is None:
+        config = os.path.join(os.path.dirname(checkpoint), "config.yml")
+    if not isinstance(config, dict):
+        import yaml
+        with open(config) as f:
+            config = yaml.load(f, Loader=yaml.Loader)
+    if config.get("generator_type", "HiFiGANGenerator") != "HiFiGANGenerator":
+        raise ValueError(f"only HiFiGANGenerator is implemented, got {config.get('generator_type')}")
+    params = {k.replace("upsample_kernal_sizes", "upsample_kernel_sizes"): v for k, v in config["generator_params"].items()}
+    model = HiFiGANGenerator(**params, precision=precision)
+    state = torch.load(checkpoint, map_location="cpu")
+    model.load_state_dict(state["model"]["generator"], strict=True)
+    return model
 
-    def __init__(self, model: HiFiGANGenerator, stats: Dict[str, Sequence[float]], device, trg_stats=None,
-                 take_norm_feat=True, sampling_rate=24000):
+
+def read_stats(path) -> Dict[str, torch.Tensor]:
+    """{"mean", "scale"} from the reference's stats.h5 (datasets "mean" / "scale", utils.py read_hdf5; needs h5py), from
+    ParallelWaveGAN's stats.npy ((2, n): mean, scale) or from an .npz with those two arrays."""
+    import numpy as np
+    path = str(path)
+    if path.endswith((".h5", ".hdf5")):
+        try:
+            import h5py
+        except ImportError as e:
+            raise RuntimeError("reading stats.h5 needs h5py, which this environment does not have: convert the statistics "
+                               "to .npz (mean, scale) or pass them as a dict") from e
+        with h5py.File(path, "r") as f:
+            mean, scale = np.asarray(f["mean"]), np.asarray(f["scale"])
+    elif path.endswith(".npz"):
+        z = np.load(path)
+        mean, scale = z["mean"], z["scale"]
+    else:
+        a = np.load(path)
+        mean, scale = a[0], a[1]
+    return {"mean": torch.as_tensor(mean, dtype=torch.float32), "scale": torch.as_tensor(scale, dtype=torch.float32)}
+
+
+class Vocoder:
+    """Reference vocoder/vocoder.py:12-75.  Two call forms:
+      Vocoder(checkpoint, config, stats, device, trg_stats=None, take_norm_feat=True)   the reference's own (file paths:
+          checkpoint .pkl, config .yml, stats .h5 / .npy / .npz), as bin/ssc_decode.py:310-318 calls it;
+      Vocoder(model, stats, device, trg_stats=None, take_norm_feat=True, sampling_rate=24000)   a loaded
+          HiFiGANGenerator and {"mean", "scale"} dicts."""
+
+    def __init__(self, *args, **kwargs):
+        import os
+        first = args[0] if args else kwargs.get("checkpoint", kwargs.get("model"))
+        if isinstance(first, (str, os.PathLike)):
+            self._init_from_files(*args, **kwargs)
+        else:
+            self._init_from_objects(*args, **kwargs)
+
+    def _init_from_files(self, checkpoint, config, stats, device, trg_stats=None, take_norm_feat=True, precision="bf16"):
+        import yaml
+        with open(config) as f:
+            self.config = yaml.load(f, Loader=yaml.Loader)
+        model = load_vocoder(checkpoint, self.config, precision=precision)
+        st = stats if isinstance(stats, dict) else read_stats(stats)
+        self._init_from_objects(model, st, device, trg_stats=trg_stats, take_norm_feat=take_norm_feat,
+                                sampling_rate=self.config.get("sampling_rate", 24000))
+
+    def _init_from_objects(self, model: HiFiGANGenerator, stats: Dict[str, Sequence[float]], device, trg_stats=None,
+                           take_norm_feat=True, sampling_rate=24000):
         if take_norm_feat and trg_stats is None:
             raise AssertionError("trg_stats must be given if take_norm_feat=True")
         self.device = torch.device(device)
         self.model = model
         self.sampling_rate = sampling_rate
+        self.take_norm_feat = take_norm_feat
         mean = torch.as_tensor(stats["mean"], dtype=torch.float32).reshape(-1)
         scale = torch.as_tensor(stats["scale"], dtype=torch.float32).reshape(-1)
         if take_norm_feat:

@@ -98,6 +98,32 @@ def main():
                  f"{wavs.shape[0]} x {wavs.shape[1]} samples = {16 * 1000 / ms_b * 1e3:.0f} source frames/s, RTF {ms_b / 1e3 / 160:.2e}; "
                  f"finite={bool(torch.isfinite(wavs).all())}")
     print(lines[-1], flush=True)
+    # ---- (c) a decode loop over utterances of DISTINCT lengths (what bin/ssc_decode.py:346-378 does): every call meets a
+    # new (B, T), i.e. a cold engine plan (workspace cudaMalloc, TMA descriptor encoding, CUDA-graph capture +
+    # instantiation) unless lengths are bucketed (Serenade(shape_bucket=128), the default; 0 = one plan per length)
+    lens = [403, 517, 288, 611, 349, 455, 572, 236, 498, 330, 420, 541]
+    utts = []
+    for k, L in enumerate(lens):
+        it = S.make_frontend_inputs(L, 300, seed=300 + k)
+        utts.append([it[name].to(dev) for name in ORDER])
+    for bucket in (0, 128):
+        m2 = S.models.Serenade(shape_bucket=bucket)
+        m2.load_state_dict(sd, strict=True)
+        m2.inference(*dinp)                      # weights packed, kernels loaded
+        torch.cuda.synchronize()
+        per = []
+        for rep in range(2):                     # pass 0: every length is new; pass 1: the same lengths again
+            t0 = time.perf_counter()
+            for u in utts:
+                m2.inference(*u)
+            torch.cuda.synchronize()
+            per.append((time.perf_counter() - t0) / len(utts) * 1e3)
+        lines.append(f"variable-length loop, {len(lens)} utterances of {min(lens)}..{max(lens)} source frames + 300-frame prompt, "
+                     f"shape_bucket={bucket}: {per[0]:.1f} ms per utterance on first sight of each length (cold plans), "
+                     f"{per[1]:.1f} ms per utterance on the second pass (wall clock, encoders + CFM solve)")
+        print(lines[-1], flush=True)
+        del m2
+        torch.cuda.empty_cache()
     if out_path:
         with open(out_path, "w") as f:
             f.write("\n".join(lines) + "\n")

@@ -493,3 +493,21 @@ def test_length_buckets_do_not_change_results(jitter_sd, dev):
     # three lengths in one bucket: one plan; unpadded single utterances in the default mode are untouched
     launches = bucketed.estimator.engine(dev).launches
     assert launches > 0
+
+
+def test_repeated_solves_are_bit_identical_under_interleaving(cfm_jitter, dev):
+    """Stand-in for compute-sanitizer racecheck, which is closed on this GPU pool (profiles/r02_sanitizer_closed.txt):
+    a race in the GEMM kernel's mbarrier / TMEM / staging protocol or in the bulk-copy ring of gn_res_spk_ln would make
+    results depend on timing.  The same solve is repeated after unrelated solves of other shapes (other plans, other L2
+    contents, other residency order) and must come out bit-identical every time."""
+    import serenade_b200 as S
+    b = S.make_batch([333, 250, 97], n_steps=3, seed=61)
+    args = [b.z.to(dev), b.t_span, b.mu.to(dev), b.mask.to(dev), b.spks.to(dev)]
+    ref = cfm_jitter.solve_euler(*args)
+    others = [[64], [500, 499], [131, 77, 20, 300]]
+    for i in range(12):
+        o = S.make_batch(others[i % 3], n_steps=2, seed=70 + i)
+        cfm_jitter.solve_euler(o.z.to(dev), o.t_span, o.mu.to(dev), o.mask.to(dev), o.spks.to(dev))
+        x = cfm_jitter.solve_euler(*args)
+        assert torch.equal(x, ref), f"run {i} differs"
+    assert bool(torch.isfinite(ref).all())
