@@ -109,6 +109,22 @@ int srn_vocoder_hop(SrnHandle* h, int32_t* hop_out);
 int srn_vocoder_decode(SrnHandle* h, const float* mel, const float* scale, const float* shift, int32_t B, int32_t T,
                        float* wave_out, void* stream);
 
+/* CFM loss value from a velocity the caller already holds, WITHOUT any device allocation.  No counterpart in the
+ * reference: added for callers that cannot call cudaMalloc (code under CUDA-graph
+ * capture, tight serving loops, harnesses that forbid it).  Needs no handle; runs on the calling thread's current device.
+ *   loss = sum(((v - u) * mask_l)^2) / (sum(mask_l) * C),  u = x1 - (1 - sigma_min) z   (the tail of srn_cfm_loss; with
+ *   mask_l NULL the sum runs over every frame and the divisor is sum(mask) * C, like the reference's compute_loss)
+ * v, x1, z (B, C, T) f32 DEVICE; mask, mask_l (B, T) u8 DEVICE (mask_l nullable); loss_out one f32 on the DEVICE.
+ * The reduction's only scratch memory, 16 KB of per-block partial sums, is a file-scope `static __device__` array
+ * (csrc/noalloc.cu; every GPU that loads the library holds it until exit), so the call makes no cudaMalloc / cudaFree and
+ * calls no allocating routine.  Limits: B * C * T <= SRN_NOALLOC_MAX_ELEMS, larger calls fail with a message.  All calls
+ * on one device share that array and it keeps the last call's contents (every slot read is rewritten first by the same
+ * call, nothing needs clearing): calls that OVERLAP on the GPU - other streams or threads - race; serialise them. */
+#define SRN_NOALLOC_MAX_ELEMS (1ll << 26)
+int srn_cfm_loss_from_velocity_noalloc(const float* v, const float* x1, const float* z, const uint8_t* mask,
+                                       const uint8_t* mask_l, int32_t B, int32_t C, int32_t T, float sigma_min,
+                                       float* loss_out, void* stream);
+
 /* Number of kernels of this library launched since the handle was created. */
 int64_t srn_launch_count(const SrnHandle* h);
 /* Use one CUDA graph per (B, T, n_steps) for srn_solve_euler (default 1). */

@@ -19,6 +19,7 @@ EXPORTED_SYMBOLS = [
     "srn_debug_enable", "srn_debug_fetch", "srn_profile_ops", "srn_content_encode", "srn_style_encode",
     "srn_set_gn_valid_only", "srn_vocoder_set_dilations", "srn_vocoder_hop", "srn_vocoder_decode",
     "srn_estimator_forward_t", "srn_cfm_loss", "srn_set_option", "srn_softmax_stats",
+    "srn_cfm_loss_from_velocity_noalloc",
 ]
 
 PRECISION_BF16 = 0
@@ -57,12 +58,15 @@ def load_library() -> C.CDLL:
                                  vp]
     lib.srn_solve_euler.argtypes = [vp, f32p, f32p, u8p, f32p, C.POINTER(C.c_float), i32, i32, i32, u8p, f32p, vp]
     lib.srn_solve_euler_host.argtypes = [vp, f32p, f32p, u8p, f32p, C.POINTER(C.c_float), i32, i32, i32, f32p, vp]
+    if hasattr(lib, "srn_cfm_loss_from_velocity_noalloc"):
+        lib.srn_cfm_loss_from_velocity_noalloc.argtypes = [f32p, f32p, f32p, u8p, u8p, i32, i32, i32, C.c_float, f32p, vp]
     lib.srn_launch_count.restype = i64
     lib.srn_launch_count.argtypes = [vp]
     lib.srn_set_use_graph.argtypes = [vp, i32]
     lib.srn_set_gn_valid_only.argtypes = [vp, i32]
-    lib.srn_set_option.argtypes = [vp, C.c_char_p, i32]
-    lib.srn_softmax_stats.argtypes = [vp, C.POINTER(i64)]
+    if hasattr(lib, "srn_set_option"):      # (absent only from older experiment builds loaded with SRN_LIB_VARIANT)
+        lib.srn_set_option.argtypes = [vp, C.c_char_p, i32]
+        lib.srn_softmax_stats.argtypes = [vp, C.POINTER(i64)]
     lib.srn_vocoder_set_dilations.argtypes = [vp, C.POINTER(C.c_int32), i32]
     lib.srn_vocoder_hop.argtypes = [vp, C.POINTER(C.c_int32)]
     lib.srn_vocoder_decode.argtypes = [vp, f32p, f32p, f32p, i32, i32, f32p, vp]
@@ -72,6 +76,8 @@ def load_library() -> C.CDLL:
     lib.srn_content_encode.argtypes = [vp, f32p, i32, i32, f32p, vp]
     lib.srn_style_encode.argtypes = [vp, f32p, i32, i32, f32p, vp]
     for name in EXPORTED_SYMBOLS:
+        if _VARIANT and not hasattr(lib, name):
+            continue
         fn = getattr(lib, name)
         if name not in ("srn_last_error", "srn_launch_count", "srn_version"):
             fn.restype = C.c_int

@@ -14,7 +14,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libserenade_b200.so")
 STAMP = os.path.join(PKG, "build", "stamp.txt")
-SOURCES = ["api.cu", "engine.cu"]
+SOURCES = ["api.cu", "engine.cu", "noalloc.cu"]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 
