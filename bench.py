@@ -508,7 +508,10 @@ def run_c4(args):
         achieved = flops_step / (ms_step / 1e3) / 1e12 / world           # per GPU
         threads = os.cpu_count() or 1
         cfg = CONFIGS["C2"]
-        cpu_fps, cpu_s = _cpu_decode_sample(cfg, threads, *cfg["cpu"])
+        if args.core:      # (scaling sweeps: the CPU leg is the same at every N)
+            cpu_fps, cpu_s = None, 0.0
+        else:
+            cpu_fps, cpu_s = _cpu_decode_sample(cfg, threads, *cfg["cpu"])
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",

@@ -36,7 +36,6 @@ template <typename OT>
 static void configure_kernels() {
   configure_bn<OT, 128>();
   configure_bn<OT, 256>();
-  SRN_CUDA(cudaFuncSetAttribute(gn_res_spk_ln<OT>, cudaFuncAttributeMaxDynamicSharedMemorySize, gnres_smem_bytes<OT>()));
 }
 
 std::unique_ptr<EngineBase> make_engine(const SrnConfig& cfg) {

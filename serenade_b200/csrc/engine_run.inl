@@ -186,9 +186,7 @@ void Engine<OT>::launch_op(Plan<OT>& pl, Op& op, int step, float* v_out, bool up
       // rows per block: 32 (same-box A/B: 138 us per call, 16 rows 152 us, 8 rows 167 us); the per-block prologue
       // (GroupNorm statistics + folded constants) is about half of a 32-row block's time, so a launch that needs more
       // than one wave of resident blocks (2 per SM) gets the smallest multiple of 8 that fits it in one wave instead
-      int rpb = row_rpb(L.T, B, 2 * num_sms_, 8, 32);
-      rpb = std::min(rpb, 256);      // (the block's mask bytes sit in a 256-entry shared array)
-      g_next_launch_smem = gnres_smem_bytes<OT>();
+      const int rpb = row_rpb(L.T, B, 2 * num_sms_, 8, 32);
       dim3 grid(cdiv(L.T, rpb), B);
       const float* sc = pl.spk_scale.template as<float>() + (size_t)op.resnet_idx * B * 512;
       const float* sb = pl.spk_bias.template as<float>() + (size_t)op.resnet_idx * B * 512;
@@ -368,10 +366,10 @@ void Engine<OT>::estimator_forward(const float* x, const float* mu, const uint8_
   pl.staged_ts.clear();
   ensure_step_buffers(pl, 1, cfg_.in_channels, (int)resnets_.size());
   stage_inputs(pl, x, mu, mask, spk, cudaMemcpyDeviceToDevice, st);
-  const float zero = 0.f;
-  SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, &t, 4, cudaMemcpyHostToDevice, st));
-  SRN_CUDA(cudaMemcpyAsync(pl.dts.p, &zero, 4, cudaMemcpyHostToDevice, st));
-  SRN_CUDA(cudaStreamSynchronize(st));   // &t / &zero are stack temporaries
+  // t by value through a one-thread kernel: no staging buffer, so the call never blocks the host (a reference-style
+  // Python Euler loop over `estimator(...)` stays asynchronous) and works under an outer stream capture
+  launch_k(set_scalars_kernel, dim3(1), dim3(32), st, pl.tsteps.template as<float>(), t, pl.dts.template as<float>(), 0.f);
+  ++launches;
   blend_active_ = false;
   prepass(pl, std::vector<float>{t}, std::vector<float>{0.f}, st);
   if (debug) {      // the hoisted time path (decoder.py:48-63, :113-157, :97): time embedding, per-resnet time biases

@@ -251,11 +251,15 @@ __device__ __forceinline__ void gn_reduce_stats(const float* __restrict__ part, 
 //                     is consumed); flush-to-zero Mish (mish_fast)
 //   gn_res_spk_ln     u = Mish(GN(y2)) * mask + r (ResnetBlock1D, decoder.py:98-99); s = LN_c(u) * scale[b] + bias[b]
 //                     (SpeakerAdapter, decoder.py:34-45) -> hres (f32 residual stream); ln = LayerNorm(s) * g1 + b1
-//                     (transformer.py:286) -> OT.  The y / res rows of a block stream through a 3-stage shared-memory
-//                     ring filled by bulk async copies (cp.async.bulk + mbarrier complete_tx: one elected thread, no
-//                     registers held for data in flight); a warp takes two rows per stage, so the per-channel constants
-//                     are fetched from shared memory once for both and the rows' reduction chains interleave; each
-//                     LayerNorm is one fused (sum, sum of squares) butterfly instead of two dependent ones.
+//                     (transformer.py:286) -> OT.  A warp takes two rows per iteration, so the per-channel constants are
+//                     fetched from shared memory once for both and the rows' reduction chains interleave; each LayerNorm
+//                     is one fused (sum, sum of squares) butterfly instead of two dependent ones; the next iteration's
+//                     rows are loaded into registers while the current ones are reduced and stored.
+//                     (A variant that streamed the rows through a shared-memory ring filled by cp.async.bulk was 5 %
+//                     faster in isolation but made the SOLVE irreproducible - about 2 solves in 1000 differed in one clip,
+//                     first differing tensor = this kernel's output, only in the full pipeline: the kernel alone was
+//                     bit-stable over 200 000 launches, tools/stress/rowkernel_stress.cu.  Not understood, so not shipped:
+//                     profiles/r02_determinism.txt.)
 // Same-box A/B against the round-1 forms: profiles/r02_ab_rowkernels_widepv.txt (117 -> 89 us and 76 -> 59 us per C2 call).
 template <typename OT>
 struct Raw8;
@@ -347,73 +351,54 @@ __global__ void __launch_bounds__(256, 4) gn_apply_kernel(const OT* __restrict__
   }
 }
 
-// rows per warp and ring stage of gn_res_spk_ln (two for 2-byte rows: the per-channel constants are fetched from
-// shared memory once for both, and the two rows' reduction chains interleave)
+// rows per warp and iteration of gn_res_spk_ln (two for 2-byte rows: the per-channel constants are fetched from shared
+// memory once for both, and the two rows' reduction chains interleave)
 template <typename OT>
 __host__ __device__ constexpr int gnres_rpw() { return sizeof(OT) == 2 ? 2 : 1; }
-// dynamic shared memory of gn_res_spk_ln: 3 stages x 8 warps x RPW rows x (y row + res row)
-template <typename OT>
-constexpr int gnres_smem_bytes() { return 3 * 8 * gnres_rpw<OT>() * 2 * kC * (int)sizeof(OT); }
-
+// (y / res rows are loaded from global memory straight into registers, one iteration ahead of their use)
 template <typename OT>
 __global__ void __launch_bounds__(256, 2) gn_res_spk_ln(const OT* __restrict__ y, const float* __restrict__ part, int mtiles,
-                                                           int T, long long bstride, const float* __restrict__ gamma,
-                                                           const float* __restrict__ beta, const OT* __restrict__ res,
-                                                           const uint8_t* __restrict__ mask, int mask_bstride, int mask_step,
-                                                           const float* __restrict__ spk_scale, const float* __restrict__ spk_bias,
-                                                           const float* __restrict__ ln_g, const float* __restrict__ ln_b,
-                                                           float* __restrict__ hres, OT* __restrict__ ln_out,
-                                                           int rows_per_block, const int* __restrict__ nvalid) {
-  constexpr int NST = 3;
+                                                               int T, long long bstride, const float* __restrict__ gamma,
+                                                               const float* __restrict__ beta, const OT* __restrict__ res,
+                                                               const uint8_t* __restrict__ mask, int mask_bstride, int mask_step,
+                                                               const float* __restrict__ spk_scale, const float* __restrict__ spk_bias,
+                                                               const float* __restrict__ ln_g, const float* __restrict__ ln_b,
+                                                               float* __restrict__ hres, OT* __restrict__ ln_out,
+                                                               int rows_per_block, const int* __restrict__ nvalid) {
   constexpr int RPW = gnres_rpw<OT>();
-  constexpr int SROWS = 8 * RPW;                         // rows per stage
-  constexpr int kRowBytes = kC * (int)sizeof(OT);
-  constexpr int kStageBytes = SROWS * 2 * kRowBytes;    // [SROWS y rows][SROWS res rows]
-  extern __shared__ __align__(128) uint8_t ring[];
+  constexpr int SROWS = 8 * RPW;                         // rows per block iteration
   __shared__ float stats[16];
   __shared__ double red[256];
   __shared__ __align__(16) float cst[6][kC];     // folded GN scale / shift, speaker scale / bias, LN gain / bias
-  __shared__ uint64_t full_bar[NST], empty_bar[NST];
-  __shared__ uint8_t s_mask[256];
   pdl_launch_dependents();
-  // weights (not produced by an earlier kernel): fetched under the previous kernel's tail, two channels per thread
   float wg[2], wb[2], wlg[2], wlb[2];
 #pragma unroll
   for (int k = 0; k < 2; ++k) {
     const int c = threadIdx.x + k * 256;
     wg[k] = gamma[c]; wb[k] = beta[c]; wlg[k] = ln_g[c]; wlb[k] = ln_b[c];
   }
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < NST; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 8); }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
   pdl_wait();
   const int b = blockIdx.y;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(r0 + rows_per_block, T);
-  const int niter = (r1 - r0 + SROWS - 1) / SROWS;
   const long long boff = b * bstride;
-  auto fill = [&](int it) {      // thread 0: rows r0 + SROWS it .. of y and res -> stage it % NST (whole rows are contiguous)
-    const int s = it % NST;
-    const int rr = r0 + SROWS * it;
-    const int n = min(SROWS, r1 - rr);
-    const uint32_t bytes = (uint32_t)n * kRowBytes;
-    const uint32_t dst = smem_u32(ring + s * kStageBytes);
-    const uint32_t bar = smem_u32(&full_bar[s]);
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(2 * bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                 "l"(y + boff + (long long)rr * kC), "r"(bytes), "r"(bar)
-                 : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst + SROWS * kRowBytes),
-                 "l"(res + boff + (long long)rr * kC), "r"(bytes), "r"(bar)
-                 : "memory");
+  Raw8<OT> ry[RPW][2], rr[RPW][2];
+  uint8_t mk[RPW];
+  auto fetch = [&](int rbase) {       // this warp's rows of the given iteration -> registers
+#pragma unroll
+    for (int j = 0; j < RPW; ++j) {
+      if (rbase + j < r1) {
+        const long long o = boff + (long long)(rbase + j) * kC + lane * 8;
+        ry[j][0].load(y + o); ry[j][1].load(y + o + 256);
+        rr[j][0].load(res + o); rr[j][1].load(res + o + 256);
+        mk[j] = mask[(long long)b * mask_bstride + (long long)(rbase + j) * mask_step];
+      }
+    }
   };
-  if (threadIdx.x == 0)
-    for (int it = 0; it < NST && it < niter; ++it) fill(it);      // in flight during the statistics prologue
-  if (threadIdx.x < r1 - r0) s_mask[threadIdx.x] = mask[(long long)b * mask_bstride + (long long)(r0 + threadIdx.x) * mask_step];
-  float wsc[2], wsb[2];      // (written once per solve by the prepass: read after the wait, in flight during the statistics)
+  int rbase = r0 + warp * RPW;
+  fetch(rbase);               // in flight during the statistics prologue
+  float wsc[2], wsb[2];
 #pragma unroll
   for (int k = 0; k < 2; ++k) {
     const int c = threadIdx.x + k * 256;
@@ -433,32 +418,11 @@ __global__ void __launch_bounds__(256, 2) gn_res_spk_ln(const OT* __restrict__ y
     cst[5][c] = wlb[k];
   }
   __syncthreads();
-  for (int it = 0; it < niter; ++it) {
-    const int s = it % NST;
-    const uint32_t ph = (uint32_t)(it / NST) & 1u;
-    const int rbase = r0 + SROWS * it + warp * RPW;      // this warp's rows: rbase .. rbase + RPW - 1
-    mbar_wait(&full_bar[s], ph);
-    Raw8<OT> ry[RPW][2], rr[RPW][2];
-#pragma unroll
-    for (int j = 0; j < RPW; ++j) {
-      if (rbase + j < r1) {
-        const OT* sy = reinterpret_cast<const OT*>(ring + s * kStageBytes) + (warp * RPW + j) * kC + lane * 8;
-        const OT* sr = sy + SROWS * kC;
-        ry[j][0].load(sy); ry[j][1].load(sy + 256);
-        rr[j][0].load(sr); rr[j][1].load(sr + 256);
-      }
-    }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty_bar[s]);
-    if (threadIdx.x == 0 && it + NST < niter) {      // all eight warps have taken their rows: refill the stage
-      mbar_wait(&empty_bar[s], ph);
-      fill(it + NST);
-    }
-    if (rbase >= r1) continue;
+  for (; rbase < r1; rbase += SROWS) {
     float u[RPW][16], m[RPW], s1[RPW], q1[RPW];
 #pragma unroll
     for (int j = 0; j < RPW; ++j) {
-      m[j] = (rbase + j < r1 && s_mask[rbase + j - r0]) ? 1.f : 0.f;
+      m[j] = (rbase + j < r1 && mk[j]) ? 1.f : 0.f;
       s1[j] = 0.f; q1[j] = 0.f;
     }
 #pragma unroll
@@ -484,7 +448,8 @@ __global__ void __launch_bounds__(256, 2) gn_res_spk_ln(const OT* __restrict__ y
         }
       }
     }
-    // SpeakerAdapter LayerNorm (biased variance, eps 1e-5): sum and sum of squares of every row in one butterfly
+    const int cur = rbase;
+    if (rbase + SROWS < r1) fetch(rbase + SROWS);      // the next rows: in flight during the reductions and stores below
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
@@ -516,7 +481,7 @@ __global__ void __launch_bounds__(256, 2) gn_res_spk_ln(const OT* __restrict__ y
           s2[j] += o[i];
           q2[j] = fmaf(o[i], o[i], q2[j]);
         }
-        if (rbase + j < r1) store8(hres + boff + (long long)(rbase + j) * kC + c, o);
+        if (cur + j < r1) store8(hres + boff + (long long)(cur + j) * kC + c, o);
       }
     }
 #pragma unroll
@@ -543,7 +508,7 @@ __global__ void __launch_bounds__(256, 2) gn_res_spk_ln(const OT* __restrict__ y
         float o[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) o[i] = fmaf((u[j][hlf * 8 + i] - mu[j]) * inv[j], g1[i], b1[i]);
-        if (rbase + j < r1) store8_op(ln_out + boff + (long long)(rbase + j) * kC + c, o);
+        if (cur + j < r1) store8_op(ln_out + boff + (long long)(cur + j) * kC + c, o);
       }
     }
   }
@@ -683,6 +648,13 @@ __global__ void __launch_bounds__(256) gemv_kernel(const float* __restrict__ W, 
   for (int i = lane; i < I; i += 32) acc += w[i] * apply_act(x[i], act_in);
   acc = warp_sum(acc);
   if (lane == 0) out[(long long)s * O + o] = apply_act(acc + (bias ? bias[o] : 0.f), act_out);
+}
+
+// *a = va, *b = vb: scalars handed to the device by value (no host staging buffer, hence no host synchronisation)
+__global__ void set_scalars_kernel(float* __restrict__ a, float va, float* __restrict__ b, float vb) {
+  pdl_launch_dependents();
+  pdl_wait();
+  if (threadIdx.x == 0) { *a = va; *b = vb; }
 }
 
 // emb[s][j] = sin(1000 t_s f_j), emb[s][half + j] = cos(...),  f_j = exp(-j ln(1e4)/(half-1))  (decoder.py:54-63)

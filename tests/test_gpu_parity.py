@@ -511,3 +511,18 @@ def test_repeated_solves_are_bit_identical_under_interleaving(cfm_jitter, dev):
         x = cfm_jitter.solve_euler(*args)
         assert torch.equal(x, ref), f"run {i} differs"
     assert bool(torch.isfinite(ref).all())
+
+
+def test_full_size_solve_is_bit_reproducible(cfm_stock, dev):
+    """The benchmark solve (C2: 16 x 1000 frames, 10 Euler steps) repeated 300 times back to back gives the same bits every
+    time.  Guards against the kind of timing-dependent difference found in round 2 (profiles/r02_determinism.txt: a
+    shared-memory-ring variant of gn_res_spk_ln made about 2 solves in 1000 differ in one clip); tools/determinism_solve.py
+    runs the same check for thousands of solves."""
+    import serenade_b200 as S
+    b = S.make_batch([1000] * 16, n_steps=10, seed=1235, infill=(0.25, 0.75))
+    args = [b.z.to(dev), b.t_span, b.mu.to(dev), b.mask.to(dev), b.spks.to(dev)]
+    ref = cfm_stock.solve_euler(*args)
+    flags = torch.zeros(300, dtype=torch.bool, device=dev)
+    for i in range(300):
+        flags[i] = (cfm_stock.solve_euler(*args) != ref).any()
+    assert int(flags.sum()) == 0, f"{int(flags.sum())} of 300 solves differed from the first"
