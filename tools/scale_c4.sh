@@ -3,7 +3,7 @@
 # bash tools/scale_c4.sh TAG     (under gpurun --gpus 8)
 TAG=${1:-c4}
 O=gpurun_out; mkdir -p $O
-for n in 1 2 4 8; do
+for n in ${SRN_SCALE_NS:-1 2 4 8}; do
   if [ $n = 1 ]; then
     timeout 600 python bench.py --config C4 --core --steps 3 --warmup 3 > $O/${TAG}_c4_n$n.json 2> $O/${TAG}_c4_n$n.err
   else
