@@ -60,6 +60,12 @@ int srn_estimator_forward(SrnHandle* h, const float* x, const float* mu, const u
 int srn_estimator_forward_t(SrnHandle* h, const float* x, const float* mu, const uint8_t* mask, const float* spk,
                             const float* t_host, int32_t B, int32_t T, float* v_out, void* stream);
 
+/* The same with the time(s) in DEVICE memory: t_dev[n_t], n_t = 1 (one time for the whole batch - the 0-dim CUDA tensor
+ * the reference's solve_euler hands its estimator, flow_matching.py:79-86) or n_t = B (one per clip).  The call enqueues
+ * work on `stream` and never waits for it, so a reference-style Python Euler loop over estimator(...) stays asynchronous. */
+int srn_estimator_forward_tdev(SrnHandle* h, const float* x, const float* mu, const uint8_t* mask, const float* spk,
+                               const float* t_dev, int32_t n_t, int32_t B, int32_t T, float* v_out, void* stream);
+
 /* CFM.compute_loss, FORWARD VALUE ONLY (flow_matching.py:95-133; what trainers/ssc.py evaluates on the dev set under
  * no_grad): given the target x1, the noise z and the times t_host[B] the reference would draw,
  *   y = (1 - (1 - sigma_min) t) z + t x1,  u = x1 - (1 - sigma_min) z,

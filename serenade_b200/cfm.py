@@ -232,12 +232,24 @@ class Decoder(nn.Module):
         spk = speaker_features.detach().to(device=dev, dtype=torch.float32).contiguous()
         m8 = _as_mask_u8(mask, B, T, dev)
         out = torch.empty_like(xf)
-        tv = t.detach().reshape(-1).to("cpu", torch.float32) if torch.is_tensor(t) else torch.tensor([float(t)])
-        if tv.numel() not in (1, B):
-            raise ValueError(f"t must be a scalar or hold one time per clip ({B}), got {tv.numel()} values")
+        t_dev = None
+        if torch.is_tensor(t) and t.is_cuda:
+            # a time that already lives on the GPU (the reference's solve_euler hands its estimator a 0-dim CUDA tensor,
+            # flow_matching.py:79-86) stays there: no device-to-host read, the call does not wait for the stream
+            t_dev = t.detach().reshape(-1).to(device=dev, dtype=torch.float32).contiguous()
+            n_t = t_dev.numel()
+        else:
+            tv = t.detach().reshape(-1).to(torch.float32) if torch.is_tensor(t) else torch.tensor([float(t)])
+            n_t = tv.numel()
+        if n_t not in (1, B):
+            raise ValueError(f"t must be a scalar or hold one time per clip ({B}), got {n_t} values")
         with torch.cuda.device(dev):
             st = torch.cuda.current_stream(dev).cuda_stream
-            if tv.numel() == 1:
+            if t_dev is not None:
+                _lib.check(eng.lib.srn_estimator_forward_tdev(eng.h, xf.data_ptr(), muf.data_ptr(), m8.data_ptr(),
+                                                              spk.data_ptr(), t_dev.data_ptr(), n_t, B, T, out.data_ptr(),
+                                                              C.c_void_p(st)), "srn_estimator_forward_tdev")
+            elif n_t == 1:
                 _lib.check(eng.lib.srn_estimator_forward(eng.h, xf.data_ptr(), muf.data_ptr(), m8.data_ptr(),
                                                          spk.data_ptr(), C.c_float(float(tv[0])), B, T, out.data_ptr(),
                                                          C.c_void_p(st)), "srn_estimator_forward")

@@ -143,6 +143,18 @@ SRN_EXPORT int srn_estimator_forward_t(SrnHandle* h, const float* x, const float
   SRN_API_END
 }
 
+SRN_EXPORT int srn_estimator_forward_tdev(SrnHandle* h, const float* x, const float* mu, const uint8_t* mask,
+                                          const float* spk, const float* t_dev, int32_t n_t, int32_t B, int32_t T,
+                                          float* v_out, void* stream) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (!x || !mu || !mask || !spk || !t_dev || !v_out) srn::fail("srn_estimator_forward_tdev: null argument");
+  if (B < 1 || T < 2) srn::fail("srn_estimator_forward_tdev: need B >= 1 and T >= 2 (got B=%d T=%d)", B, T);
+  if (n_t != 1 && n_t != B) srn::fail("srn_estimator_forward_tdev: n_t must be 1 or B = %d (got %d)", B, n_t);
+  h->eng->estimator_forward_tdev(x, mu, mask, spk, t_dev, n_t, B, T, v_out, static_cast<cudaStream_t>(stream));
+  SRN_API_END
+}
+
 SRN_EXPORT int srn_cfm_loss(SrnHandle* h, const float* x1, const float* z, const float* t_host, const float* mu,
                             const uint8_t* mask, const float* spk, const uint8_t* mask_l, int32_t B, int32_t T,
                             float sigma_min, float* y_out, float* loss_out, void* stream) {

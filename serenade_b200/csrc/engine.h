@@ -29,6 +29,9 @@ class EngineBase {
   // per-clip times t[B] (host): what Decoder.forward does when t is a vector (decoder.py:401-402)
   virtual void estimator_forward_t(const float* x, const float* mu, const uint8_t* mask, const float* spk,
                                    const float* t_host, int B, int T, float* v_out, cudaStream_t st) = 0;
+  // the time(s) in device memory: n_t = 1 (shared by the batch) or B (one per clip); no host round trip
+  virtual void estimator_forward_tdev(const float* x, const float* mu, const uint8_t* mask, const float* spk,
+                                      const float* t_dev, int n_t, int B, int T, float* v_out, cudaStream_t st) = 0;
   // CFM.compute_loss forward value (flow_matching.py:95-133) for given noise z and times t; no gradients
   virtual void cfm_loss(const float* x1, const float* z, const float* t_host, const float* mu, const uint8_t* mask,
                         const float* spk, const uint8_t* mask_l, int B, int T, float sigma_min, float* y_out,

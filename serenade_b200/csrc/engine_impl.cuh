@@ -130,6 +130,8 @@ class Engine : public EngineBase {
                          int T, float* v_out, cudaStream_t st) override;
   void estimator_forward_t(const float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_host,
                            int B, int T, float* v_out, cudaStream_t st) override;
+  void estimator_forward_tdev(const float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_dev,
+                              int n_t, int B, int T, float* v_out, cudaStream_t st) override;
   void cfm_loss(const float* x1, const float* z, const float* t_host, const float* mu, const uint8_t* mask,
                 const float* spk, const uint8_t* mask_l, int B, int T, float sigma_min, float* y_out, float* loss_out,
                 cudaStream_t st) override;
@@ -231,6 +233,14 @@ class Engine : public EngineBase {
   int tb_bstride_ = 0;          // 512 while an estimator call with per-clip times runs (estimator_forward_t)
   DevBuf loss_v_, loss_part_, loss_lmask_;
   cudaStream_t capture_stream_ = nullptr;
+  // Pinned staging for the small per-call tables (t, dt, per-clip t): the host values go through a page-locked slot so
+  // that the upload needs no stream synchronisation; a slot is reused only after its own copy has finished.
+  static constexpr int kPinSlots = 4;
+  static constexpr size_t kPinSlotFloats = 4096;
+  float* pin_ = nullptr;
+  cudaEvent_t pin_ev_[kPinSlots] = {};
+  int pin_next_ = 0;
+  void upload_floats(void* dst_dev, const float* src_host, size_t n, cudaStream_t st);
 
   // weights
   const HostTensor& hw(const std::string& key, std::initializer_list<int64_t> dims);
@@ -259,6 +269,8 @@ class Engine : public EngineBase {
   void solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bool blend, cudaStream_t st);
   void capture_tap(const Plan<OT>& pl, const Tap& tap, cudaStream_t st);
   void check_abort();
+  void estimator_forward_times(const float* x, const float* mu, const uint8_t* mask, const float* spk,
+                               const float* t_src, bool t_on_device, int n_t, int B, int T, float* v_out, cudaStream_t st);
 };
 
 }  // namespace srn

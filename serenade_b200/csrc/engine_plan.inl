@@ -165,7 +165,11 @@ inline int pick_bn(int N, long long row_tiles) {
   if (!little_waste) return 128;
   // waves x relative cost of one tile (a 256 x 128 tile costs a bit more than half a 256 x 256 one)
   const double c256 = (double)((nt256 * row_tiles + 73) / 74) * 1.0;
-  const double c128 = (double)((nt128 * row_tiles + 73) / 74) * 0.58;
+  static const double k128 = [] {      // SRN_BN128_COST: A/B switch for the cost ratio (profiles/r02_ab_bn128.txt)
+    const char* e = getenv("SRN_BN128_COST");
+    return e != nullptr && atof(e) > 0.0 ? atof(e) : 0.58;
+  }();
+  const double c128 = (double)((nt128 * row_tiles + 73) / 74) * k128;
   return c256 <= c128 ? 256 : 128;
 }
 }  // namespace

@@ -289,6 +289,30 @@ void Engine<OT>::stage_inputs(Plan<OT>& pl, const float* x, const float* mu, con
   SRN_CUDA(cudaMemcpyAsync(pl.spk_in.p, spk, (size_t)B * cfg_.spk_embed_dim * 4, kind, st));
 }
 
+// n floats from ordinary host memory to the device on `st` without blocking the host on the stream: the values are
+// copied into a page-locked slot first and the slot is reused only once the copy out of it has completed (its event).
+// Tables larger than a slot (never the case for the reference's shapes) take the synchronising path.
+template <typename OT>
+void Engine<OT>::upload_floats(void* dst_dev, const float* src_host, size_t n, cudaStream_t st) {
+  if (n == 0) return;
+  if (n > kPinSlotFloats) {
+    SRN_CUDA(cudaMemcpyAsync(dst_dev, src_host, n * 4, cudaMemcpyHostToDevice, st));
+    SRN_CUDA(cudaStreamSynchronize(st));
+    return;
+  }
+  if (pin_ == nullptr) {
+    SRN_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&pin_), kPinSlots * kPinSlotFloats * 4, cudaHostAllocDefault));
+    for (auto& e : pin_ev_) SRN_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  const int slot = pin_next_;
+  pin_next_ = (pin_next_ + 1) % kPinSlots;
+  SRN_CUDA(cudaEventSynchronize(pin_ev_[slot]));      // (returns at once for an event never recorded)
+  float* h = pin_ + (size_t)slot * kPinSlotFloats;
+  std::memcpy(h, src_host, n * 4);
+  SRN_CUDA(cudaMemcpyAsync(dst_dev, h, n * 4, cudaMemcpyHostToDevice, st));
+  SRN_CUDA(cudaEventRecord(pin_ev_[slot], st));
+}
+
 // Step-invariant work hoisted out of the Euler loop (SURVEY.md finding 10): mu columns of the packed
 // conv input, SpeakerAdapter scale / bias per resnet, and the time-embedding MLP + per-resnet time bias
 // for every step (the time path depends only on t, which the whole batch shares: decoder.py:401-402, :97).
@@ -385,18 +409,36 @@ void Engine<OT>::estimator_forward(const float* x, const float* mu, const uint8_
 template <typename OT>
 void Engine<OT>::estimator_forward_t(const float* x, const float* mu, const uint8_t* mask, const float* spk,
                                      const float* t_host, int B, int T, float* v_out, cudaStream_t st) {
+  estimator_forward_times(x, mu, mask, spk, t_host, false, B, B, T, v_out, st);
+}
+
+// The same with the time(s) in DEVICE memory - one value shared by the batch (n_t = 1: what the reference's solve_euler
+// hands its estimator, a 0-dim CUDA tensor) or one per clip (n_t = B).  Nothing comes back to the host.
+template <typename OT>
+void Engine<OT>::estimator_forward_tdev(const float* x, const float* mu, const uint8_t* mask, const float* spk,
+                                        const float* t_dev, int n_t, int B, int T, float* v_out, cudaStream_t st) {
+  if (n_t != 1 && n_t != B) fail("estimator_forward_tdev: n_t must be 1 or B (%d), got %d", B, n_t);
+  estimator_forward_times(x, mu, mask, spk, t_dev, true, n_t, B, T, v_out, st);
+}
+
+template <typename OT>
+void Engine<OT>::estimator_forward_times(const float* x, const float* mu, const uint8_t* mask, const float* spk,
+                                         const float* t_src, bool t_on_device, int n_t, int B, int T, float* v_out,
+                                         cudaStream_t st) {
   Plan<OT>& pl = get_plan(B, T);
   last_plan_ = &pl;
   pl.staged_ts.clear();
-  ensure_step_buffers(pl, B, cfg_.in_channels, (int)resnets_.size());
+  ensure_step_buffers(pl, n_t, cfg_.in_channels, (int)resnets_.size());
   stage_inputs(pl, x, mu, mask, spk, cudaMemcpyDeviceToDevice, st);
-  const std::vector<float> ts(t_host, t_host + B), zeros(B, 0.f);
-  SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, ts.data(), (size_t)B * 4, cudaMemcpyHostToDevice, st));
-  SRN_CUDA(cudaMemcpyAsync(pl.dts.p, zeros.data(), (size_t)B * 4, cudaMemcpyHostToDevice, st));
-  SRN_CUDA(cudaStreamSynchronize(st));   // ts / zeros are host temporaries
+  if (t_on_device)
+    SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, t_src, (size_t)n_t * 4, cudaMemcpyDeviceToDevice, st));
+  else
+    upload_floats(pl.tsteps.p, t_src, (size_t)n_t, st);        // (through pinned staging: no host sync)
+  SRN_CUDA(cudaMemsetAsync(pl.dts.p, 0, (size_t)n_t * 4, st));
   blend_active_ = false;
-  prepass(pl, ts, zeros, st);
-  tb_bstride_ = 512;
+  const std::vector<float> count(n_t, 0.f);                    // (the prepass reads the times on the device; it only
+  prepass(pl, count, count, st);                               //  needs to know how many there are)
+  tb_bstride_ = n_t == 1 ? 0 : 512;
   try {
     run_forward(pl, 0, v_out, false, st);
   } catch (...) {
@@ -423,8 +465,7 @@ void Engine<OT>::cfm_loss(const float* x1, const float* z, const float* t_host, 
   if (loss_v_.bytes < (size_t)n * 4) loss_v_.alloc((size_t)n * 4);
   if (loss_part_.bytes < (size_t)nblk * 16) loss_part_.alloc((size_t)nblk * 16);
   // t on the device first: the mix kernel reads it (estimator_forward_t stages the same values again)
-  SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, t_host, (size_t)B * 4, cudaMemcpyHostToDevice, st));
-  SRN_CUDA(cudaStreamSynchronize(st));
+  upload_floats(pl.tsteps.p, t_host, (size_t)B, st);
   launch_k(cfm_mix_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), st, x1, z, (const float*)pl.tsteps.template as<float>(),
            (long long)C * T, n, oms, y_out);
   ++launches;
@@ -454,13 +495,11 @@ void Engine<OT>::solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bo
   const size_t tb_before = pl.tb_steps;
   ensure_step_buffers(pl, n_steps, cfg_.in_channels, (int)resnets_.size());
   // The (t, dt) tables stay on the device between calls: a decode loop passes the same t_span every time, and then
-  // nothing is uploaded and the call never blocks the host (the copies below need a sync: ts / dts are temporaries).
+  // nothing is uploaded; a new t_span goes through pinned staging (upload_floats), so the call never blocks the host.
   const std::vector<float> span(t_span, t_span + n_steps + 1);
   if (tb_before != (size_t)pl.tb_steps || pl.staged_ts != span) {
-    SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, ts.data(), (size_t)n_steps * 4, cudaMemcpyHostToDevice, st));
-    SRN_CUDA(cudaMemcpyAsync(pl.dts.p, dts.data(), (size_t)n_steps * 4, cudaMemcpyHostToDevice, st));
-    SRN_CUDA(cudaStreamSynchronize(st));
-    check_abort();                       // (reports a timeout of an earlier asynchronous solve)
+    upload_floats(pl.tsteps.p, ts.data(), (size_t)n_steps, st);
+    upload_floats(pl.dts.p, dts.data(), (size_t)n_steps, st);
     pl.staged_ts = span;
   }
   blend_active_ = blend;

@@ -35,6 +35,9 @@ Engine<OT>::~Engine() {
   for (auto& g : voc_graphs_)
     if (g.exec) cudaGraphExecDestroy(g.exec);
   voc_graphs_.clear();
+  for (auto& e : pin_ev_)
+    if (e) cudaEventDestroy(e);
+  if (pin_) cudaFreeHost(pin_);
   plans_.clear();
   arena_.clear();
 }

@@ -75,6 +75,25 @@ def test_estimator_with_one_time_per_clip(prec, cfms, jitter_sd, dev):
     v_same = cfm.estimator(b.z.to(dev), b.mask.to(dev), b.mu.to(dev), torch.full((3,), 0.4), b.spks.to(dev))
     v_scalar = cfm.estimator(b.z.to(dev), b.mask.to(dev), b.mu.to(dev), torch.tensor(0.4), b.spks.to(dev))
     assert torch.equal(v_same, v_scalar)
+    # times that already live on the GPU take srn_estimator_forward_tdev (no device-to-host read): same bits, and a
+    # reference-style Euler loop over estimator(...) with a device-resident t reproduces the library's own solve loop
+    v_dev = cfm.estimator(b.z.to(dev), b.mask.to(dev), b.mu.to(dev), t.to(dev), b.spks.to(dev))
+    assert torch.equal(v_dev, v)
+    v_dev0 = cfm.estimator(b.z.to(dev), b.mask.to(dev), b.mu.to(dev), torch.tensor(0.4, device=dev), b.spks.to(dev))
+    assert torch.equal(v_dev0, v_scalar)
+    x = b.z.to(dev)
+    mask, mu, spk = b.mask.to(dev), b.mu.to(dev), b.spks.to(dev)
+    t_span = torch.linspace(0, 1, 4, device=dev)
+    tt, dt = t_span[0], t_span[1] - t_span[0]
+    for step in range(1, 4):                                  # flow_matching.py:79-91, all on the device
+        x = x + dt * cfm.estimator(x, mask, mu, tt, spk)
+        tt = tt + dt
+        if step < 3:
+            dt = t_span[step + 1] - tt
+    want = cfm.solve_euler(b.z.to(dev), t_span=t_span, mu=mu, mask=mask, trg_spks=spk)
+    # the fused Euler update rounds x + dt v once, torch twice: last-bit differences in x, which a bf16 operand
+    # rounding of the next step's input can amplify - far below the per-step tolerance either way
+    assert rel_l2(x.cpu(), want.cpu()) < 1e-3
 
 
 def test_loss_draws_like_the_reference_and_rejects_bad_input(cfms, dev):

@@ -1,4 +1,4 @@
-"""Per-op CUDA-event timing table of one estimator call (srn_profile_ops).  python tools/profile_ops.py B T [out]"""
+"""Per-op CUDA-event timing table of one estimator call (srn_profile_ops).  python tools/profile_ops.py B T [out] [reps]"""
 import json
 import os
 import sys
@@ -12,13 +12,14 @@ import serenade_b200 as S  # noqa: E402
 def main():
     B, T = int(sys.argv[1]), int(sys.argv[2])
     out = sys.argv[3] if len(sys.argv) > 3 else None
+    reps = int(sys.argv[4]) if len(sys.argv) > 4 else 5
     dev = torch.device("cuda", 0)
     cfm = S.CFM(in_channels=242, out_channels=80, spk_embed_dim=256, decoder_channels=(512, 512),
                 decoder_attention_head_dim=512)
     cfm.load_state_dict(S.make_state_dict(0, False), strict=True)
-    ops = cfm.estimator.engine(dev).profile_ops(B, T, reps=5)
+    ops = cfm.estimator.engine(dev).profile_ops(B, T, reps=reps)
     tot = sum(o["ms"] for o in ops)
-    lines = [f"# per-op timing, one estimator call, B={B} T={T}, total {tot:.3f} ms (isolated, hot L2, CUDA events)"]
+    lines = [f"# per-op timing, one estimator call, B={B} T={T}, total {tot:.3f} ms (isolated, hot L2, CUDA events, {reps} launches per op)"]
     agg = {}
     for o in ops:
         tf = o["flops"] / o["ms"] / 1e9 if o["flops"] else 0.0
