@@ -96,6 +96,37 @@ def test_estimator_with_one_time_per_clip(prec, cfms, jitter_sd, dev):
     assert rel_l2(x.cpu(), want.cpu()) < 1e-3
 
 
+def test_estimator_call_can_be_captured_in_the_callers_cuda_graph(cfms, dev):
+    """With `t` on the device the single-step entry point enqueues copies and kernels only (no allocation, no host
+    synchronisation, no host-side value baked into a launch), so a caller can capture it in their own CUDA graph - e.g. a
+    custom solver loop - and replay it with new inputs."""
+    import serenade_b200 as S
+    cfm = cfms["bf16"]
+    b1 = S.make_batch([72, 64], n_steps=1, seed=51)
+    b2 = S.make_batch([72, 64], n_steps=1, seed=52)
+    mask, spk = b1.mask.to(dev), b1.spks.to(dev)
+    x, mu, t = b1.z.to(dev).clone(), b1.mu.to(dev).clone(), torch.tensor(0.3, device=dev)
+    eager1 = cfm.estimator(x, mask, mu, t, spk)                     # (also builds the plan: allocation happens here)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    side = torch.cuda.Stream(dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g, stream=side):
+            out = cfm.estimator(x, mask, mu, t, spk)
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, eager1)
+    x.copy_(b2.z.to(dev))
+    mu.copy_(b2.mu.to(dev))
+    t.fill_(0.8)
+    g.replay()
+    torch.cuda.synchronize()
+    got = out.clone()
+    eager2 = cfm.estimator(b2.z.to(dev), mask, b2.mu.to(dev), torch.tensor(0.8), spk)
+    assert torch.equal(got, eager2) and not torch.equal(got, eager1)
+
+
 def test_loss_draws_like_the_reference_and_rejects_bad_input(cfms, dev):
     import serenade_b200 as S
     cfm = cfms["bf16"]
