@@ -75,10 +75,10 @@ def _traffic(config):
             d = json.load(open(p))
             if d.get("config", "C2") != config:
                 continue
-            return float(d["dram_bytes_per_step"]), d.get("source", p)
+            return float(d["dram_bytes_per_step"]), d.get("source", p), d.get("dram_bytes_per_step_warm")
         except Exception:
             continue
-    return None, None
+    return None, None, None
 
 
 def _peaks():
@@ -373,7 +373,7 @@ def run_ours(args):
         best_ref = min((v["ms_per_step"] for v in gpu_ref.values() if isinstance(v, dict) and "ms_per_step" in v),
                        default=None)
         gpu_ref["speedup_over_best_eager"] = best_ref / ms_step if best_ref else None
-        traffic, traffic_src = _traffic(args.config)
+        traffic, traffic_src, traffic_warm = _traffic(args.config)
         threads = os.cpu_count() or 1
         cpu_fps, cpu_s = _cpu_decode_sample(cfg, threads, *cfg["cpu"])
         tf = lambda fl, ms: fl / (ms / 1e3) / 1e12 if ms else None
@@ -391,6 +391,7 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                          "frac": achieved / peaks["tf_sustained"], "traffic": traffic, "traffic_source": traffic_src,
+                         "traffic_warm_caches": traffic_warm,
                          "launch": f"one CUDA-graph launch = one step ({n_euler} Euler steps x {B} clips); gemm_kernel is the "
                                    "dominant kernel (its share of the step is gemm_share_of_step); FLOPs are SURVEY 8d's "
                                    "F(L) summed over the clips' VALID lengths",

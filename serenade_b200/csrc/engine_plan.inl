@@ -158,6 +158,13 @@ inline bool noshift_enabled() {
   }();
   return on;
 }
+inline bool zigzag_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("SRN_ZIGZAG");
+    return !(e != nullptr && e[0] == '0');
+  }();
+  return on;
+}
 // row_tiles = number of 256-row pair tiles; one CTA pair per SM pair (74 on a B200)
 inline int pick_bn(int N, long long row_tiles) {
   const long long nt256 = (N + 255) / 256, nt128 = (N + 127) / 128;
@@ -744,6 +751,18 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
     op.grid = dim3(1, pl.lv[0].mtiles, B);
     pl.euler_op = (int)pl.ops.size();
     pl.ops.push_back(op);
+  }
+  // Zig-zag tile order (GemmParams::rev): every GEMM walks its tiles in the direction opposite to the one in which its
+  // input was written, so that what the producer wrote last - the part of a larger-than-L2 tensor that is still cached -
+  // is read first.  Row kernels write in ascending order; the row-max pass reads what the exp pass reads (the QKV
+  // output) and is mostly skipped, so the exp pass takes the same direction.  SRN_ZIGZAG=0: all ascending.
+  if (zigzag_enabled()) {
+    int dir = 0;
+    for (Op& op : pl.ops) {
+      if (op.kind != OP_GEMM) { dir = 0; continue; }
+      op.gp.rev = 1 - dir;
+      if (op.gp.epi != EPI_ROWMAX) dir = op.gp.rev;
+    }
   }
 }
 

@@ -140,6 +140,7 @@ struct GemmParams {
   int* noshift;
   unsigned long long* ns_count;   // EPI_ROWMAX: [0] += shift-free entries, [1] += entries (statistics only), or null
   int nz_norm;      // number of (batch, head) entries of qk_norm2
+  int rev;          // 1: process the tiles in descending order (gemm_mainloop.cuh: logical)
   float noshift_max; // the bound below which an entry runs shift-free (64; SRN_NOSHIFT_MAX overrides it for tests)
   const uint8_t* keymask;   // (B, keys): key k of batch b takes part iff keymask[b*keymask_bstride + k*keymask_step] != 0
   int keymask_bstride;

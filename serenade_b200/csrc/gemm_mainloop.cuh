@@ -54,6 +54,10 @@ __global__ void __launch_bounds__(GemmCfg<BN>::kThreads, 1) gemm_kernel(const __
   const int npairs = gridDim.x / 2;
   // tiles of this pair: pair0, pair0 + npairs, ...
   const int t_begin = pair0, t_end = total_tiles, t_step = npairs;
+  // p.rev: the same tiles in the opposite order (last (z, mi, ni) first).  A launch whose input is larger than the L2
+  // and was written by the launch before it in ascending tile order finds the END of that tensor still cached and its
+  // beginning evicted; reading in the writer's order is the worst case for an LRU-like cache (every line misses).
+  auto logical = [&](int tile) -> int { return p.rev ? total_tiles - 1 - tile : tile; };
 
   pdl_launch_dependents();
   if (threadIdx.x == 0) SRN_STAMP(0);
@@ -154,8 +158,9 @@ __global__ void __launch_bounds__(GemmCfg<BN>::kThreads, 1) gemm_kernel(const __
   // divisions per tile in front of its MMAs cost the mainloop-bound launches ~450 clocks per tile.
   struct TileCoord {
     int z, mi, ni, a, c, d, ntn, ntm;
-    __device__ __forceinline__ void init(int tile, int step, int ntn_, int ntm_) {
-      ntn = ntn_; ntm = ntm_;
+    bool back;
+    __device__ __forceinline__ void init(int tile, int step, int ntn_, int ntm_, bool back_) {
+      ntn = ntn_; ntm = ntm_; back = back_;
       const int tmn = ntn * ntm;
       z = tile / tmn;
       const int rem = tile - z * tmn;
@@ -165,11 +170,19 @@ __global__ void __launch_bounds__(GemmCfg<BN>::kThreads, 1) gemm_kernel(const __
       c = r1 / ntn; d = r1 - c * ntn;
     }
     __device__ __forceinline__ void advance() {
-      ni += d;
-      if (ni >= ntn) { ni -= ntn; ++mi; }
-      mi += c;
-      if (mi >= ntm) { mi -= ntm; ++z; }
-      z += a;
+      if (!back) {
+        ni += d;
+        if (ni >= ntn) { ni -= ntn; ++mi; }
+        mi += c;
+        if (mi >= ntm) { mi -= ntm; ++z; }
+        z += a;
+      } else {
+        ni -= d;
+        if (ni < 0) { ni += ntn; --mi; }
+        mi -= c;
+        if (mi < 0) { mi += ntm; --z; }
+        z -= a;
+      }
     }
   };
   auto tile_nkb = [&](int ext, bool g1) -> int {
@@ -188,8 +201,9 @@ __global__ void __launch_bounds__(GemmCfg<BN>::kThreads, 1) gemm_kernel(const __
         uint32_t wa = 0, wap = 0, wb = 0, wbp = 0;
         const int kcb = p.seg[0].nblk;
         for (int tile = t_begin; tile < t_end; tile += t_step) {
-          const int z = tile / tiles_mn;
-          const int rem = tile % tiles_mn;
+          const int lt = logical(tile);
+          const int z = lt / tiles_mn;
+          const int rem = lt % tiles_mn;
           const int mi = rem / p.ntn, ni = rem - mi * p.ntn;
           const int b = z / p.HB;
           if (skip_pad(tile_ext(b), mi, ni)) continue;
@@ -216,9 +230,10 @@ __global__ void __launch_bounds__(GemmCfg<BN>::kThreads, 1) gemm_kernel(const __
         }
       } else {      // (the per-segment boxes of the plain path)
         for (int tile = t_begin; tile < t_end; tile += t_step) {
-          const int z = tile / tiles_mn;
+          const int lt = logical(tile);
+          const int z = lt / tiles_mn;
           if (skip_tile(z)) continue;
-          const int rem = tile % tiles_mn;
+          const int rem = lt % tiles_mn;
           const int mi = rem / p.ntn, ni = rem - mi * p.ntn;
           const int b = z / p.HB;
           const int ext = tile_ext(b);
@@ -256,7 +271,7 @@ __global__ void __launch_bounds__(GemmCfg<BN>::kThreads, 1) gemm_kernel(const __
       uint32_t stage = 0, phase = 0;
       uint32_t it = 0;
       TileCoord tc;
-      tc.init(t_begin, t_step, p.ntn, p.ntm);
+      tc.init(logical(t_begin), t_step, p.ntn, p.ntm, p.rev != 0);
       int cur_z = -1, cur_ext = 0x7fffffff;
       if (p.win) {
         uint32_t wa = 0, wap = 0, wb = 0, wbp = 0;
@@ -355,10 +370,11 @@ __global__ void __launch_bounds__(GemmCfg<BN>::kThreads, 1) gemm_kernel(const __
     };
     int pre_tile = -1;        // the tile pre_s / pre_k were requested for
     for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
-      const int z = tile / tiles_mn;
+      const int lt = logical(tile);
+      const int z = lt / tiles_mn;
       if (skip_tile(z)) { --it; continue; }
       const bool noshift = EPI == EPI_EXP && p.noshift != nullptr && s_ns[z] != 0;
-      const int rem = tile % tiles_mn;
+      const int rem = lt % tiles_mn;
       const int mi = rem / p.ntn, ni = rem - mi * p.ntn;
       const int b = z / p.HB;
       const int h = z - b * p.HB;
@@ -491,8 +507,8 @@ __global__ void __launch_bounds__(GemmCfg<BN>::kThreads, 1) gemm_kernel(const __
         // the next tile's side inputs: in flight during this tile's chunks
         const int tn = tile + t_step;
         if (tn < t_end) {
-          const int zn = tn / tiles_mn;
-          const int remn = tn % tiles_mn;
+          const int zn = logical(tn) / tiles_mn;
+          const int remn = logical(tn) % tiles_mn;
           pre_tile = tn;        // (a skipped tile's values are simply never used)
           if constexpr (EPI != EPI_ROWMAX) {
             const int rown = ((remn / p.ntn) * 2 + (int)rank) * 128 + q * 32 + lane;

@@ -30,6 +30,8 @@ def main():
     torch.cuda.synchronize()
     f = flags.cpu()
     bad = f.any(dim=1).nonzero().flatten().tolist()
+    bits = int(ref.view(torch.int32).to(torch.int64).sum().item())        # (exact: integer sum of the bit patterns)
+    print(f"bit checksum of the first solve: {bits}  (sum {float(ref.double().sum()):.6f})")
     print(f"{reps} solves of B={B} T={T} steps={n}: {len(bad)} differ from the first"
           + (f"; solves {bad[:12]}, clips {[f[i].nonzero().flatten().tolist() for i in bad[:12]]}" if bad else " (deterministic)"),
           flush=True)
