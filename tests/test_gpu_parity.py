@@ -233,6 +233,48 @@ def test_skipped_tiles_never_leak_stale_data(jitter_sd, dev):
     assert torch.equal(again, fresh)
 
 
+@pytest.mark.parametrize("lengths", [[2], [3], [5, 2], [9, 8, 3], [255], [257, 256, 1], [513, 40]], ids=str)
+def test_edge_shapes_vs_oracle(cfm_jitter, jitter_sd, dev, lengths):
+    """Shapes at the edges of the tiling: the two-frame minimum, odd lengths (the transposed conv's trimmed frame), one
+    frame either side of a 256-row tile, a one-frame clip inside a padded batch (its half-rate level has one frame, its
+    attention one key).  One estimator call and a 3-step solve against the oracle."""
+    import serenade_b200 as S
+    from oracle import cfm_oracle as O
+    b = S.make_batch(lengths, n_steps=3, seed=61)
+    t = torch.tensor(0.55)
+    v = cfm_jitter.estimator(b.z.to(dev), b.mask.to(dev), b.mu.to(dev), t, b.spks.to(dev)).cpu()
+    x = cfm_jitter.solve_euler(b.z.to(dev), b.t_span, b.mu.to(dev), b.mask.to(dev), b.spks.to(dev)).cpu()
+    with torch.inference_mode():
+        v_ref = O.estimator_forward(jitter_sd, b.z, b.mask, b.mu, t, b.spks)
+        x_ref = O.solve_euler(jitter_sd, b.z, b.t_span, b.mu, b.mask, b.spks)
+    ev, ex = rel_l2(v, v_ref), rel_l2(x, x_ref)
+    _report(f"edge_{'_'.join(map(str, lengths))}.txt", f"lengths {lengths}: per-step rel_l2={ev:.3e} final rel_l2={ex:.3e}")
+    assert torch.isfinite(v).all() and torch.isfinite(x).all()
+    assert ev < BF16_STEP_TOL and ex < BF16_FINAL_TOL
+    pad = ~b.mask.expand_as(x)
+    assert float(v[pad].abs().sum()) == 0.0 and torch.equal(x[pad], b.z[pad])
+
+
+def test_wide_batch_beyond_the_per_launch_tables(cfm_jitter, jitter_sd, dev):
+    """260 clips: more batch entries than the 256 row extents a launch keeps in shared memory (padded-frame skipping is
+    switched off for such a plan, engine_plan.inl) and more (batch, head) entries (1040) than the 1024 shift-free flags
+    (every entry then takes the row-max pass).  Same answer as the oracle."""
+    import serenade_b200 as S
+    from oracle import cfm_oracle as O
+    lengths = [4 + (7 * i) % 13 for i in range(260)]
+    b = S.make_batch(lengths, n_steps=2, seed=62)
+    t = torch.tensor(0.2)
+    v = cfm_jitter.estimator(b.z.to(dev), b.mask.to(dev), b.mu.to(dev), t, b.spks.to(dev)).cpu()
+    free, total = cfm_jitter.estimator.engine(dev).softmax_stats()
+    with torch.inference_mode():
+        v_ref = O.estimator_forward(jitter_sd, b.z, b.mask, b.mu, t, b.spks)
+    e = rel_l2(v, v_ref)
+    _report("wide_batch_260.txt", f"260 clips of 4..16 frames: per-step rel_l2={e:.3e}; shift-free entries {free}/{total}")
+    assert torch.isfinite(v).all() and e < BF16_STEP_TOL
+    pad = ~b.mask.expand_as(v)
+    assert float(v[pad].abs().sum()) == 0.0
+
+
 def test_solver_matches_oracle_mixed_lengths(cfm_jitter, jitter_sd, dev):
     import serenade_b200 as S
     from oracle import cfm_oracle as O
