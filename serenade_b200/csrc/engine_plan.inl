@@ -507,8 +507,14 @@ void Engine<OT>::build_plan(Plan<OT>& pl) {
   const int B = pl.B, T = pl.T, H = 4, C = 512;
   const int T2 = (T + 1) / 2;
   pl.Tp = 2 * T2;
-  pl.lv[0] = Level{T, pl.Tp, round_up(T, 8), cdiv(T, 256), 1};
-  pl.lv[1] = Level{T2, T2, round_up(T2, 8), cdiv(T2, 256), 2};
+  // Sp: the row pitch of P~, V^T and the softmax statistics.  A multiple of 64 elements keeps every 128-byte box row of
+  // the P~ V operands inside one 128-byte line (SRN_SP_ALIGN=8 restores the round-1 pitch for the A/B)
+  static const int sp_align = [] {
+    const char* e = getenv("SRN_SP_ALIGN");
+    return e != nullptr && atoi(e) >= 8 ? atoi(e) : 64;
+  }();
+  pl.lv[0] = Level{T, pl.Tp, round_up(T, sp_align), cdiv(T, 256), 1};
+  pl.lv[1] = Level{T2, T2, round_up(T2, sp_align), cdiv(T2, 256), 2};
   const size_t rows = (size_t)B * pl.Tp;
   const size_t es = sizeof(OT);
   pl.xin.alloc(rows * 256 * es);
