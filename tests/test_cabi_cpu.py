@@ -81,3 +81,33 @@ def test_product_package_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".inl", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src.replace("the oracle", ""), f"{f} references oracle/"
+
+
+def test_header_is_plain_c_and_links_from_a_c_program(tmp_path):
+    """The boundary is a C ABI: include/serenade_b200.h compiles as C (gcc -std=c99 -Wall -Werror), and a C program that takes
+    the address of every declared entry point links against the in-tree library and runs its two GPU-free calls."""
+    import re
+    import shutil
+    import subprocess
+    from serenade_b200 import _lib
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "serenade_b200.h")).read()
+    names = sorted(set(re.findall(r"\b(srn_[a-z0-9_]+)\s*\(", hdr)))
+    assert set(names) == set(_lib.EXPORTED_SYMBOLS)
+    src = tmp_path / "link_check.c"
+    src.write_text('#include <stdio.h>\n#include "serenade_b200.h"\nint main(void) {\n  void* fns[] = {'
+                   + ", ".join(f"(void*){n}" for n in names)
+                   + '};\n  unsigned i, n = 0;\n  for (i = 0; i < sizeof fns / sizeof fns[0]; ++i) n += fns[i] != 0;\n'
+                   '  printf("%u %d [%s]\\n", n, srn_version(), srn_last_error());\n  return 0;\n}\n')
+    exe = tmp_path / "link_check"
+    libdir = os.path.dirname(_lib.LIB_PATH)
+    cmd = ["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(root, "include"), str(src),
+           "-o", str(exe), "-L", libdir, "-l:" + os.path.basename(_lib.LIB_PATH), "-Wl,-rpath," + libdir]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    count, version = out.stdout.split()[:2]
+    assert int(count) == len(names) and int(version) >= 100
