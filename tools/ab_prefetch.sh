@@ -1,5 +1,7 @@
 #!/bin/bash
-# A/B of the L2 operand prefetch (SRN_PREFETCH_DIST = K blocks ahead; 0 = off) on one box: per-op table and C2 / C5 / C3 solves.
+# A/B of the L2 operand prefetch (SRN_PREFETCH_DIST = K blocks ahead; 0 = off) on one box: per-op table and C2 / C5 solves.
+# The switch existed only in the experiment build measured in profiles/r02_ab_prefetch.txt (the prefetch was slower and was
+# removed: DESIGN.md 3.4); the script is kept as the record of how those numbers were taken.
 TAG=${1:-pf}; shift; O=gpurun_out; mkdir -p $O
 for d in "$@"; do
   SRN_PREFETCH_DIST=$d timeout 200 python tools/profile_ops.py 16 1000 $O/${TAG}_ops_pf$d.txt 20 > /dev/null 2>&1; head -1 $O/${TAG}_ops_pf$d.txt
