@@ -85,6 +85,13 @@ int srn_solve_euler(SrnHandle* h, float* x_inout, const float* mu, const uint8_t
                     const float* t_span_host, int32_t n_steps, int32_t B, int32_t T, const uint8_t* blend_mask,
                     const float* blend_src, void* stream);
 
+/* srn_solve_euler with t_span in DEVICE memory (n_steps + 1 f32) - what the reference's CFM.inference builds
+ * (flow_matching.py:61: torch.linspace(..., device=mu.device)).  The (t, dt) tables are formed on the device with the same
+ * fp32 additions as on the host path, so the result is bit-identical and the call never waits for the stream. */
+int srn_solve_euler_tdev(SrnHandle* h, float* x_inout, const float* mu, const uint8_t* mask, const float* spk,
+                         const float* t_span_dev, int32_t n_steps, int32_t B, int32_t T, const uint8_t* blend_mask,
+                         const float* blend_src, void* stream);
+
 /* Same with HOST buffers (pinned for best speed): uploads z/mu/mask/spk, solves, downloads the mel. */
 int srn_solve_euler_host(SrnHandle* h, const float* z_host, const float* mu_host, const uint8_t* mask_host,
                          const float* spk_host, const float* t_span_host, int32_t n_steps, int32_t B, int32_t T,

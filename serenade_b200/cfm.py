@@ -129,8 +129,8 @@ def _as_mask_u8(mask: torch.Tensor, B: int, T: int, device) -> torch.Tensor:
 
 
 def _tspan_host(t_span: torch.Tensor) -> torch.Tensor:
-    """t_span as a contiguous f32 CPU tensor (the C ABI takes the grid from host memory).  Pass a CPU tensor to keep the
-    call asynchronous: a device tensor (what the reference builds, flow_matching.py:61) costs one blocking D2H read."""
+    """t_span as a contiguous f32 CPU tensor for the entry points that take the grid from host memory (solve_euler itself
+    keeps a CUDA t_span on the device: srn_solve_euler_tdev)."""
     return t_span.detach().to("cpu", torch.float32).contiguous()
 
 
@@ -350,21 +350,30 @@ class CFM(nn.Module):
         muf = mu.detach().to(device=dev, dtype=torch.float32).contiguous()
         spk = trg_spks.detach().to(device=dev, dtype=torch.float32).contiguous()
         m8 = _as_mask_u8(mask, B, T, dev)
-        ts = _tspan_host(t_span)
-        n_steps = ts.numel() - 1
+        # a grid that already lives on the GPU (the reference builds it there, flow_matching.py:61) stays there
+        ts_dev = t_span.detach().reshape(-1).to(device=dev, dtype=torch.float32).contiguous() if t_span.is_cuda else None
+        ts = _tspan_host(t_span) if ts_dev is None else None
+        n_steps = (ts_dev if ts_dev is not None else ts).numel() - 1
         if n_steps < 1:
             raise ValueError("t_span needs at least two points")
         bm = bs = None
         if blend_mask is not None:
             bm = _as_mask_u8(blend_mask, B, T, dev)
             bs = blend_src.detach().to(device=dev, dtype=torch.float32).contiguous()
-        ts_p = C.cast(C.c_void_p(ts.data_ptr()), C.POINTER(C.c_float))
         with torch.cuda.device(dev):
             st = torch.cuda.current_stream(dev).cuda_stream
-            _lib.check(eng.lib.srn_solve_euler(eng.h, xs.data_ptr(), muf.data_ptr(), m8.data_ptr(), spk.data_ptr(),
-                                               ts_p, n_steps, B, T, bm.data_ptr() if bm is not None else None,
-                                               bs.data_ptr() if bs is not None else None, C.c_void_p(st)),
-                       "srn_solve_euler")
+            if ts_dev is not None:
+                _lib.check(eng.lib.srn_solve_euler_tdev(eng.h, xs.data_ptr(), muf.data_ptr(), m8.data_ptr(), spk.data_ptr(),
+                                                        ts_dev.data_ptr(), n_steps, B, T,
+                                                        bm.data_ptr() if bm is not None else None,
+                                                        bs.data_ptr() if bs is not None else None, C.c_void_p(st)),
+                           "srn_solve_euler_tdev")
+            else:
+                ts_p = C.cast(C.c_void_p(ts.data_ptr()), C.POINTER(C.c_float))
+                _lib.check(eng.lib.srn_solve_euler(eng.h, xs.data_ptr(), muf.data_ptr(), m8.data_ptr(), spk.data_ptr(),
+                                                   ts_p, n_steps, B, T, bm.data_ptr() if bm is not None else None,
+                                                   bs.data_ptr() if bs is not None else None, C.c_void_p(st)),
+                           "srn_solve_euler")
         return xs if T == T_in else xs[:, :, :T_in].contiguous()
 
     @torch.inference_mode()

@@ -179,6 +179,21 @@ SRN_EXPORT int srn_solve_euler(SrnHandle* h, float* x_inout, const float* mu, co
   SRN_API_END
 }
 
+SRN_EXPORT int srn_solve_euler_tdev(SrnHandle* h, float* x_inout, const float* mu, const uint8_t* mask, const float* spk,
+                                    const float* t_span_dev, int32_t n_steps, int32_t B, int32_t T,
+                                    const uint8_t* blend_mask, const float* blend_src, void* stream) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (!x_inout || !mu || !mask || !spk || !t_span_dev) srn::fail("srn_solve_euler_tdev: null argument");
+  if (B < 1 || T < 2 || n_steps < 1)
+    srn::fail("srn_solve_euler_tdev: need B >= 1, T >= 2, n_steps >= 1 (got %d, %d, %d)", B, T, n_steps);
+  if ((blend_mask == nullptr) != (blend_src == nullptr))
+    srn::fail("srn_solve_euler_tdev: blend_mask and blend_src must be given together");
+  h->eng->solve_euler(x_inout, mu, mask, spk, t_span_dev, n_steps, B, T, blend_mask, blend_src,
+                      static_cast<cudaStream_t>(stream), true);
+  SRN_API_END
+}
+
 SRN_EXPORT int srn_solve_euler_host(SrnHandle* h, const float* z_host, const float* mu_host, const uint8_t* mask_host,
                          const float* spk_host, const float* t_span_host, int32_t n_steps, int32_t B, int32_t T,
                          float* mel_out_host, void* stream) {

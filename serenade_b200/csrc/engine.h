@@ -38,7 +38,7 @@ class EngineBase {
                         float* loss_out, cudaStream_t st) = 0;
   virtual void solve_euler(float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
                            int n_steps, int B, int T, const uint8_t* blend_mask, const float* blend_src,
-                           cudaStream_t st) = 0;
+                           cudaStream_t st, bool t_span_on_device = false) = 0;
   virtual void solve_euler_host(const float* z, const float* mu, const uint8_t* mask, const float* spk,
                                 const float* t_span, int n_steps, int B, int T, float* mel_out, cudaStream_t st) = 0;
   virtual std::string profile_ops(int B, int T, int reps) = 0;

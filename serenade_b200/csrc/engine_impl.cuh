@@ -137,7 +137,7 @@ class Engine : public EngineBase {
                 cudaStream_t st) override;
   void solve_euler(float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
                    int n_steps, int B, int T, const uint8_t* blend_mask, const float* blend_src,
-                   cudaStream_t st) override;
+                   cudaStream_t st, bool t_span_on_device = false) override;
   void solve_euler_host(const float* z, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
                         int n_steps, int B, int T, float* mel_out, cudaStream_t st) override;
   std::string profile_ops(int B, int T, int reps) override;
@@ -266,7 +266,8 @@ class Engine : public EngineBase {
   void stage_inputs(Plan<OT>& pl, const float* x, const float* mu, const uint8_t* mask, const float* spk,
                     cudaMemcpyKind kind, cudaStream_t st);
   void prepass(Plan<OT>& pl, const std::vector<float>& ts, const std::vector<float>& dts, cudaStream_t st);
-  void solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bool blend, cudaStream_t st);
+  void solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bool blend, cudaStream_t st,
+                    bool t_span_on_device = false);
   void capture_tap(const Plan<OT>& pl, const Tap& tap, cudaStream_t st);
   void check_abort();
   void estimator_forward_times(const float* x, const float* mu, const uint8_t* mask, const float* spk,

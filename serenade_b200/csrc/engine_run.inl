@@ -478,10 +478,20 @@ void Engine<OT>::cfm_loss(const float* x1, const float* z, const float* t_host, 
 }
 
 template <typename OT>
-void Engine<OT>::solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bool blend, cudaStream_t st) {
+void Engine<OT>::solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bool blend, cudaStream_t st,
+                              bool t_span_on_device) {
   // flow_matching.py:79-91 in fp32: t += dt; dt = t_span[k+1] - t  (keeps the reference's last-ulp wobble)
-  std::vector<float> ts(n_steps), dts(n_steps);
-  {
+  std::vector<float> ts(n_steps), dts(n_steps);      // (the prepass only needs their length: it reads the device tables)
+  last_plan_ = &pl;
+  const size_t tb_before = pl.tb_steps;
+  ensure_step_buffers(pl, n_steps, cfg_.in_channels, (int)resnets_.size());
+  if (t_span_on_device) {
+    // the grid never visits the host: one thread builds the tables with the same additions (rowops.cuh)
+    launch_k(tspan_tables_kernel, dim3(1), dim3(32), st, t_span, n_steps, pl.tsteps.template as<float>(),
+             pl.dts.template as<float>());
+    ++launches;
+    pl.staged_ts.clear();
+  } else {
     float t = t_span[0];
     float dt = t_span[1] - t_span[0];
     for (int s = 1; s <= n_steps; ++s) {
@@ -490,17 +500,14 @@ void Engine<OT>::solve_staged(Plan<OT>& pl, const float* t_span, int n_steps, bo
       t = t + dt;
       if (s < n_steps) dt = t_span[s + 1] - t;
     }
-  }
-  last_plan_ = &pl;
-  const size_t tb_before = pl.tb_steps;
-  ensure_step_buffers(pl, n_steps, cfg_.in_channels, (int)resnets_.size());
-  // The (t, dt) tables stay on the device between calls: a decode loop passes the same t_span every time, and then
-  // nothing is uploaded; a new t_span goes through pinned staging (upload_floats), so the call never blocks the host.
-  const std::vector<float> span(t_span, t_span + n_steps + 1);
-  if (tb_before != (size_t)pl.tb_steps || pl.staged_ts != span) {
-    upload_floats(pl.tsteps.p, ts.data(), (size_t)n_steps, st);
-    upload_floats(pl.dts.p, dts.data(), (size_t)n_steps, st);
-    pl.staged_ts = span;
+    // The (t, dt) tables stay on the device between calls: a decode loop passes the same t_span every time, and then
+    // nothing is uploaded; a new t_span goes through pinned staging (upload_floats), so the call never blocks the host.
+    const std::vector<float> span(t_span, t_span + n_steps + 1);
+    if (tb_before != (size_t)pl.tb_steps || pl.staged_ts != span) {
+      upload_floats(pl.tsteps.p, ts.data(), (size_t)n_steps, st);
+      upload_floats(pl.dts.p, dts.data(), (size_t)n_steps, st);
+      pl.staged_ts = span;
+    }
   }
   blend_active_ = blend;
   if (use_graph && !debug) {
@@ -556,7 +563,7 @@ void Engine<OT>::softmax_stats(int64_t* out2) {
 template <typename OT>
 void Engine<OT>::solve_euler(float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
                              int n_steps, int B, int T, const uint8_t* blend_mask, const float* blend_src,
-                             cudaStream_t st) {
+                             cudaStream_t st, bool t_span_on_device) {
   NvtxRange range("srn.solve_euler");
   Plan<OT>& pl = get_plan(B, T);
   stage_inputs(pl, x, mu, mask, spk, cudaMemcpyDeviceToDevice, st);
@@ -565,7 +572,7 @@ void Engine<OT>::solve_euler(float* x, const float* mu, const uint8_t* mask, con
     SRN_CUDA(cudaMemcpyAsync(pl.blend_mask.p, blend_mask, (size_t)B * T, cudaMemcpyDeviceToDevice, st));
     SRN_CUDA(cudaMemcpyAsync(pl.blend_src.p, blend_src, (size_t)B * cfg_.out_channels * T * 4, cudaMemcpyDeviceToDevice, st));
   }
-  solve_staged(pl, t_span, n_steps, blend, st);
+  solve_staged(pl, t_span, n_steps, blend, st, t_span_on_device);
   SRN_CUDA(cudaMemcpyAsync(x, pl.x_state.p, (size_t)B * cfg_.out_channels * T * 4, cudaMemcpyDeviceToDevice, st));
 }
 

@@ -657,6 +657,23 @@ __global__ void set_scalars_kernel(float* __restrict__ a, float va, float* __res
   if (threadIdx.x == 0) { *a = va; *b = vb; }
 }
 
+// The (t, dt) tables of the Euler loop from a t_span that lives on the device, in the reference's own fp32 arithmetic
+// (flow_matching.py:79-91: t += dt; dt = t_span[k + 1] - t - the running t makes dt wobble in the last ulp, and the host
+// path of solve_staged does exactly the same additions): one thread, n sequential steps.
+__global__ void tspan_tables_kernel(const float* __restrict__ t_span, int n, float* __restrict__ ts, float* __restrict__ dts) {
+  pdl_launch_dependents();
+  pdl_wait();
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  float t = t_span[0];
+  float dt = __fsub_rn(t_span[1], t_span[0]);
+  for (int s = 1; s <= n; ++s) {
+    ts[s - 1] = t;
+    dts[s - 1] = dt;
+    t = __fadd_rn(t, dt);
+    if (s < n) dt = __fsub_rn(t_span[s + 1], t);
+  }
+}
+
 // emb[s][j] = sin(1000 t_s f_j), emb[s][half + j] = cos(...),  f_j = exp(-j ln(1e4)/(half-1))  (decoder.py:54-63)
 __global__ void sinusoid_kernel(const float* __restrict__ ts, int dim, float e /* ln(1e4)/(half-1) */,
                                 float* __restrict__ emb) {

@@ -275,6 +275,21 @@ def test_wide_batch_beyond_the_per_launch_tables(cfm_jitter, jitter_sd, dev):
     assert float(v[pad].abs().sum()) == 0.0
 
 
+def test_device_and_host_time_grids_give_identical_solves(cfm_jitter, dev):
+    """solve_euler with t_span on the GPU (what the reference's CFM.inference builds, flow_matching.py:61) forms its (t, dt)
+    tables on the device with the same fp32 additions as the host path: same bits, for a uniform grid whose step is not
+    representable (the running t wobbles in the last ulp) and for an uneven one."""
+    import serenade_b200 as S
+    b = S.make_batch([96, 64], n_steps=7, seed=63)
+    args = (b.mu.to(dev), b.mask.to(dev), b.spks.to(dev))
+    for grid in (torch.linspace(0, 1, 8), torch.tensor([0.0, 0.05, 0.2, 0.25, 0.6, 0.61, 1.0])):
+        x_host = cfm_jitter.solve_euler(b.z.to(dev), grid, *args)
+        x_dev = cfm_jitter.solve_euler(b.z.to(dev), grid.to(dev), *args)
+        x_host2 = cfm_jitter.solve_euler(b.z.to(dev), grid.clone(), *args)      # (and back: the cached host tables were dropped)
+        assert torch.equal(x_host, x_dev) and torch.equal(x_host, x_host2)
+        assert torch.isfinite(x_dev).all()
+
+
 def test_solver_matches_oracle_mixed_lengths(cfm_jitter, jitter_sd, dev):
     import serenade_b200 as S
     from oracle import cfm_oracle as O
