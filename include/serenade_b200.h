@@ -77,6 +77,12 @@ int srn_cfm_loss(SrnHandle* h, const float* x1, const float* z, const float* t_h
                  const float* spk, const uint8_t* mask_l, int32_t B, int32_t T, float sigma_min, float* y_out,
                  float* loss_out, void* stream);
 
+/* srn_cfm_loss with the times t_dev[B] in DEVICE memory, where the reference draws them (flow_matching.py:115:
+ * torch.rand([b, 1, 1], device=mu.device)): no device-to-host read, the call never waits for the stream. */
+int srn_cfm_loss_tdev(SrnHandle* h, const float* x1, const float* z, const float* t_dev, const float* mu,
+                      const uint8_t* mask, const float* spk, const uint8_t* mask_l, int32_t B, int32_t T, float sigma_min,
+                      float* y_out, float* loss_out, void* stream);
+
 /* x <- solve_euler(x, t_span, mu, mask, spk) in place on DEVICE memory.  t_span is a HOST array of
  * n_steps + 1 f32 values.  blend_mask / blend_src (DEVICE, nullable): optional infill blend, after
  * every step x[b,:,t] = blend_src[b,:,t] where blend_mask[b,t] != 0.  The reference has no blend

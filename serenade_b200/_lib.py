@@ -18,7 +18,7 @@ EXPORTED_SYMBOLS = [
     "srn_estimator_forward", "srn_solve_euler", "srn_solve_euler_host", "srn_launch_count", "srn_set_use_graph",
     "srn_debug_enable", "srn_debug_fetch", "srn_profile_ops", "srn_content_encode", "srn_style_encode",
     "srn_set_gn_valid_only", "srn_vocoder_set_dilations", "srn_vocoder_hop", "srn_vocoder_decode",
-    "srn_estimator_forward_t", "srn_estimator_forward_tdev", "srn_solve_euler_tdev", "srn_cfm_loss", "srn_set_option", "srn_softmax_stats",
+    "srn_estimator_forward_t", "srn_estimator_forward_tdev", "srn_solve_euler_tdev", "srn_cfm_loss_tdev", "srn_cfm_loss", "srn_set_option", "srn_softmax_stats",
     "srn_cfm_loss_from_velocity_noalloc",
 ]
 
@@ -58,6 +58,8 @@ def load_library() -> C.CDLL:
         lib.srn_estimator_forward_tdev.argtypes = [vp, f32p, f32p, u8p, f32p, f32p, i32, i32, i32, f32p, vp]
     lib.srn_cfm_loss.argtypes = [vp, f32p, f32p, C.POINTER(C.c_float), f32p, u8p, f32p, u8p, i32, i32, C.c_float, f32p, f32p,
                                  vp]
+    if hasattr(lib, "srn_cfm_loss_tdev"):
+        lib.srn_cfm_loss_tdev.argtypes = [vp, f32p, f32p, f32p, f32p, u8p, f32p, u8p, i32, i32, C.c_float, f32p, f32p, vp]
     lib.srn_solve_euler.argtypes = [vp, f32p, f32p, u8p, f32p, C.POINTER(C.c_float), i32, i32, i32, u8p, f32p, vp]
     if hasattr(lib, "srn_solve_euler_tdev"):
         lib.srn_solve_euler_tdev.argtypes = [vp, f32p, f32p, u8p, f32p, f32p, i32, i32, i32, u8p, f32p, vp]

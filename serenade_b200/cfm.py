@@ -307,18 +307,21 @@ class CFM(nn.Module):
         spk = spks.detach().to(device=dev, dtype=torch.float32).contiguous()
         m8 = _as_mask_u8(mask, B, T, dev)
         l8 = _as_mask_u8(mask_l, B, T, dev) if mask_l is not None else None
-        tv = t.detach().reshape(-1).to("cpu", torch.float32)
-        if tv.numel() != B:
+        if t.numel() != B:
             raise ValueError(f"t must hold one time per clip ({B})")
-        tarr = (C.c_float * B)(*tv.tolist())
         y = torch.empty_like(x1f)
         loss = torch.empty((), dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
             st = torch.cuda.current_stream(dev).cuda_stream
-            _lib.check(eng.lib.srn_cfm_loss(eng.h, x1f.data_ptr(), zf.data_ptr(), tarr, muf.data_ptr(), m8.data_ptr(),
-                                            spk.data_ptr(), l8.data_ptr() if l8 is not None else None, B, T,
-                                            C.c_float(self.sigma_min), y.data_ptr(), loss.data_ptr(), C.c_void_p(st)),
-                       "srn_cfm_loss")
+            tail = (muf.data_ptr(), m8.data_ptr(), spk.data_ptr(), l8.data_ptr() if l8 is not None else None, B, T,
+                    C.c_float(self.sigma_min), y.data_ptr(), loss.data_ptr(), C.c_void_p(st))
+            if t.is_cuda:       # drawn on the device like the reference's (flow_matching.py:115): it stays there
+                td = t.detach().reshape(-1).to(device=dev, dtype=torch.float32).contiguous()
+                _lib.check(eng.lib.srn_cfm_loss_tdev(eng.h, x1f.data_ptr(), zf.data_ptr(), td.data_ptr(), *tail),
+                           "srn_cfm_loss_tdev")
+            else:
+                tarr = (C.c_float * B)(*t.detach().reshape(-1).to(torch.float32).tolist())
+                _lib.check(eng.lib.srn_cfm_loss(eng.h, x1f.data_ptr(), zf.data_ptr(), tarr, *tail), "srn_cfm_loss")
         return loss, y
 
     @torch.inference_mode()

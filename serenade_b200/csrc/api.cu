@@ -166,6 +166,18 @@ SRN_EXPORT int srn_cfm_loss(SrnHandle* h, const float* x1, const float* z, const
   SRN_API_END
 }
 
+SRN_EXPORT int srn_cfm_loss_tdev(SrnHandle* h, const float* x1, const float* z, const float* t_dev, const float* mu,
+                                 const uint8_t* mask, const float* spk, const uint8_t* mask_l, int32_t B, int32_t T,
+                                 float sigma_min, float* y_out, float* loss_out, void* stream) {
+  SRN_API_BEGIN
+  check_handle(h);
+  if (!x1 || !z || !t_dev || !mu || !mask || !spk || !y_out || !loss_out) srn::fail("srn_cfm_loss_tdev: null argument");
+  if (B < 1 || T < 2) srn::fail("srn_cfm_loss_tdev: need B >= 1 and T >= 2 (got B=%d T=%d)", B, T);
+  h->eng->cfm_loss(x1, z, t_dev, mu, mask, spk, mask_l, B, T, sigma_min, y_out, loss_out, static_cast<cudaStream_t>(stream),
+                   true);
+  SRN_API_END
+}
+
 SRN_EXPORT int srn_solve_euler(SrnHandle* h, float* x_inout, const float* mu, const uint8_t* mask, const float* spk,
                     const float* t_span_host, int32_t n_steps, int32_t B, int32_t T, const uint8_t* blend_mask,
                     const float* blend_src, void* stream) {

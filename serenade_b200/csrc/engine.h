@@ -35,7 +35,7 @@ class EngineBase {
   // CFM.compute_loss forward value (flow_matching.py:95-133) for given noise z and times t; no gradients
   virtual void cfm_loss(const float* x1, const float* z, const float* t_host, const float* mu, const uint8_t* mask,
                         const float* spk, const uint8_t* mask_l, int B, int T, float sigma_min, float* y_out,
-                        float* loss_out, cudaStream_t st) = 0;
+                        float* loss_out, cudaStream_t st, bool t_on_device = false) = 0;
   virtual void solve_euler(float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
                            int n_steps, int B, int T, const uint8_t* blend_mask, const float* blend_src,
                            cudaStream_t st, bool t_span_on_device = false) = 0;

@@ -134,7 +134,7 @@ class Engine : public EngineBase {
                               int n_t, int B, int T, float* v_out, cudaStream_t st) override;
   void cfm_loss(const float* x1, const float* z, const float* t_host, const float* mu, const uint8_t* mask,
                 const float* spk, const uint8_t* mask_l, int B, int T, float sigma_min, float* y_out, float* loss_out,
-                cudaStream_t st) override;
+                cudaStream_t st, bool t_on_device = false) override;
   void solve_euler(float* x, const float* mu, const uint8_t* mask, const float* spk, const float* t_span,
                    int n_steps, int B, int T, const uint8_t* blend_mask, const float* blend_src,
                    cudaStream_t st, bool t_span_on_device = false) override;

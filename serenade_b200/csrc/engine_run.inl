@@ -454,7 +454,7 @@ void Engine<OT>::estimator_forward_times(const float* x, const float* mu, const 
 template <typename OT>
 void Engine<OT>::cfm_loss(const float* x1, const float* z, const float* t_host, const float* mu, const uint8_t* mask,
                           const float* spk, const uint8_t* mask_l, int B, int T, float sigma_min, float* y_out,
-                          float* loss_out, cudaStream_t st) {
+                          float* loss_out, cudaStream_t st, bool t_on_device) {
   Plan<OT>& pl = get_plan(B, T);
   pl.staged_ts.clear();
   const int C = cfg_.out_channels;
@@ -465,11 +465,14 @@ void Engine<OT>::cfm_loss(const float* x1, const float* z, const float* t_host, 
   if (loss_v_.bytes < (size_t)n * 4) loss_v_.alloc((size_t)n * 4);
   if (loss_part_.bytes < (size_t)nblk * 16) loss_part_.alloc((size_t)nblk * 16);
   // t on the device first: the mix kernel reads it (estimator_forward_t stages the same values again)
-  upload_floats(pl.tsteps.p, t_host, (size_t)B, st);
+  if (t_on_device)
+    SRN_CUDA(cudaMemcpyAsync(pl.tsteps.p, t_host, (size_t)B * 4, cudaMemcpyDeviceToDevice, st));
+  else
+    upload_floats(pl.tsteps.p, t_host, (size_t)B, st);
   launch_k(cfm_mix_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), st, x1, z, (const float*)pl.tsteps.template as<float>(),
            (long long)C * T, n, oms, y_out);
   ++launches;
-  estimator_forward_t(y_out, mu, mask, spk, t_host, B, T, loss_v_.template as<float>(), st);
+  estimator_forward_times(y_out, mu, mask, spk, t_host, t_on_device, B, B, T, loss_v_.template as<float>(), st);
   launch_k(cfm_loss_partial_kernel, dim3(nblk), dim3(256), st, (const float*)loss_v_.template as<float>(), x1, z, mask_l,
            mask_l != nullptr ? mask_l : mask, T, C, T, n, oms, loss_part_.template as<double>());
   launch_k(cfm_loss_final_kernel, dim3(1), dim3(32), st, (const double*)loss_part_.template as<double>(), nblk, C, loss_out);

@@ -53,6 +53,11 @@ def test_loss_matches_reference_golden(name, prec, cfms, dev):
     with open(os.path.join("gpurun_out", f"loss_{prec}_{name}.txt"), "w") as f:
         f.write(f"{name} ({prec}): loss {float(loss):.6f} reference {float(g['loss']):.6f} rel err {err:.2e}\n")
     assert err < LOSS_TOL[prec]
+    # t on the host (srn_cfm_loss) and on the device (srn_cfm_loss_tdev, above) are the same computation
+    loss_h, y_h = cfm.compute_loss(torch.from_numpy(g["x1"]).to(dev), b.mask.to(dev), b.mu.to(dev), b.spks.to(dev),
+                                   mask_l=mask_l.to(dev) if mask_l is not None else None,
+                                   z=torch.from_numpy(g["z"]).to(dev), t=torch.from_numpy(g["t"]))
+    assert torch.equal(loss_h, loss) and torch.equal(y_h, y)
 
 
 @pytest.mark.parametrize("prec", ["tf32", "bf16"])
