@@ -47,6 +47,37 @@ def test_batches_respect_limits_and_sort_descending():
     assert all(len(b) * lengths[b[0]] <= 220 or len(b) == 1 for b in small)
 
 
+def test_sharding_properties_hold_for_arbitrary_inputs():
+    """Property test (hypothesis): for any lengths, world size and limits - every clip lands on exactly one rank and in
+    exactly one batch, ranks differ by at most one clip's cost, batches are sorted longest-first and respect both limits,
+    and the assignment is deterministic."""
+    from hypothesis import given, settings
+    from hypothesis import strategies as st
+
+    @settings(max_examples=200, deadline=None)
+    @given(lengths=st.lists(st.integers(2, 6000), min_size=0, max_size=80), world=st.integers(1, 8),
+           max_batch=st.integers(1, 16), limit=st.one_of(st.none(), st.integers(6000, 40000)))
+    def check(lengths, world, max_batch, limit):
+        parts = sharding.assign_clips(lengths, world)
+        assert len(parts) == world
+        assert sorted(i for p in parts for i in p) == list(range(len(lengths)))
+        assert parts == sharding.assign_clips(list(lengths), world)
+        loads = [sum(estimator_flops(lengths[i]) for i in p) for p in parts]
+        if lengths:       # greedy longest-first: no rank exceeds another by more than the largest single clip
+            assert max(loads) - min(loads) <= max(estimator_flops(L) for L in lengths) + 1e-6
+        for p in parts:
+            batches = sharding.make_batches(p, lengths, max_batch=max_batch, max_padded_frames=limit)
+            assert sorted(i for b in batches for i in b) == sorted(p)
+            for b in batches:
+                ls = [lengths[i] for i in b]
+                assert 1 <= len(b) <= max_batch and ls == sorted(ls, reverse=True)
+                if limit is not None:
+                    assert len(b) == 1 or len(b) * ls[0] <= limit
+            firsts = [lengths[b[0]] for b in batches]
+            assert firsts == sorted(firsts, reverse=True)
+    check()
+
+
 def _worker(rank, world, port, n, q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     import torch.distributed as dist
